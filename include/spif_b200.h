@@ -1,0 +1,162 @@
+/* spif_b200.h -- C-ABI of the B200-native (sm_100a) sparse-FFN kernels.
+ *
+ * This is the drop-in boundary for SparkInfer's activation-sparse FFN path: every entry point below is what the
+ * reference's ggml CUDA backend would bind in place of its own kernels.  Citations are file:line in the reference
+ * tree (ganminghao/SparkInfer).  INTEGRATION.md shows the glue a maintainer adds to ggml-cuda.cu.
+ *
+ * Conventions (identical to the reference's op contract):
+ *   - all pointers are DEVICE pointers unless a name ends in _host; the callee borrows, never frees or retains;
+ *   - weights are contiguous row-major, one row per neuron, nb[1] = ggml_row_size(type, n_embd), for ALL THREE
+ *     matrices (W_down is stored transposed, src/llama-model.cpp:2763); rows must be 16-byte aligned;
+ *   - activations / mask / outputs are F32, contiguous, token-major (x + n_embd*tok, dst + n_ff*tok);
+ *   - `type` uses ggml's type ids (ggml/include/ggml.h:385-415);
+ *   - a neuron is active for token t  <=>  !(sparse_idx[t][neu] < thr)   (mm-sparse.cu:22; NaN counts as active);
+ *   - `neuron_idx` (nullable, I32[m]) maps weight row -> original neuron id exactly like the reference's GPU cache
+ *     (mm-sparse.cu:20): NULL means identity and m == n_ff.  The same mechanism expresses a GPU *shard*;
+ *   - work is enqueued on `stream`; no allocation, no implicit synchronisation, no default-stream use, re-entrant;
+ *     scratch comes from the caller (`ws`, sized by spif_workspace_size) so CUDA-graph capture is legal;
+ *   - every function returns 0 on success, a negative SPIF_E* code for argument errors, or a positive cudaError_t.
+ *     The glue turns non-zero into GGML_ABORT (the reference aborts on the same conditions).
+ * There is NO CPU fallback: without a CUDA device every compute entry point returns an error.
+ */
+#ifndef SPIF_B200_H
+#define SPIF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPIF_B200_ABI_VERSION 1
+
+typedef struct CUstream_st * spif_stream_t; /* == cudaStream_t */
+
+enum spif_type { /* ggml_type values */
+    SPIF_TYPE_F32  = 0,
+    SPIF_TYPE_F16  = 1,
+    SPIF_TYPE_Q4_0 = 2,
+    SPIF_TYPE_Q8_0 = 8,
+    SPIF_TYPE_BF16 = 30,
+};
+
+enum spif_arch { /* activation recipe between gate/up and down, src/llama-graph.cpp:1063-1094 */
+    SPIF_ARCH_PROSPARSE  = 0, /* h = fatrelu(gate, 0.01) * up      (LLM_ARCH_PROSPARSE_LLAMA) */
+    SPIF_ARCH_RELU_GATED = 1, /* h = relu(gate) * relu(up)         (BAMBOO, QWEN2)            */
+    SPIF_ARCH_RELU_UP    = 2, /* h = relu(up), no gate matrix      (OPT, FALCON)              */
+    SPIF_ARCH_SILU_GATED = 3, /* h = silu(gate) * up -- Llama-3 top-k config; no reference code path */
+};
+
+enum spif_flags {
+    /* Round x to the weight float type before the dot and the hidden value before the axpy, like the reference CPU
+     * backend does (ggml-cpu.c:1832-1856, 2196-2207).  Default (0) keeps both in F32 like the reference CUDA kernels
+     * (mm-sparse.cu:55-57, axpy-sparse.cu:44).  Only meaningful for F16/BF16 weights. */
+    SPIF_FLAG_CPU_ROUNDING = 1 << 0,
+    /* sparse_idx is indexed by weight row (shard-local mask of length m) instead of by neuron id */
+    SPIF_FLAG_MASK_BY_ROW  = 1 << 1,
+    /* accumulate the down projection with float atomics (fast, run-to-run unstable, like axpy-sparse.cu:84).
+     * Default is the deterministic two-level reduction. */
+    SPIF_FLAG_ATOMIC_DOWN  = 1 << 2,
+};
+
+enum spif_error {
+    SPIF_OK            = 0,
+    SPIF_E_TYPE        = -1, /* unsupported weight type for this op (reference: GGML_ABORT "unsupported type") */
+    SPIF_E_SHAPE       = -2, /* shape/alignment precondition violated (reference: GGML_ASSERT) */
+    SPIF_E_NULL        = -3, /* required pointer missing (reference: "missing sparse_idx") */
+    SPIF_E_WORKSPACE   = -4, /* ws too small / misaligned */
+    SPIF_E_UNSUPPORTED = -5,
+    SPIF_E_NO_DEVICE   = -6,
+};
+
+int          spif_abi_version(void);
+const char * spif_error_string(int code);
+/* number of SMs etc. of the current device; returns an error without a GPU */
+int          spif_device_sm_count(int * sm_count);
+
+size_t spif_row_size(int type, int64_t n_embd); /* == ggml_row_size */
+
+/* Scratch needed by any entry point below for these sizes (bytes; 256-byte aligned pointer required). */
+size_t spif_workspace_size(int n_embd, int n_ff, int n_tok);
+
+/* ---- mask -> compact active-index list -------------------------------------------------------------------------
+ * The reference never materialises the list (every kernel re-tests the float mask, mm-sparse.cu:22, axpy-sparse.cu:53);
+ * this is the north-star's "threshold mask + warp-ballot/prefix-scan compaction".  For each token t:
+ *   idx_out[t*m .. t*m+count_out[t])  = ascending weight rows r whose neuron is active for t.
+ * If union_idx/union_count are non-NULL they receive the same for "active for ANY token" (batched path).       */
+int spif_mask_compact(const float * sparse_idx, const int32_t * neuron_idx, int m, int n_ff, int n_tok, float thr,
+                      int flags, int32_t * idx_out, int32_t * count_out, int32_t * union_idx, int32_t * union_count,
+                      spif_stream_t stream);
+
+/* ---- top-k mask (Llama-3 / SiLU config; no reference code) ----------------------------------------
+ * sparse_idx_out[t][i] = 1.0f for the k largest score[t][i] (ties -> lower index), else 0.0f.                    */
+int spif_topk_mask(const float * score, int n_ff, int n_tok, int k, float * sparse_idx_out, void * ws, size_t ws_bytes,
+                   spif_stream_t stream);
+
+/* ---- GGML_OP_MUL_MAT_SPARSE (ggml.c:3310-3331; CUDA mm-sparse.cu:366-431, mmq-sparse.cu:293-394) ------------------
+ * dst[t][neu] = dot(W[row], x[t]) for active rows, 0 elsewhere (dst {n_ff, n_tok} is zero-filled by the callee).
+ * Types: F16, BF16, Q8_0 (reference) and Q4_0 (claimed by supports_op, ggml-cuda.cu:4594-4663, never implemented). */
+int spif_mul_mat_sparse(int type, const void * w, const float * x, const float * sparse_idx,
+                        const int32_t * neuron_idx, float * dst, int n_embd, int n_ff, int m, int n_tok, float thr,
+                        int flags, void * ws, size_t ws_bytes, spif_stream_t stream);
+
+/* ---- GGML_OP_AXPY_SPARSE (ggml.c:3333-3356; CUDA axpy-sparse.cu:139-204, axpyq-sparse.cu:135-185) -----------------
+ * dst[t][:] = sum over active rows with hid[t][neu] != 0 of hid[t][neu] * Wt[row][:]   (dst {n_embd, n_tok}).
+ * Deterministic (fixed summation order) unless SPIF_FLAG_ATOMIC_DOWN.                                              */
+int spif_axpy_sparse(int type, const void * wt, const float * hid, const float * sparse_idx,
+                     const int32_t * neuron_idx, float * dst, int n_embd, int n_ff, int m, int n_tok, float thr,
+                     int flags, void * ws, size_t ws_bytes, spif_stream_t stream);
+
+/* ---- GGML_OP_FATRELU / GGML_UNARY-style helpers next to the path (unary.cu:564-652) ----------------------------- */
+int spif_fatrelu(const float * x, float * y, int64_t n, float threshold, spif_stream_t stream);
+int spif_shifted_step(const float * x, float * y, int64_t n, float threshold, spif_stream_t stream);
+
+/* ---- predictor (build_predictor, src/llama-graph.cpp:865-894: six stock nodes in the reference) ------------------
+ * sparse_idx_out[t][i] = sigmoid(Wpd[i] . relu(Wpu . x[t] + bpu) + bpd[i]).  Wpu {n_embd, r}, Wpd {r, n_ff} row-major
+ * F16/BF16; biases nullable.  logits_out (nullable) receives the pre-sigmoid values (flip accounting).
+ * flags: SPIF_FLAG_CPU_ROUNDING rounds x and the hidden vector to the weight type like the CPU backend's mul_mat.   */
+int spif_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,
+                   const float * x, float * sparse_idx_out, float * logits_out, int n_embd, int r, int n_ff, int n_tok,
+                   int flags, void * ws, size_t ws_bytes, spif_stream_t stream);
+
+/* ---- whole layer: build_sparse_ffn (src/llama-graph.cpp:896-1142), GPU-resident rows ----------------------------
+ * Equivalent to MUL_MAT_SPARSE(up), MUL_MAT_SPARSE(gate), [+bias], activation, AXPY_SPARSE(down), [+bias] on the rows
+ * this device holds; the place to call it from is the fusion block of the node loop (ggml-cuda.cu:3578-3870).       */
+typedef struct spif_ffn_args {
+    int32_t arch;   /* enum spif_arch */
+    int32_t type;   /* enum spif_type of the three FFN matrices */
+    int32_t n_embd;
+    int32_t n_ff;   /* length of the mask / of a dense hidden vector */
+    int32_t m;      /* rows held here (== n_ff when neuron_idx == NULL) */
+    int32_t n_tok;
+    int32_t flags;  /* enum spif_flags */
+    float   thr;    /* SPIF_SPARSE_THRESHOLD, default 0.5f */
+    const void *    w_up;       /* {n_embd, m} */
+    const void *    w_gate;     /* {n_embd, m}; NULL for SPIF_ARCH_RELU_UP */
+    const void *    w_down_t;   /* {n_embd, m} (transposed down) */
+    const float *   b_up;       /* nullable, indexed by neuron id */
+    const float *   b_gate;     /* nullable */
+    const float *   b_down;     /* nullable {n_embd}; added once (pass NULL on all but one shard) */
+    const float *   x;          /* {n_embd, n_tok} */
+    const float *   sparse_idx; /* {n_ff, n_tok} (or {m, n_tok} with SPIF_FLAG_MASK_BY_ROW) */
+    const int32_t * neuron_idx; /* nullable I32[m] */
+    float *         y;          /* out {n_embd, n_tok} */
+    float *         hidden_out; /* nullable out, dense {n_ff, n_tok}: hid for active rows held here, 0 elsewhere */
+    int32_t *       stats_out;  /* nullable out I32[n_tok][4]: {n_active, n_nonzero_hidden, 0, 0} */
+} spif_ffn_args;
+
+int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif_stream_t stream);
+
+/* ---- balancer helpers (build_dfr, src/llama-graph.cpp:910-930; binbcast.cu:26-42; sumcols.cu; argsort.cu) ---------
+ * One fused kernel: per group of `g` consecutive neurons, delta = #(active, token) pairs, then
+ *   ema != 0 : dfr = lambda*dfr + (1-lambda)*delta/(n_tok*g)        (SPIF_DFR_EMA variant, binbcast.cu:28-34)
+ *   ema == 0 : dfr = lambda*dfr + delta/(n_tok*g)
+ * replacing shifted_step + sum_cols + reshape + sum_rows + scale_add.  In place on dfr_scores {n_ff/g}.            */
+int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,
+                    float * dfr_scores, spif_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPIF_B200_H */

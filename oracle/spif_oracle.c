@@ -488,7 +488,10 @@ int spifo_topk_mask(const float * score, int n_ff, int k, float * out) {
     for (int s = 0; s < k; ++s) {
         int best = s;
         for (int j = s + 1; j < n_ff; ++j) {
-            float a = score[ord[j]], b = score[ord[best]];
+            /* total order on the bit patterns (so -0 < +0 and NaNs are ordered), same key as the CUDA radix select */
+            uint32_t a = f2u(score[ord[j]]), b = f2u(score[ord[best]]);
+            a = (a & 0x80000000u) ? ~a : (a | 0x80000000u);
+            b = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
             if (a > b || (a == b && ord[j] < ord[best])) {
                 best = j;
             }

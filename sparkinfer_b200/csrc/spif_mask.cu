@@ -1,0 +1,253 @@
+// spif_mask.cu -- mask compaction (warp ballot + prefix scan), top-k mask, the two SparkInfer unary ops and the fused
+// DFR (decayed firing rate) update used by the balancer.
+//
+// Reference: the mask is the float tensor `sparse_idx`; no index list is ever built (mm-sparse.cu:22, axpy-sparse.cu:53).
+// fatrelu / shifted_step: ggml/src/ggml-cuda/unary.cu:564-652.  build_dfr: src/llama-graph.cpp:910-930 with
+// op_scale_add(_ema) ggml/src/ggml-cuda/binbcast.cu:26-42.
+#include "spif_common.cuh"
+
+// ---------------------------------------------------------------------------------------------------------------
+// One CTA per token (+ one for the union over tokens).  Warps own contiguous row chunks; two passes (count, then
+// rank = warp base + running ballot popcount), output ascending == the order the reference CPU loops visit rows
+// (ggml-cpu.c:1773-1779, 2195-2212).
+__global__ void __launch_bounds__(1024) spif_mask_compact_kernel(const float * __restrict__ sparse_idx,
+                                                                  const int32_t * __restrict__ neuron_idx, int m, int n_ff,
+                                                                  int n_tok, float thr, int by_row,
+                                                                  int32_t * __restrict__ idx_out,
+                                                                  int32_t * __restrict__ count_out,
+                                                                  int32_t * __restrict__ union_idx,
+                                                                  int32_t * __restrict__ union_count) {
+    __shared__ int warp_cnt[32];
+    const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+    const bool     is_union = (blockIdx.x == n_tok);
+    const int      mask_len = by_row ? m : n_ff;
+    const int      chunk    = ((m + nwarp * 32 - 1) / (nwarp * 32)) * 32;
+    const int      r0 = warp * chunk, r1 = min(r0 + chunk, m);
+
+    auto test = [&](int row) -> bool {
+        const int neu = neuron_idx ? __ldg(neuron_idx + row) : row;
+        const int mi  = by_row ? row : neu;
+        if (!is_union) {
+            return spif_is_active(__ldg(sparse_idx + (size_t) blockIdx.x * mask_len + mi), thr);
+        }
+        bool a = false;
+        for (int t = 0; t < n_tok; ++t) {
+            a = a || spif_is_active(__ldg(sparse_idx + (size_t) t * mask_len + mi), thr);
+        }
+        return a;
+    };
+
+    int cnt = 0;
+    for (int base = r0; base < r1; base += 32) {
+        const int  row = base + lane;
+        const bool a   = (row < r1) && test(row);
+        cnt += __popc(__ballot_sync(0xffffffffu, a));
+    }
+    if (lane == 0) {
+        warp_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < nwarp; ++w) {
+        const int v = warp_cnt[w];
+        before += (w < warp) ? v : 0;
+        total += v;
+    }
+    int32_t * out = is_union ? union_idx : idx_out + (size_t) blockIdx.x * m;
+    int       run = before;
+    for (int base = r0; base < r1; base += 32) {
+        const int      row  = base + lane;
+        const bool     a    = (row < r1) && test(row);
+        const unsigned ball = __ballot_sync(0xffffffffu, a);
+        if (a) {
+            out[run + __popc(ball & ((1u << lane) - 1u))] = row;
+        }
+        run += __popc(ball);
+    }
+    if (tid == 0) {
+        if (is_union) {
+            *union_count = total;
+        } else {
+            count_out[blockIdx.x] = total;
+        }
+    }
+}
+
+int spif_launch_mask_compact(const float * sparse_idx, const int32_t * neuron_idx, int m, int n_ff, int n_tok, float thr,
+                             int flags, int32_t * idx_out, int32_t * count_out, int32_t * union_idx, int32_t * union_count,
+                             cudaStream_t stream) {
+    const bool want_union = union_idx != nullptr && union_count != nullptr;
+    spif_mask_compact_kernel<<<n_tok + (want_union ? 1 : 0), 1024, 0, stream>>>(
+        sparse_idx, neuron_idx, m, n_ff, n_tok, thr, (flags & SPIF_FLAG_MASK_BY_ROW) ? 1 : 0, idx_out, count_out,
+        union_idx, union_count);
+    SPIF_CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// top-k mask: one CTA per token.  4-pass MSB radix select on order-preserving uint keys finds the k-th largest key;
+// everything above it is selected, ties at the threshold are taken in ascending index order (ballot prefix scan).
+__device__ __forceinline__ uint32_t float_key(float f) {
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // larger float -> larger key (NaN sorts by bit pattern)
+}
+
+__global__ void __launch_bounds__(1024) spif_topk_mask_kernel(const float * __restrict__ score, int n_ff, int k,
+                                                               float * __restrict__ out) {
+    __shared__ int      hist[256];
+    __shared__ uint32_t s_prefix, s_prefix_mask;
+    __shared__ int      s_k;
+    __shared__ int      warp_cnt[32];
+    const float *       sc = score + (size_t) blockIdx.x * n_ff;
+    float *             o  = out + (size_t) blockIdx.x * n_ff;
+    const int           tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+
+    if (k <= 0) {
+        for (int i = tid; i < n_ff; i += blockDim.x) {
+            o[i] = 0.f;
+        }
+        return;
+    }
+    if (k >= n_ff) {
+        for (int i = tid; i < n_ff; i += blockDim.x) {
+            o[i] = 1.f;
+        }
+        return;
+    }
+    if (tid == 0) {
+        s_prefix      = 0;
+        s_prefix_mask = 0;
+        s_k           = k;
+    }
+    for (int pass = 3; pass >= 0; --pass) {
+        for (int i = tid; i < 256; i += blockDim.x) {
+            hist[i] = 0;
+        }
+        __syncthreads();
+        const uint32_t pre = s_prefix, pmask = s_prefix_mask;
+        const int      sh  = pass * 8;
+        for (int i = tid; i < n_ff; i += blockDim.x) {
+            const uint32_t key = float_key(sc[i]);
+            if ((key & pmask) == pre) {
+                atomicAdd(&hist[(key >> sh) & 255], 1);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int need = s_k, b = 255;
+            for (; b > 0; --b) {
+                if (hist[b] >= need) {
+                    break;
+                }
+                need -= hist[b];
+            }
+            s_k           = need;  // how many to take among keys with this prefix digit
+            s_prefix      = pre | ((uint32_t) b << sh);
+            s_prefix_mask = pmask | (255u << sh);
+        }
+        __syncthreads();
+    }
+    const uint32_t kth      = s_prefix;  // key of the k-th largest
+    const int      need_eq  = s_k;       // how many keys == kth to take (lowest indices first)
+    // ordered pass over indices: warps own contiguous chunks
+    const int chunk = ((n_ff + nwarp * 32 - 1) / (nwarp * 32)) * 32;
+    const int r0 = warp * chunk, r1 = min(r0 + chunk, n_ff);
+    int       cnt = 0;
+    for (int base = r0; base < r1; base += 32) {
+        const int  i  = base + lane;
+        const bool eq = (i < r1) && float_key(sc[i]) == kth;
+        cnt += __popc(__ballot_sync(0xffffffffu, eq));
+    }
+    if (lane == 0) {
+        warp_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    int run = 0;
+    for (int w = 0; w < warp; ++w) {
+        run += warp_cnt[w];
+    }
+    for (int base = r0; base < r1; base += 32) {
+        const int      i    = base + lane;
+        const uint32_t key  = (i < r1) ? float_key(sc[i]) : 0u;
+        const bool     eq   = (i < r1) && key == kth;
+        const unsigned ball = __ballot_sync(0xffffffffu, eq);
+        if (i < r1) {
+            bool sel = key > kth;
+            if (eq) {
+                sel = (run + __popc(ball & ((1u << lane) - 1u))) < need_eq;
+            }
+            o[i] = sel ? 1.0f : 0.0f;
+        }
+        run += __popc(ball);
+    }
+}
+
+int spif_launch_topk_mask(const float * score, int n_ff, int n_tok, int k, float * out, cudaStream_t stream) {
+    spif_topk_mask_kernel<<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
+    SPIF_CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// GGML_OP_FATRELU: x > t ? x : 0 ; GGML_OP_SHIFTED_STEP: (x + t) > 0 ? 1 : 0     (unary.cu:571,616)
+template <int OP> __global__ void spif_unary_kernel(const float * __restrict__ x, float * __restrict__ y, int64_t n, float t) {
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const float v = x[i];
+        y[i]          = (OP == 0) ? ((v > t) ? v : 0.0f) : (((v + t) > 0.0f) ? 1.0f : 0.0f);
+    }
+}
+
+int spif_launch_unary(int op, const float * x, float * y, int64_t n, float t, cudaStream_t stream) {
+    if (n <= 0) {
+        return 0;
+    }
+    const int     threads = 256;
+    const int64_t blocks  = (n + threads - 1) / threads;
+    if (op == 0) {
+        spif_unary_kernel<0><<<(unsigned) blocks, threads, 0, stream>>>(x, y, n, t);
+    } else {
+        spif_unary_kernel<1><<<(unsigned) blocks, threads, 0, stream>>>(x, y, n, t);
+    }
+    SPIF_CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// DFR update: one warp per neuron group.  delta = number of (neuron in group, token) pairs that are active.
+__global__ void spif_dfr_update_kernel(const float * __restrict__ sparse_idx, int n_ff, int n_tok, int g, float thr,
+                                       float lambda, int ema, float * __restrict__ dfr) {
+    const int grp  = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n_g  = n_ff / g;
+    if (grp >= n_g) {
+        return;
+    }
+    int cnt = 0;
+    for (int e = lane; e < g * n_tok; e += 32) {
+        const int t = e / g, j = e - t * g;
+        // build_dfr tests with ggml_shifted_step(sparse_idx, -0.5): (p + (-thr)) > 0, i.e. strictly above the threshold
+        // (llama-graph.cpp:911, unary.cu:611-613) -- not the kernels' !(p < thr)
+        cnt += ((sparse_idx[(size_t) t * n_ff + (size_t) grp * g + j] + (-thr)) > 0.0f) ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    if (lane == 0) {
+        const float norm  = (float) n_tok * (float) g;
+        const float delta = (float) cnt / norm;
+        const float old   = dfr[grp];
+        dfr[grp]          = ema ? (lambda * old + (1.0f - lambda) * delta) : (lambda * old + delta);
+    }
+}
+
+int spif_launch_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,
+                           float * dfr, cudaStream_t stream) {
+    const int n_g     = n_ff / g;
+    const int threads = 256;
+    const int blocks  = (n_g * 32 + threads - 1) / threads;
+    spif_dfr_update_kernel<<<blocks, threads, 0, stream>>>(sparse_idx, n_ff, n_tok, g, thr, lambda, ema, dfr);
+    SPIF_CUDA_TRY(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,165 @@
+"""Host-side mirror of the reference's ggml operator surface for the sparse-FFN path.
+
+Names and argument meaning follow the reference's op constructors (ggml/include/ggml.h:964-980,1159-1165,1443-1455;
+ggml/src/ggml.c:3310-3356) and graph recipe (src/llama-graph.cpp:865-1142):
+
+    mul_mat_sparse(a, b, sparse_idx, neu_info)      GGML_OP_MUL_MAT_SPARSE
+    axpy_sparse(a, b, sparse_idx, neu_info)         GGML_OP_AXPY_SPARSE
+    fatrelu(a, threshold) / shifted_step(a, t)      GGML_OP_FATRELU / GGML_OP_SHIFTED_STEP
+    predictor(...)                                  llm_graph_context::build_predictor
+    sparse_ffn(...)                                 llm_graph_context::build_sparse_ffn (GPU-resident rows)
+
+Weights are passed as raw byte tensors (uint8, CUDA) in ggml row layout plus a ggml type id; activations are F32
+CUDA tensors, token-major.  Errors the reference turns into GGML_ASSERT/GGML_ABORT surface as SpifError.
+torch is used for device memory and streams only.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import FfnArgs, check
+
+GGML_TYPE_F32, GGML_TYPE_F16, GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_BF16 = 0, 1, 2, 8, 30
+ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
+FLAG_CPU_ROUNDING, FLAG_MASK_BY_ROW, FLAG_ATOMIC_DOWN = 1, 2, 4
+SPARSE_THRESHOLD = 0.5  # SPIF_SPARSE_THRESHOLD, mm-sparse.cu:5-7
+
+
+def _p(t):
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "device-resident contiguous tensor required"
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def row_size(ggml_type, n_embd):
+    return _lib.load().spif_row_size(ggml_type, n_embd)
+
+
+class Workspace:
+    """Caller-owned scratch (the analogue of ctx.pool() allocations, mmq-sparse.cu:339): allocated once, reused."""
+
+    def __init__(self, n_embd, n_ff, n_tok=1, device="cuda"):
+        self.nbytes = _lib.load().spif_workspace_size(n_embd, n_ff, n_tok)
+        self.buf = torch.empty(self.nbytes + 256, dtype=torch.uint8, device=device)
+        off = (-self.buf.data_ptr()) % 256
+        self.ptr = ctypes.c_void_p(self.buf.data_ptr() + off)
+
+
+def _ws(ws, n_embd, n_ff, n_tok, device):
+    return ws if ws is not None else Workspace(n_embd, n_ff, n_tok, device)
+
+
+def mask_compact(sparse_idx, neuron_idx=None, thr=SPARSE_THRESHOLD, flags=0, want_union=False):
+    """-> (idx [n_tok, m] int32, count [n_tok] int32[, union_idx [m], union_count [1]])"""
+    L = _lib.load()
+    n_tok, n_mask = sparse_idx.shape
+    m = n_mask if neuron_idx is None else neuron_idx.numel()
+    n_ff = n_mask  # with FLAG_MASK_BY_ROW the mask is shard-local and n_mask == m
+    idx = torch.empty((n_tok, m), dtype=torch.int32, device=sparse_idx.device)
+    cnt = torch.empty((n_tok,), dtype=torch.int32, device=sparse_idx.device)
+    uidx = torch.empty((m,), dtype=torch.int32, device=sparse_idx.device) if want_union else None
+    ucnt = torch.empty((1,), dtype=torch.int32, device=sparse_idx.device) if want_union else None
+    check(L.spif_mask_compact(_p(sparse_idx), _p(neuron_idx), m, n_ff, n_tok, thr, flags, _p(idx), _p(cnt), _p(uidx),
+                              _p(ucnt), _stream()), "spif_mask_compact")
+    return (idx, cnt, uidx, ucnt) if want_union else (idx, cnt)
+
+
+def topk_mask(score, k):
+    L = _lib.load()
+    n_tok, n_ff = score.shape
+    out = torch.empty_like(score)
+    check(L.spif_topk_mask(_p(score), n_ff, n_tok, k, _p(out), None, 0, _stream()), "spif_topk_mask")
+    return out
+
+
+def mul_mat_sparse(a, a_type, b, sparse_idx, neu_info=None, n_ff=None, thr=SPARSE_THRESHOLD, flags=0, ws=None):
+    """ggml_mul_mat_sparse(ctx, a, b, sparse_idx, neu_info): a = weights {n_embd, m} (bytes), b = x {n_embd, n_tok},
+    result {n_ff, n_tok} F32, zero where inactive (ggml.c:3310-3331)."""
+    L = _lib.load()
+    n_tok, n_embd = b.shape
+    m = a.numel() // max(1, row_size(a_type, n_embd)) if neu_info is None else neu_info.numel()
+    n_ff = n_ff if n_ff is not None else (sparse_idx.shape[1] if not (flags & FLAG_MASK_BY_ROW) else m)
+    dst = torch.empty((n_tok, n_ff), dtype=torch.float32, device=b.device)
+    ws = _ws(ws, n_embd, n_ff, n_tok, b.device)
+    check(L.spif_mul_mat_sparse(a_type, _p(a), _p(b), _p(sparse_idx), _p(neu_info), _p(dst), n_embd, n_ff, m, n_tok, thr,
+                                flags, ws.ptr, ws.nbytes, _stream()), "spif_mul_mat_sparse")
+    return dst
+
+
+def axpy_sparse(a, a_type, b, sparse_idx, neu_info=None, n_embd=None, thr=SPARSE_THRESHOLD, flags=0, ws=None):
+    """ggml_axpy_sparse(ctx, a, b, sparse_idx, neu_info): a = W_down^T {n_embd, m} (bytes), b = hidden {n_ff, n_tok},
+    result {n_embd, n_tok} (ggml.c:3333-3356)."""
+    L = _lib.load()
+    n_tok, n_ff = b.shape
+    assert n_embd is not None
+    m = a.numel() // max(1, row_size(a_type, n_embd)) if neu_info is None else neu_info.numel()
+    dst = torch.empty((n_tok, n_embd), dtype=torch.float32, device=b.device)
+    ws = _ws(ws, n_embd, n_ff, n_tok, b.device)
+    check(L.spif_axpy_sparse(a_type, _p(a), _p(b), _p(sparse_idx), _p(neu_info), _p(dst), n_embd, n_ff, m, n_tok, thr,
+                             flags, ws.ptr, ws.nbytes, _stream()), "spif_axpy_sparse")
+    return dst
+
+
+def fatrelu(a, threshold):
+    L = _lib.load()
+    y = torch.empty_like(a)
+    check(L.spif_fatrelu(_p(a), _p(y), a.numel(), threshold, _stream()), "spif_fatrelu")
+    return y
+
+
+def shifted_step(a, threshold):
+    L = _lib.load()
+    y = torch.empty_like(a)
+    check(L.spif_shifted_step(_p(a), _p(y), a.numel(), threshold, _stream()), "spif_shifted_step")
+    return y
+
+
+def predictor(pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, n_ff, flags=0, want_logits=False, ws=None,
+              out=None):
+    """build_predictor(cur, pred_up, pred_up_b, pred_down, pred_down_b): -> sparse_idx {n_ff, n_tok} (and logits)"""
+    L = _lib.load()
+    n_tok, n_embd = cur.shape
+    out = out if out is not None else torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device)
+    logits = torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device) if want_logits else None
+    ws = _ws(ws, n_embd, n_ff, n_tok, cur.device)
+    check(L.spif_predictor(p_type, _p(pred_up), _p(pred_up_b), _p(pred_down), _p(pred_down_b), _p(cur), _p(out), _p(logits),
+                           n_embd, r, n_ff, n_tok, flags, ws.ptr, ws.nbytes, _stream()), "spif_predictor")
+    return (out, logits) if want_logits else out
+
+
+def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx=None, up_b=None, gate_b=None,
+               down_b=None, thr=SPARSE_THRESHOLD, flags=0, want_hidden=False, want_stats=False, ws=None, out=None):
+    """build_sparse_ffn for the rows resident on this device.  -> y {n_embd, n_tok} [, hidden {n_ff, n_tok}][, stats]"""
+    L = _lib.load()
+    n_tok, n_embd = cur.shape
+    m = n_ff if neuron_idx is None else neuron_idx.numel()
+    y = out if out is not None else torch.empty((n_tok, n_embd), dtype=torch.float32, device=cur.device)
+    hid = torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device) if want_hidden else None
+    stats = torch.zeros((n_tok, 4), dtype=torch.int32, device=cur.device) if want_stats else None
+    ws = _ws(ws, n_embd, n_ff, n_tok, cur.device)
+    a = FfnArgs(arch=arch, type=w_type, n_embd=n_embd, n_ff=n_ff, m=m, n_tok=n_tok, flags=flags, thr=thr,
+                w_up=_p(up), w_gate=_p(gate), w_down_t=_p(down_t), b_up=_p(up_b), b_gate=_p(gate_b), b_down=_p(down_b),
+                x=_p(cur), sparse_idx=_p(sparse_idx), neuron_idx=_p(neuron_idx), y=_p(y), hidden_out=_p(hid),
+                stats_out=_p(stats))
+    check(L.spif_sparse_ffn(ctypes.byref(a), ws.ptr, ws.nbytes, _stream()), "spif_sparse_ffn")
+    res = [y]
+    if want_hidden:
+        res.append(hid)
+    if want_stats:
+        res.append(stats)
+    return res[0] if len(res) == 1 else tuple(res)
+
+
+def dfr_update(sparse_idx, dfr_scores, g, lam, ema=True, thr=SPARSE_THRESHOLD):
+    """build_dfr's score update (src/llama-graph.cpp:911-918), in place on dfr_scores {n_ff / g}"""
+    L = _lib.load()
+    n_tok, n_ff = sparse_idx.shape
+    check(L.spif_dfr_update(_p(sparse_idx), n_ff, n_tok, g, thr, lam, 1 if ema else 0, _p(dfr_scores), _stream()),
+          "spif_dfr_update")
+    return dfr_scores

@@ -1,0 +1,112 @@
+"""GPU parity: the CUDA path (through the C-ABI) against the oracle on the same seeded inputs.  -m gpu."""
+import numpy as np
+import pytest
+
+import synth
+from oracle_lib import ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, BF16, F16, Q4_0, Q8_0, TYPE_NAMES
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def dev(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    return t.cuda() if dtype is None else t.to(dtype).cuda()
+
+
+def rel_err(a, b):
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+# tolerance, relative to max|y_oracle| (BASELINE.json north_star: 1e-3 for FP16; the format's own bound otherwise)
+TOL_DEFAULT = {F16: 1e-3, BF16: 8e-3, Q8_0: 2e-2, Q4_0: 2e-2}
+TOL_CPU_ROUNDING = {F16: 2e-5, BF16: 2e-5}
+
+SHAPES = [(512, 1024, 1), (1376, 2048, 1), (4096, 1536, 1), (5120, 1408, 1), (512, 1024, 3), (8192, 640, 2)]
+
+
+@pytest.mark.parametrize("wtype", [F16, BF16])
+@pytest.mark.parametrize("n_embd,n_ff,n_tok", SHAPES)
+def test_mul_mat_sparse_and_axpy(oracle, wtype, n_embd, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + n_embd + n_ff
+    Wu, _, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qd = oracle.quantize(wtype, Wu), oracle.quantize(wtype, Wd)
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, 0.15, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    for flags, tol in ((0, TOL_DEFAULT[wtype]), (sp.FLAG_CPU_ROUNDING, TOL_CPU_ROUNDING[wtype])):
+        ref_u = oracle.mul_mat_sparse(wtype, qu, x, p, n_embd, n_ff)
+        got_u = sp.mul_mat_sparse(dev(qu), wtype, dev(x), dev(p), flags=flags, ws=ws).cpu().numpy()
+        assert np.array_equal(got_u == 0, ref_u == 0) or rel_err(got_u, ref_u) < tol
+        assert rel_err(got_u, ref_u) < tol, (TYPE_NAMES[wtype], flags, rel_err(got_u, ref_u))
+        # inactive entries are exactly zero (dst is zero-filled, mm-sparse.cu:397)
+        assert np.all(got_u[p < 0.5] == 0.0)
+        hid = (ref_u * np.random.default_rng(seed + 3).normal(0, 1, ref_u.shape)).astype(np.float32)
+        hid[:, ::7] = 0.0  # alpha == 0 rows are skipped
+        ref_y = oracle.axpy_sparse(wtype, qd, hid, p, n_embd, n_ff)
+        got_y = sp.axpy_sparse(dev(qd), wtype, dev(hid), dev(p), n_embd=n_embd, flags=flags, ws=ws).cpu().numpy()
+        assert rel_err(got_y, ref_y) < tol, (TYPE_NAMES[wtype], flags, rel_err(got_y, ref_y))
+
+
+@pytest.mark.parametrize("arch", [ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP])
+@pytest.mark.parametrize("wtype", [F16, BF16])
+@pytest.mark.parametrize("n_embd,n_ff,n_tok", SHAPES)
+def test_sparse_ffn_fused(oracle, arch, wtype, n_embd, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + 7 * n_embd + n_ff + arch
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(wtype, w) for w in (Wu, Wg, Wd))
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, 0.12, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    y_ref, _, _, hid_ref = oracle.sparse_ffn(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)
+    for flags, tol in ((0, TOL_DEFAULT[wtype]), (sp.FLAG_CPU_ROUNDING, TOL_CPU_ROUNDING[wtype])):
+        y, hid, stats = sp.sparse_ffn(arch, wtype, dev(qu), None if arch == ARCH_RELU_UP else dev(qg), dev(qd), dev(x),
+                                      dev(p), n_ff, flags=flags, want_hidden=True, want_stats=True, ws=ws)
+        y, hid, stats = y.cpu().numpy(), hid.cpu().numpy(), stats.cpu().numpy()
+        assert rel_err(y, y_ref) < tol, (TYPE_NAMES[wtype], arch, flags, rel_err(y, y_ref))
+        # hidden: compare on active rows (the oracle's dense hidden also holds act(bias) on inactive rows: none here)
+        act = ~(p < 0.5)
+        assert rel_err(hid * act, hid_ref * act) < max(tol, 1e-3)
+        assert np.array_equal(stats[:, 0], act.sum(axis=1))
+    # determinism: two runs are bit-identical (the reference CUDA axpy is not, axpy-sparse.cu:9-11)
+    y1 = sp.sparse_ffn(arch, wtype, dev(qu), None if arch == ARCH_RELU_UP else dev(qg), dev(qd), dev(x), dev(p), n_ff, ws=ws)
+    y2 = sp.sparse_ffn(arch, wtype, dev(qu), None if arch == ARCH_RELU_UP else dev(qg), dev(qd), dev(x), dev(p), n_ff, ws=ws)
+    assert torch.equal(y1, y2)
+
+
+@pytest.mark.parametrize("n_ff,n_tok", [(1024, 1), (13824, 1), (11008, 4), (28672, 2), (33, 1)])
+def test_mask_compact_bit_exact(oracle, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    p = synth.direct_mask(n_ff, n_tok, 0.1, synth.SEED0 + n_ff, near=0.01)
+    p[0, :5] = [np.nan, 0.5, np.nextafter(np.float32(0.5), np.float32(0)), 0.0, 1.0][:min(5, n_ff)]
+    idx, cnt, uidx, ucnt = sp.mask_compact(dev(p), want_union=True)
+    idx, cnt, uidx, ucnt = idx.cpu().numpy(), cnt.cpu().numpy(), uidx.cpu().numpy(), ucnt.cpu().numpy()
+    union = np.zeros(n_ff, bool)
+    for t in range(n_tok):
+        ref_idx = oracle.mask_compact(p[t])
+        assert cnt[t] == len(ref_idx)
+        assert np.array_equal(idx[t, :cnt[t]], ref_idx)
+        union[ref_idx] = True
+    assert ucnt[0] == union.sum() and np.array_equal(uidx[:ucnt[0]], np.nonzero(union)[0])
+
+
+@pytest.mark.parametrize("ptype", [F16, BF16])
+@pytest.mark.parametrize("n_embd,r,n_ff,n_tok", [(512, 128, 1024, 1), (5120, 1024, 2048, 1), (4096, 256, 1536, 2)])
+def test_predictor(oracle, ptype, n_embd, r, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + n_embd + r
+    wpu, wpd, bpd = synth.predictor_weights(n_embd, r, n_ff, 0.1, seed)
+    bpu = np.random.default_rng(seed + 5).normal(0, 0.05, r).astype(np.float32)
+    qpu, qpd = oracle.quantize(ptype, wpu), oracle.quantize(ptype, wpd)
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p_ref, z_ref = oracle.predictor(ptype, qpu, bpu, qpd, bpd, x, n_embd, r, n_ff)
+    p_gpu, z_gpu = sp.predictor(dev(qpu), dev(bpu), dev(qpd), dev(bpd), dev(x), ptype, r, n_ff,
+                                flags=sp.FLAG_CPU_ROUNDING, want_logits=True)
+    p_gpu, z_gpu = p_gpu.cpu().numpy(), z_gpu.cpu().numpy()
+    assert np.abs(z_gpu - z_ref).max() < 1e-4 * max(1.0, np.abs(z_ref).max())
+    flips = (p_gpu < 0.5) != (p_ref < 0.5)
+    # north_star: flips are only allowed where |logit - threshold| < 1e-4 (threshold 0.5 on the sigmoid <=> logit 0)
+    assert np.all(np.abs(z_ref[flips]) < 1e-4), f"{flips.sum()} flips, worst |logit| {np.abs(z_ref[flips]).max()}"
+    assert np.abs(p_gpu - p_ref).max() < 1e-5

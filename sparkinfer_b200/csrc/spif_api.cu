@@ -14,9 +14,20 @@ static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
         cudaGetLastError();
         return SPIF_E_NO_DEVICE;
     }
-    SPIF_CUDA_TRY(cudaDeviceGetAttribute(&ctx.sm_count, cudaDevAttrMultiProcessorCount, dev));
-    SPIF_CUDA_TRY(cudaDeviceGetAttribute(&ctx.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    ctx.stream = (cudaStream_t) stream;
+    // device attributes are immutable: cache them per device (benign race: every writer stores the same values)
+    static int cached_sm[64], cached_smem[64];
+    const int  slot = dev & 63;
+    if (cached_sm[slot] == 0) {
+        int sm = 0, smem = 0;
+        SPIF_CUDA_TRY(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+        SPIF_CUDA_TRY(cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        cached_smem[slot] = smem;
+        cached_sm[slot]   = sm;
+    }
+    ctx.device         = dev;
+    ctx.sm_count       = cached_sm[slot];
+    ctx.max_smem_optin = cached_smem[slot];
+    ctx.stream         = (cudaStream_t) stream;
     return 0;
 }
 
@@ -85,12 +96,12 @@ size_t spif_row_size(int type, int64_t n) {
     }
 }
 
-// partials for up to 160 CTAs per token + per-CTA stats + predictor hidden + Q8_1-style activations; rounded up
+// partials for up to 320 CTAs (2 per SM) per token + per-CTA stats + predictor hidden + Q8_1-style activations; rounded up
 size_t spif_workspace_size(int n_embd, int n_ff, int n_tok) {
     if (n_embd <= 0 || n_ff <= 0 || n_tok <= 0) {
         return 0;
     }
-    const size_t P    = 160;
+    const size_t P    = 320;
     size_t       need = sizeof(float) * (size_t) n_tok * P * n_embd;  // partial y per CTA
     need += sizeof(int32_t) * (size_t) n_tok * P * 2;                 // stats
     need += sizeof(float) * (size_t) n_tok * 2048;                    // predictor hidden (r <= 2048)

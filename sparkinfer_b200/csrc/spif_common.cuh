@@ -174,15 +174,35 @@ __device__ __forceinline__ float spif_activation(int arch, float g, float u) {
 // internal launchers (defined in the .cu files, called from spif_api.cu)
 
 struct spif_launch_ctx {
+    int          device;
     int          sm_count;
     int          max_smem_optin;
     cudaStream_t stream;
 };
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel instantiation, device): `done` is a per-instantiation
+// bitmask; setting the attribute twice is harmless, so no locking is needed.
+template <typename K> static inline int spif_set_max_smem_once(K kern, size_t smem, int device, unsigned long long & done) {
+    const unsigned long long bit = 1ull << (device & 63);
+    if (!(done & bit) || smem > 48 * 1024) {
+        if (!(done & bit)) {
+            SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            done |= bit;
+        }
+    }
+    return 0;
+}
+
 int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,
                     size_t ws_bytes, const spif_launch_ctx & ctx);
 
 enum { SPIF_MODE_FUSED = 0, SPIF_MODE_GEMV = 1, SPIF_MODE_AXPY = 2 };
+
+// workspace regions (spif_workspace_size reserves them for 320 CTAs): [partials + stats][predictor hidden][...]
+static inline size_t spif_ws_partials_bytes(int n_embd, int n_tok) {
+    size_t b = sizeof(float) * (size_t) n_tok * 320 * n_embd + sizeof(int32_t) * (size_t) n_tok * 320 * 2;
+    return (b + 255) & ~(size_t) 255;
+}
 
 // internal flag (never part of the ABI): GEMV over every row, no mask, bias + relu epilogue (predictor up projection)
 #define SPIF_INTERNAL_DENSE (1 << 30)

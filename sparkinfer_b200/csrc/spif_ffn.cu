@@ -21,6 +21,8 @@
 //     partials in a fixed order -> run-to-run bit-stable, unlike axpy-sparse.cu:84.
 #include "spif_common.cuh"
 
+#include <cstdlib>
+
 #define SPIF_NB        2   /* neurons per reduction batch */
 #define SPIF_MAX_WARPS 17  /* 16 consumer warps + 1 producer */
 
@@ -46,7 +48,26 @@ struct FfnKParams {
     float                 thr;
     int                   arch, flags;
     int                   zero_fill;  // GEMV with identity mapping: zero-fill inactive dst entries in-kernel
+    unsigned int          magic;      // floor(2^32 / P) + 1: rank / P == __umulhi(rank, magic) for rank < 2^20
+    unsigned long long *  trace;      // debug: [P][8] globaltimer stamps (spif_debug_set_trace), normally NULL
 };
+
+static unsigned long long * g_spif_trace = nullptr;  // debug only; see tools/trace_ffn.py
+extern "C" void spif_debug_set_trace(void * dev_ptr) {
+    g_spif_trace = (unsigned long long *) dev_ptr;
+}
+
+__device__ __forceinline__ unsigned long long gtime_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define SPIF_STAMP(k)                                                         \
+    do {                                                                      \
+        if (p.trace && threadIdx.x == 0 && blockIdx.y == 0) {                 \
+            p.trace[(size_t) blockIdx.x * 8 + (k)] = gtime_ns();              \
+        }                                                                     \
+    } while (0)
 
 // ---------------------------------------------------------------------------------------------------------------
 // mask -> this CTA's share of the ascending active list.  All threads of the CTA take part.
@@ -73,67 +94,165 @@ __device__ __forceinline__ void build_my_list(const FfnKParams & p, const float 
         __syncthreads();
         return;
     }
-    // each warp owns a contiguous chunk of rows, a multiple of 32 long -> ranks are ordered by (warp, group, lane)
-    const int chunk = ((p.m + nwarp * 32 - 1) / (nwarp * 32)) * 32;
-    const int r0    = warp * chunk;
-    const int r1    = min(r0 + chunk, p.m);
+    // Each warp owns a contiguous chunk of rows (a multiple of 128 long), so global ranks are ordered by
+    // (warp, position in chunk).  Two passes: count, then rank = warp base + running popcount.  All loads of a batch
+    // are unconditional (clamped addresses, no branches) so ptxas issues them back to back: a pass costs one memory
+    // round trip per batch, not one per 32 rows.  Pass 2 re-reads the mask from L1.
+    const int  chunk    = ((p.m + nwarp * 128 - 1) / (nwarp * 128)) * 128;
+    const int  r0       = min(warp * chunk, p.m);
+    const int  r1       = min(r0 + chunk, p.m);
+    const bool indirect = (p.neuron_idx != nullptr);
+    const bool by_row   = (p.flags & SPIF_FLAG_MASK_BY_ROW) != 0;
+    const bool rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
+    const bool vec_ok   = !indirect && (p.m % 4 == 0) && ((reinterpret_cast<uintptr_t>(mask) & 15) == 0) &&
+                        (MODE != SPIF_MODE_AXPY || (reinterpret_cast<uintptr_t>(hid) & 15) == 0);
 
-    auto test = [&](int row, int & neu, float & alpha) -> bool {
-        neu          = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
-        const int mi = (p.flags & SPIF_FLAG_MASK_BY_ROW) ? row : neu;
-        bool      a  = spif_is_active(__ldg(mask + mi), p.thr);
-        alpha        = 0.f;
-        if (MODE == SPIF_MODE_AXPY) {
-            alpha = __ldg(hid + neu);
-            if (p.flags & SPIF_FLAG_CPU_ROUNDING) {
-                alpha = round_through<WT>(alpha);
+    auto alpha_of = [&](float h) -> float { return rounding ? round_through<WT>(h) : h; };
+    int  cnt = 0, before = 0, total = 0;
+
+    if (vec_ok) {
+        // ---- direct mask: 128-bit loads, lane l holds rows base + 4l .. 4l+3 of each 128-row group
+        constexpr int  VB   = (MODE == SPIF_MODE_AXPY) ? 5 : 10;  // 128 * VB rows per warp and batch
+        const float4 * m4   = reinterpret_cast<const float4 *>(mask);
+        const float4 * h4   = reinterpret_cast<const float4 *>(hid);
+        const int      last = p.m / 4 - 1;
+        auto bits_of = [&](const float4 & v, const float4 & h, int row) -> unsigned {
+            unsigned b = 0;
+            b |= (row + 0 < r1 && spif_is_active(v.x, p.thr)) ? 1u : 0u;
+            b |= (row + 1 < r1 && spif_is_active(v.y, p.thr)) ? 2u : 0u;
+            b |= (row + 2 < r1 && spif_is_active(v.z, p.thr)) ? 4u : 0u;
+            b |= (row + 3 < r1 && spif_is_active(v.w, p.thr)) ? 8u : 0u;
+            if (MODE == SPIF_MODE_AXPY) {  // axpy-sparse.cu:53, ggml-cpu.c:2208: alpha == 0 rows are skipped
+                b &= (alpha_of(h.x) == 0.0f ? 0u : 1u) | (alpha_of(h.y) == 0.0f ? 0u : 2u) |
+                     (alpha_of(h.z) == 0.0f ? 0u : 4u) | (alpha_of(h.w) == 0.0f ? 0u : 8u);
             }
-            a = a && !(alpha == 0.0f);  // axpy-sparse.cu:53, ggml-cpu.c:2208
+            return b;
+        };
+        for (int base = r0; base < r1; base += 128 * VB) {
+            float4 v[VB], h[VB];
+#pragma unroll
+            for (int j = 0; j < VB; ++j) {
+                const int f = min((base + 128 * j) / 4 + lane, last);
+                v[j]        = __ldg(m4 + f);
+                h[j]        = (MODE == SPIF_MODE_AXPY) ? __ldg(h4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int j = 0; j < VB; ++j) {
+                cnt += __popc(bits_of(v[j], h[j], base + 128 * j + 4 * lane));
+            }
         }
-        return a;
-    };
-
-    // pass 1: count
-    int cnt = 0;
-    for (int base = r0; base < r1; base += 32) {
-        const int row = base + lane;
-        int       neu;
-        float     alpha;
-        const bool a = (row < r1) && test(row, neu, alpha);
-        cnt += __popc(__ballot_sync(0xffffffffu, a));
-    }
-    if (lane == 0) {
-        warp_cnt[warp] = cnt;
-    }
-    __syncthreads();
-    int before = 0, total = 0;
-    for (int w = 0; w < nwarp; ++w) {
-        const int v = warp_cnt[w];
-        before += (w < warp) ? v : 0;
-        total += v;
-    }
-    // pass 2: ranks (mask re-read hits L1)
-    int run = before;
-    for (int base = r0; base < r1; base += 32) {
-        const int row = base + lane;
-        int       neu = 0;
-        float     alpha;
-        const bool     a    = (row < r1) && test(row, neu, alpha);
-        const unsigned ball = __ballot_sync(0xffffffffu, a);
-        if (a) {
-            const int rank = run + __popc(ball & ((1u << lane) - 1u));
-            if (rank % P == c) {
-                const int k = rank / P;
-                list_row[k] = row;
-                list_neu[k] = neu;
-                if (MODE == SPIF_MODE_AXPY) {
-                    list_alpha[k] = alpha;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        }
+        if (lane == 0) {
+            warp_cnt[warp] = cnt;
+        }
+        __syncthreads();
+        for (int w = 0; w < nwarp; ++w) {
+            const int x = warp_cnt[w];
+            before += (w < warp) ? x : 0;
+            total += x;
+        }
+        int run = before;
+        for (int base = r0; base < r1; base += 128 * VB) {
+            float4 v[VB], h[VB];
+#pragma unroll
+            for (int j = 0; j < VB; ++j) {
+                const int f = min((base + 128 * j) / 4 + lane, last);
+                v[j]        = __ldg(m4 + f);
+                h[j]        = (MODE == SPIF_MODE_AXPY) ? __ldg(h4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int j = 0; j < VB; ++j) {
+                const int      row0 = base + 128 * j + 4 * lane;
+                const unsigned b    = bits_of(v[j], h[j], row0);
+                const int      mine = __popc(b);
+                int            incl = mine;  // inclusive prefix of `mine` over lanes
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                    incl += (lane >= o) ? t : 0;
+                }
+                int         rank  = run + incl - mine;
+                const float hv[4] = { h[j].x, h[j].y, h[j].z, h[j].w };
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int row = row0 + e;
+                    if (b & (1u << e)) {
+                        const int k = (int) __umulhi((unsigned) rank, p.magic);  // rank / P without a divide
+                        if (rank - k * P == c) {
+                            list_row[k] = row;
+                            list_neu[k] = row;
+                            if (MODE == SPIF_MODE_AXPY) {
+                                list_alpha[k] = alpha_of(hv[e]);
+                            }
+                        }
+                        ++rank;
+                    } else if (MODE == SPIF_MODE_GEMV && p.zero_fill && row < r1 && (row - (int) __umulhi((unsigned) row, p.magic) * P) == c) {
+                        dense[row] = 0.0f;  // dst[neu] of inactive neurons (mm-sparse.cu:397)
+                    }
+                }
+                run += __shfl_sync(0xffffffffu, incl, 31);
+            }
+        }
+    } else {
+        // ---- gathered mask (GPU cache / shard rows -> neuron ids) or unaligned: scalar loads, batches of 8
+        constexpr int SB    = 8;
+        const int     lastr = max(r1 - 1, 0);
+        for (int pass = 0; pass < 2; ++pass) {
+            int run = before;
+            for (int base = r0; base < r1; base += 32 * SB) {
+                int   neu[SB];
+                float v[SB], al[SB];
+#pragma unroll
+                for (int j = 0; j < SB; ++j) {
+                    const int row = min(base + j * 32 + lane, lastr);
+                    neu[j]        = indirect ? __ldg(p.neuron_idx + row) : row;
+                }
+#pragma unroll
+                for (int j = 0; j < SB; ++j) {
+                    const int row = min(base + j * 32 + lane, lastr);
+                    v[j]          = __ldg(mask + (by_row ? row : neu[j]));
+                    al[j]         = (MODE == SPIF_MODE_AXPY) ? alpha_of(__ldg(hid + neu[j])) : 1.0f;
+                }
+#pragma unroll
+                for (int j = 0; j < SB; ++j) {
+                    const int      row  = base + j * 32 + lane;
+                    const bool     a    = (row < r1) && spif_is_active(v[j], p.thr) && !(al[j] == 0.0f);
+                    const unsigned ball = __ballot_sync(0xffffffffu, a);
+                    if (pass == 0) {
+                        cnt += __popc(ball);
+                    } else {
+                        if (a) {
+                            const int rank = run + __popc(ball & ((1u << lane) - 1u));
+                            const int k = (int) __umulhi((unsigned) rank, p.magic);
+                            if (rank - k * P == c) {
+                                list_row[k] = row;
+                                list_neu[k] = neu[j];
+                                if (MODE == SPIF_MODE_AXPY) {
+                                    list_alpha[k] = al[j];
+                                }
+                            }
+                        } else if (MODE == SPIF_MODE_GEMV && p.zero_fill && row < r1 && (row - (int) __umulhi((unsigned) row, p.magic) * P) == c) {
+                            dense[row] = 0.0f;
+                        }
+                        run += __popc(ball);
+                    }
                 }
             }
-        } else if (MODE == SPIF_MODE_GEMV && p.zero_fill && row < r1 && (row % P) == c) {
-            dense[row] = 0.0f;  // identity mapping: dst[neu] for inactive neurons (mm-sparse.cu:397)
+            if (pass == 0) {
+                if (lane == 0) {
+                    warp_cnt[warp] = cnt;
+                }
+                __syncthreads();
+                for (int w = 0; w < nwarp; ++w) {
+                    const int x = warp_cnt[w];
+                    before += (w < warp) ? x : 0;
+                    total += x;
+                }
+            }
         }
-        run += __popc(ball);
     }
     if (tid == 0) {
         s_counts[0] = (total > c) ? (total - c + P - 1) / P : 0;  // my share
@@ -199,8 +318,10 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
         }
         mbar_fence_init();
     }
+    SPIF_STAMP(0);
     // everything above overlaps the previous kernel's tail under programmatic dependent launch
     pdl_wait_prior_grid();
+    SPIF_STAMP(1);
 
     const float * mask  = p.mask + (size_t) tok * p.mask_len;
     const float * xg    = p.x ? p.x + (size_t) tok * p.n_embd : nullptr;
@@ -210,6 +331,7 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
     build_my_list<MODE, WT>(p, mask, hid, dense, warp_cnt, list_row, list_neu, list_alpha, s_counts);  // ends with __syncthreads
     const int my_count = s_counts[0];
     pdl_launch_dependents();
+    SPIF_STAMP(2);
 
     if (warp == nwc) {
         // ================= producer warp: stream weight rows of my active neurons =================
@@ -302,6 +424,9 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
                     const int i = b * SPIF_NB + j;
                     const int s = i % p.S;
                     mbar_wait(&full[s], (i / p.S) & 1);
+                    if (i == 0) {
+                        SPIF_STAMP(3);
+                    }
                     const uint4 * ur = reinterpret_cast<const uint4 *>(ring + (size_t) s * stage_bytes);
                     const uint4 * gr = reinterpret_cast<const uint4 *>(ring + (size_t) s * stage_bytes + p.row_bytes);
 #pragma unroll
@@ -418,6 +543,7 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
                 n_nonzero += nq;
             }
         }
+        SPIF_STAMP(4);
         if (MODE == SPIF_MODE_FUSED) {
             for (int j = 0; j < n_pend; ++j) {
                 const int slot = q_done % p.D;
@@ -446,13 +572,17 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
             st[1]        = n_nonzero;
         }
     }
+    SPIF_STAMP(5);
+    if (p.trace && threadIdx.x == 0 && blockIdx.y == 0) {
+        p.trace[(size_t) blockIdx.x * 8 + 6] = (unsigned long long) my_count;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 // y[t][col] = sum_p partials[t][p][col] (+ b_down[col]) in a fixed order.  block (32 column-vectors, 16 p-chunks):
 // every thread has all of its <= SPIF_RED_PER loads in flight at once (one L2 round trip), then a fixed-order smem sum.
 #define SPIF_RED_CHUNKS 16
-#define SPIF_RED_PER    10 /* ceil(P / 16) for P <= 160 SMs */
+#define SPIF_RED_PER    20 /* ceil(P / 16) for P <= 320 CTAs */
 __global__ void __launch_bounds__(32 * SPIF_RED_CHUNKS) spif_reduce_partials_kernel(const float * __restrict__ partials,
                                                                                      const float * __restrict__ b_down,
                                                                                      float * __restrict__ y,
@@ -511,9 +641,13 @@ __global__ void __launch_bounds__(32 * SPIF_RED_CHUNKS) spif_reduce_partials_ker
 // host-side launcher
 
 template <typename WT, int VPT, int MODE>
-static int launch_t(const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
-    auto kern = spif_ffn_kernel<WT, VPT, MODE>;
-    SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+static int launch_t(const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream, int device) {
+    auto                      kern = spif_ffn_kernel<WT, VPT, MODE>;
+    static unsigned long long done = 0;
+    int                       rc0  = spif_set_max_smem_once(kern, smem, device, done);
+    if (rc0) {
+        return rc0;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = grid;
     cfg.blockDim           = dim3(threads);
@@ -529,26 +663,26 @@ static int launch_t(const FfnKParams & kp, dim3 grid, int threads, size_t smem, 
 }
 
 template <typename WT, int MODE>
-static int launch_v(int vpt, const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+static int launch_v(int vpt, const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream, int device) {
     switch (vpt) {
         case 1:
-            return launch_t<WT, 1, MODE>(kp, grid, threads, smem, stream);
+            return launch_t<WT, 1, MODE>(kp, grid, threads, smem, stream, device);
         case 2:
-            return launch_t<WT, 2, MODE>(kp, grid, threads, smem, stream);
+            return launch_t<WT, 2, MODE>(kp, grid, threads, smem, stream, device);
         default:
-            return launch_t<WT, 4, MODE>(kp, grid, threads, smem, stream);
+            return launch_t<WT, 4, MODE>(kp, grid, threads, smem, stream, device);
     }
 }
 
 template <typename WT>
-static int launch_m(int mode, int vpt, const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+static int launch_m(int mode, int vpt, const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream, int device) {
     switch (mode) {
         case SPIF_MODE_FUSED:
-            return launch_v<WT, SPIF_MODE_FUSED>(vpt, kp, grid, threads, smem, stream);
+            return launch_v<WT, SPIF_MODE_FUSED>(vpt, kp, grid, threads, smem, stream, device);
         case SPIF_MODE_GEMV:
-            return launch_v<WT, SPIF_MODE_GEMV>(vpt, kp, grid, threads, smem, stream);
+            return launch_v<WT, SPIF_MODE_GEMV>(vpt, kp, grid, threads, smem, stream, device);
         default:
-            return launch_v<WT, SPIF_MODE_AXPY>(vpt, kp, grid, threads, smem, stream);
+            return launch_v<WT, SPIF_MODE_AXPY>(vpt, kp, grid, threads, smem, stream, device);
     }
 }
 
@@ -560,7 +694,10 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     SPIF_REQUIRE(a.n_embd <= 16384, SPIF_E_SHAPE);
     SPIF_REQUIRE(a.neuron_idx != nullptr || a.m == a.n_ff, SPIF_E_SHAPE);
 
-    const int P = ctx.sm_count;
+    // tuning knobs (read once): CTAs per SM and ring depth.  Defaults chosen from profiles/ (see DESIGN.md).
+    static const int k_ctas_per_sm = [] { const char * e = getenv("SPIF_CTAS_PER_SM"); int v = e ? atoi(e) : 1; return v < 1 ? 1 : (v > 2 ? 2 : v); }();
+    static const int k_max_stages  = [] { const char * e = getenv("SPIF_STAGES"); int v = e ? atoi(e) : 8; return v < 2 ? 2 : (v > 8 ? 8 : v); }();
+    const int P = ctx.sm_count * k_ctas_per_sm;
     SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_CHUNKS * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
     FfnKParams kp = {};
     kp.w_up       = (const unsigned char *) a.w_up;
@@ -582,6 +719,8 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     kp.arch       = a.arch;
     kp.flags      = a.flags;
     kp.dense_out  = (mode == SPIF_MODE_GEMV) ? dst_dense : a.hidden_out;
+    kp.trace      = g_spif_trace;
+    kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;
     const bool dense_list = (a.flags & SPIF_INTERNAL_DENSE) != 0;
     SPIF_REQUIRE(dense_list || a.sparse_idx != nullptr, SPIF_E_NULL);
     kp.zero_fill  = (mode == SPIF_MODE_GEMV && a.neuron_idx == nullptr && !dense_list) ? 1 : 0;
@@ -599,11 +738,11 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     kp.D             = (mode == SPIF_MODE_FUSED) ? 2 * SPIF_NB : 0;
     const size_t fixed =
         (size_t) 8 * (2 * 8 + kp.D) + sizeof(float) * 2 * 16 * SPIF_NB * 2 + sizeof(int) * (32 + 4) + (size_t) 12 * kp.list_cap + 256;
-    const size_t budget = (size_t) ctx.max_smem_optin - 1024;
+    const size_t budget = ((size_t) ctx.max_smem_optin - 1024) / k_ctas_per_sm - (k_ctas_per_sm > 1 ? 1024 : 0);
     const size_t dbytes = (size_t) kp.D * kp.row_bytes;
     SPIF_REQUIRE(budget > fixed + dbytes + 2 * (size_t) nmat * kp.row_bytes, SPIF_E_SHAPE);
     int S = (int) ((budget - fixed - dbytes) / ((size_t) nmat * kp.row_bytes));
-    S     = S > 8 ? 8 : S;
+    S     = S > k_max_stages ? k_max_stages : S;
     kp.S  = S;
     const size_t smem = (size_t) S * nmat * kp.row_bytes + dbytes + fixed;
 
@@ -623,8 +762,8 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     }
 
     const dim3 grid(P, a.n_tok);
-    int        rc = (a.type == SPIF_TYPE_F16) ? launch_m<spif_f16>(mode, vpt, kp, grid, threads, smem, ctx.stream) :
-                                                launch_m<spif_bf16>(mode, vpt, kp, grid, threads, smem, ctx.stream);
+    int        rc = (a.type == SPIF_TYPE_F16) ? launch_m<spif_f16>(mode, vpt, kp, grid, threads, smem, ctx.stream, ctx.device) :
+                                                launch_m<spif_bf16>(mode, vpt, kp, grid, threads, smem, ctx.stream, ctx.device);
     if (rc) {
         return rc;
     }

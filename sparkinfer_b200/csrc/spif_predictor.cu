@@ -131,9 +131,13 @@ __global__ void __launch_bounds__((PD_ROWS + 1) * 32, 1) spif_pred_down_kernel(c
 }
 
 template <typename WT, int VL>
-static int launch_pd(const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream) {
-    auto kern = spif_pred_down_kernel<WT, VL>;
-    SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+static int launch_pd(const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream, int device) {
+    auto                      kern = spif_pred_down_kernel<WT, VL>;
+    static unsigned long long done = 0;
+    int                       rc0  = spif_set_max_smem_once(kern, smem, device, done);
+    if (rc0) {
+        return rc0;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = grid;
     cfg.blockDim           = dim3((PD_ROWS + 1) * 32);
@@ -148,28 +152,30 @@ static int launch_pd(const PredDownParams & p, dim3 grid, size_t smem, cudaStrea
     return 0;
 }
 
-template <typename WT> static int launch_pd_v(int vl, const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream) {
+template <typename WT> static int launch_pd_v(int vl, const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream, int device) {
     switch (vl) {
         case 1:
-            return launch_pd<WT, 1>(p, grid, smem, stream);
+            return launch_pd<WT, 1>(p, grid, smem, stream, device);
         case 2:
-            return launch_pd<WT, 2>(p, grid, smem, stream);
+            return launch_pd<WT, 2>(p, grid, smem, stream, device);
         case 4:
-            return launch_pd<WT, 4>(p, grid, smem, stream);
+            return launch_pd<WT, 4>(p, grid, smem, stream, device);
         default:
-            return launch_pd<WT, 8>(p, grid, smem, stream);
+            return launch_pd<WT, 8>(p, grid, smem, stream, device);
     }
 }
 
-// ws: [h1 n_tok*r f32]
 int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,
                           const float * x, float * sparse_idx_out, float * logits_out, int n_embd, int r, int n_ff,
                           int n_tok, int flags, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
     SPIF_REQUIRE(ptype == SPIF_TYPE_F16 || ptype == SPIF_TYPE_BF16, SPIF_E_TYPE);
     SPIF_REQUIRE(n_embd > 0 && n_embd % 8 == 0 && r > 0 && r % 8 == 0 && r <= 2048 && n_ff > 0 && n_tok > 0, SPIF_E_SHAPE);
+    // the hidden vector lives after the FFN's partials region so a predictor may run concurrently with an FFN
+    // kernel that shares the workspace (look-ahead overlap, llama-graph.cpp:939-946)
+    const size_t h1_off   = spif_ws_partials_bytes(n_embd, n_tok);
     const size_t h1_bytes = sizeof(float) * (size_t) n_tok * r;
-    SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= h1_bytes, SPIF_E_WORKSPACE);
-    float * h1 = (float *) ws;
+    SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= h1_off + h1_bytes, SPIF_E_WORKSPACE);
+    float * h1 = (float *) ((char *) ws + h1_off);
 
     // up: dense GEMV + bias + relu through the FFN kernel template
     spif_ffn_args a = {};
@@ -204,6 +210,6 @@ int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const 
     const int    vl  = Vr <= 32 ? 1 : (Vr <= 64 ? 2 : (Vr <= 128 ? 4 : 8));
     const size_t smem = (size_t) PD_STAGES * PD_ROWS * p.row_bytes + 16 * PD_STAGES + 64;
     const dim3   grid(ctx.sm_count, n_tok);
-    return (ptype == SPIF_TYPE_F16) ? launch_pd_v<spif_f16>(vl, p, grid, smem, ctx.stream) :
-                                      launch_pd_v<spif_bf16>(vl, p, grid, smem, ctx.stream);
+    return (ptype == SPIF_TYPE_F16) ? launch_pd_v<spif_f16>(vl, p, grid, smem, ctx.stream, ctx.device) :
+                                      launch_pd_v<spif_bf16>(vl, p, grid, smem, ctx.stream, ctx.device);
 }

@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- decode tok/s of the activation-sparse FFN path (predictor -> mask -> gathered gate/up -> down axpy) on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torch.distributed.run, one rank per GPU)
+    python bench.py --impl reference ...                     (the reference's own CPU ops on the box's host cores)
+
+A "step" is one decode token (bs = 1) through the sparse-FFN path of EVERY layer of the named architecture: per layer
+the look-ahead predictor (src/llama-graph.cpp:932-946) and build_sparse_ffn (:896-1142).  Attention is out of scope
+(SURVEY.md 8): the per-layer FFN inputs x_l are synthetic N(0,1) vectors, weights are random-init in the real shapes,
+the predictor is synthetic with per-neuron biases that give a Zipf-like hotness at mean activity rho.
+
+  value     whole-job tok/s with the x_l already resident in HBM (one D2D refresh of the x stack per step);
+  e2e       the same metric with the x stack coming from pinned HOST memory every step and the y stack read back;
+  roofline  the fused sparse-FFN kernel: algorithmic bytes (2A+Z)*row_bytes per layer over its live-measured duration;
+  cpu_baseline  the reference CPU path (oracle/_ref, else the oracle port) on a bounded sample of the same workload.
+
+At N > 1 the FFN neurons are sharded over the ranks and every layer ends in one NCCL allreduce of y (strong scaling).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+F16, Q4_0, Q8_0, BF16 = 1, 2, 8, 30
+WORKLOADS = {
+    # name: n_embd, n_ff, n_layer, activation recipe (spif_arch), label as in BASELINE.json configs
+    "prosparse-13b": dict(n_embd=5120, n_ff=13824, n_layer=40, arch=0, label="ProSparse-Llama-2-13B FP16 bs=1 decode"),
+    "prosparse-7b": dict(n_embd=4096, n_ff=11008, n_layer=32, arch=0, label="ProSparse-Llama-2-7B FP16 bs=1 decode"),
+    "relullama-70b": dict(n_embd=8192, n_ff=28672, n_layer=80, arch=0, label="ReluLLaMA-70B FP16 bs=1 decode"),
+}
+GROUP = 16  # neurons per placement group
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="prosparse-13b", choices=sorted(WORKLOADS))
+    ap.add_argument("--rho", type=float, default=0.10, help="mean fraction of neurons the predictor marks active")
+    ap.add_argument("--rank", type=int, default=1024, help="predictor rank r (pred_lora)")
+    ap.add_argument("--pool", type=int, default=8, help="distinct x stacks cycled through (distinct masks per token)")
+    ap.add_argument("--cpu-layers", type=int, default=4, help="layers in the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons through NVML while the timed region runs"""
+
+    def __init__(self, index, period=0.002):
+        super().__init__(daemon=True)
+        self.period, self.samples, self.reasons, self.max_mhz = period, [], set(), None
+        self._stop_evt = threading.Event()
+        self.h = None
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:  # NVML missing: clocks are reported as null, the run is still valid
+            self.h = None
+
+    def run(self):
+        if self.h is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=1.0)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def synth_hotness(n_ff, rho, seed):
+    """per-neuron firing probability, Zipf-like over groups of GROUP neurons, mean rho (same recipe as tests/synth.py)"""
+    rng = np.random.default_rng(seed)
+    n_g = n_ff // GROUP
+    ranks = rng.permutation(n_g) + 1
+    w = 1.0 / ranks ** 0.7
+    p_g = np.clip(w / w.mean() * rho, 1e-4, 1.0 - 1e-4)
+    return p_g  # per group
+
+
+def bias_for(p_neuron):
+    """logit ~ N(0, 1/2) for the synthetic predictor (x ~ N(0,1), relu halves the variance) -> bias at the p-quantile"""
+    from statistics import NormalDist
+    nd = NormalDist()
+    s = float(np.sqrt(0.5))
+    return np.array([s * nd.inv_cdf(float(p)) for p in p_neuron], dtype=np.float32)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def build_stack(a, wl, rank, world, device):
+    """random-init weights of the named architecture, resident on this rank's GPU (only this shard's rows)"""
+    import torch
+    import sparkinfer_b200 as sp
+    from sparkinfer_b200 import placement
+    from sparkinfer_b200.stack import FfnStack, LayerWeights
+
+    E, F, L, R = wl["n_embd"], wl["n_ff"], wl["n_layer"], a.rank
+    n_g = F // GROUP
+    assert n_g % world == 0, "neuron groups must divide over the shards"
+    m = F // world
+    gen = torch.Generator(device=device).manual_seed(a.seed + 7919 * rank)
+    u8 = lambda t: t.view(torch.uint8).reshape(-1)
+
+    def half(rows, cols, std):
+        return u8(torch.empty((rows, cols), dtype=torch.float16, device=device).normal_(0.0, std, generator=gen))
+
+    layers, expect = [], []
+    for l in range(L):
+        p_g = synth_hotness(F, a.rho, a.seed + l)                   # identical on every rank
+        shard_of = placement.initial_placement(p_g, world)
+        mine = np.nonzero(shard_of == rank)[0]
+        p_n = np.repeat(p_g[mine], GROUP)                           # this shard's neurons, ascending
+        expect.append(float(p_n.sum()))
+        bpd = torch.from_numpy(bias_for(p_n)).to(device)
+        # the replicated predictor up-projection must be the SAME on every rank: seed it by layer only
+        gpu_l = torch.Generator(device=device).manual_seed(a.seed + 104729 * (l + 1))
+        wpu = u8(torch.empty((R, E), dtype=torch.float16, device=device).normal_(0.0, E ** -0.5, generator=gpu_l))
+        layers.append(LayerWeights(up=half(m, E, 0.02), gate=half(m, E, 0.02), down_t=half(m, E, 0.02), pred_up=wpu,
+                                   pred_down=half(m, R, R ** -0.5), pred_down_b=bpd, m=m))
+    group = torch.distributed.group.WORLD if world > 1 else None
+    st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device)
+    return st, expect
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the sparse-FFN path has no CPU fallback")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    import sparkinfer_b200 as sp  # noqa: F401  (raises if libspif_b200.so is missing)
+
+    wl = WORKLOADS[a.workload]
+    E, F, L, R = wl["n_embd"], wl["n_ff"], wl["n_layer"], a.rank
+    st, expect = build_stack(a, wl, rank, world, device)
+    row_bytes = 2 * E
+
+    # x pool: identical on all ranks (x is replicated), pinned on the host for the e2e leg
+    rng = np.random.default_rng(a.seed + 1)
+    x_host = torch.from_numpy(rng.normal(0.0, 1.0, (a.pool, L, 1, E)).astype(np.float32)).pin_memory()
+    y_host = torch.empty((L, 1, E), dtype=torch.float32).pin_memory()
+    x_pool = x_host.to(device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # eager warm-up (sets kernel attributes) + per-pool-entry activity statistics for the byte accounting
+    A_pool, Z_pool = [], []
+    for i in range(a.pool):
+        st.x.copy_(x_pool[i])
+        st.step_eager(want_stats=True)
+        torch.cuda.synchronize()
+        s = st.stats.cpu().numpy()[:, 0, :]
+        A_pool.append(s[:, 0].astype(np.int64))
+        Z_pool.append(s[:, 1].astype(np.int64))
+    launches_per_step = st.launches_per_step
+    g_step = st.capture()
+    g_ffn = st.capture(st.ffn_only_eager)
+    g_pred = st.capture(st.predict_only_eager)
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    def step_resident(i):
+        st.x.copy_(x_pool[i % a.pool])     # D2D, 4*L*E bytes: a new token's activations -> new masks every step
+        g_step.replay()
+
+    def step_e2e(i):
+        st.x.copy_(x_host[i % a.pool], non_blocking=True)
+        g_step.replay()
+        y_host.copy_(st.y, non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # a decode step's result is needed on the host before the next
+
+    sampler = ClockSampler(physical_gpu_index(local))
+    sampler.start()
+    ms_value = timed(step_resident, a.steps, max(a.warmup, 3))
+    clocks = sampler.stop()
+    ms_e2e = timed(step_e2e, a.steps, max(a.warmup, 3))
+
+    # ---- roofline leg: the sparse FFNs alone (fused kernel + fixed-order partial reduction per layer), masks of pool[0]
+    st.x.copy_(x_pool[0])
+    g_step.replay()
+    torch.cuda.synchronize()
+    reps = max(10, min(200, a.steps // 10))
+    ms_ffn = timed(lambda i: g_ffn.replay(), reps, 3) / reps
+    ms_pred = timed(lambda i: g_pred.replay(), reps, 3) / reps
+    A0, Z0 = A_pool[0], Z_pool[0]
+    ffn_bytes = float(((2 * A0 + Z0) * row_bytes).sum())          # this rank's shard, all layers of one step
+    pred_bytes = float(L * (E * R + R * st.m) * 2)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6650"
+    achieved = ffn_bytes / (ms_ffn * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_top_kernel.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = ms_value / a.steps
+    A_mean = float(np.mean([x.mean() for x in A_pool]))
+    Z_mean = float(np.mean([x.mean() for x in Z_pool]))
+    out = {
+        "metric": "decode tok/s ProSparse-13B bs1; sparse-FFN effective HBM GB/s vs B200 peak",
+        "value": 1e3 / ms_step, "unit": "tok/s (sparse-FFN path of all layers: predictor + mask + gate/up + down)",
+        "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16 weights, f32 accumulate",
+        "data": "synthetic: random-init weights, synthetic predictor (Zipf hotness over 16-neuron groups), N(0,1) x",
+        "config": {"workload": wl["label"], "n_embd": E, "n_ff": F, "n_layer": L, "pred_rank": R, "rho": a.rho,
+                   "active_rows_per_layer": A_mean * world if world > 1 else A_mean,
+                   "nonzero_hidden_per_layer": Z_mean * world if world > 1 else Z_mean,
+                   "sharding": f"neuron groups of {GROUP} over {world} GPU(s), one allreduce of y per layer"
+                   if world > 1 else "all neurons resident on 1 GPU",
+                   "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
+                         ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool},
+        "e2e": {"value": 1e3 / (ms_e2e / a.steps), "unit": "tok/s", "h2d_bytes_per_step": 4 * L * E,
+                "d2h_bytes_per_step": 4 * L * E},
+        "gpu_launches": launches_per_step * a.steps,
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src,
+                     "kernel": "spif_ffn_kernel<f16,FUSED> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call",
+                     "bytes_per_launch": ffn_bytes / L, "us_per_launch": ms_ffn * 1e3 / L,
+                     "predictor": {"achieved": pred_bytes / (ms_pred * 1e-3) / 1e9, "us_per_layer": ms_pred * 1e3 / L,
+                                   "bytes_per_layer": pred_bytes / L},
+                     "layer": {"achieved": (ffn_bytes + pred_bytes + 4 * L * (2 * E + st.m)) / (ms_step * 1e-3) / 1e9,
+                               "us_per_layer": ms_step * 1e3 / L}},
+    }
+    if world == 1 and not a.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_baseline(a, wl, iters=8, warmup=2)
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def host_layers(a, wl, n_layers):
+    """random-init host copies of the first n_layers layers (CPU legs only; values differ from the GPU's, shapes and
+    activity statistics are the same)"""
+    import torch
+    E, F, R = wl["n_embd"], wl["n_ff"], a.rank
+    g = torch.Generator().manual_seed(a.seed)
+
+    def half(rows, cols, std):
+        t = torch.empty((rows, cols), dtype=torch.float32).normal_(0.0, std, generator=g).to(torch.float16)
+        return t.numpy().view(np.uint8).reshape(-1)
+
+    up, gate, down, wpu, wpd, bpd = [], [], [], [], [], []
+    for l in range(n_layers):
+        up.append(half(F, E, 0.02)), gate.append(half(F, E, 0.02)), down.append(half(F, E, 0.02))
+        wpu.append(half(R, E, E ** -0.5)), wpd.append(half(F, R, R ** -0.5))
+        bpd.append(bias_for(np.repeat(synth_hotness(F, a.rho, a.seed + l), GROUP)))
+    x = np.random.default_rng(a.seed + 1).normal(0.0, 1.0, (n_layers, 1, E)).astype(np.float32)
+    return up, gate, down, wpu, wpd, bpd, x
+
+
+def cpu_stack_tok_s(a, wl, iters, warmup):
+    """time the reference CPU sparse-FFN path (all host threads) on a bounded sample: the first --cpu-layers layers of
+    the workload, scaled to the full layer count.  -> (tok/s, kind, cores, sample description)"""
+    import oracle_lib  # test infrastructure: the checker / CPU baseline, never the product path
+    wl_L = wl["n_layer"]
+    nl = min(a.cpu_layers, wl_L)
+    cores = os.cpu_count() or 1
+    if oracle_lib.Ref.available():
+        lib, kind = oracle_lib.Ref(), "reference"
+    else:
+        lib, kind = oracle_lib.Oracle(), "port"
+    up, gate, down, wpu, wpd, bpd, x = host_layers(a, wl, nl)
+    us, _ = oracle_lib.stack_time(lib, wl["arch"], F16, F16, up, gate, down, wpu, wpd, bpd, x, wl["n_embd"], wl["n_ff"],
+                                  a.rank, 1, cores, warmup, iters)
+    if us <= 0:
+        raise RuntimeError("CPU stack timing failed")
+    tok_s = 1e6 / (us * wl_L / nl)
+    sample = (f"{nl} of {wl_L} layers (predictor + sparse FFN, look-ahead order), median of {iters} steps after {warmup} "
+              f"warm-up, {cores} threads, scaled x{wl_L / nl:g} to the full stack")
+    return tok_s, kind, cores, sample
+
+
+def cpu_baseline(a, wl, iters, warmup):
+    tok_s, kind, cores, sample = cpu_stack_tok_s(a, wl, iters, warmup)
+    return {"value": tok_s, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample}
+
+
+def run_reference(a):
+    """the reference's own CPU implementation of the path (oracle/_ref = its unmodified ggml CPU ops) on the host cores"""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    wl = WORKLOADS[a.workload]
+    iters = max(3, min(a.steps, 200))       # bounded: each step is ~10 ms of CPU work per sampled layer
+    warmup = max(3, min(a.warmup, 10))
+    t0 = time.time()
+    tok_s, kind, cores, sample = cpu_stack_tok_s(a, wl, iters, warmup)
+    E, F, L = wl["n_embd"], wl["n_ff"], wl["n_layer"]
+    out = {
+        "impl": "reference",
+        "metric": "decode tok/s ProSparse-13B bs1; sparse-FFN effective HBM GB/s vs B200 peak",
+        "value": tok_s, "unit": "tok/s (sparse-FFN path of all layers: predictor + mask + gate/up + down)",
+        "n_gpus": a.gpus, "steps": iters, "warmup": warmup, "ms_per_step": 1e3 / tok_s, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f16 weights, f32 accumulate", "data": "synthetic",
+        "config": {"workload": wl["label"], "n_embd": E, "n_ff": F, "n_layer": L, "pred_rank": a.rank, "rho": a.rho,
+                   "sharding": "host cores only (reference CPU path, all neurons CPU-side)"},
+        "cpu_baseline": {"value": tok_s, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": tok_s, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": round(time.time() - t0, 1),
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

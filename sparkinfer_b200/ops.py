@@ -134,14 +134,16 @@ def predictor(pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, n_ff, 
 
 
 def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx=None, up_b=None, gate_b=None,
-               down_b=None, thr=SPARSE_THRESHOLD, flags=0, want_hidden=False, want_stats=False, ws=None, out=None):
+               down_b=None, thr=SPARSE_THRESHOLD, flags=0, want_hidden=False, want_stats=False, ws=None, out=None,
+               stats=None):
     """build_sparse_ffn for the rows resident on this device.  -> y {n_embd, n_tok} [, hidden {n_ff, n_tok}][, stats]"""
     L = _lib.load()
     n_tok, n_embd = cur.shape
     m = n_ff if neuron_idx is None else neuron_idx.numel()
     y = out if out is not None else torch.empty((n_tok, n_embd), dtype=torch.float32, device=cur.device)
     hid = torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device) if want_hidden else None
-    stats = torch.zeros((n_tok, 4), dtype=torch.int32, device=cur.device) if want_stats else None
+    if stats is None and want_stats:
+        stats = torch.zeros((n_tok, 4), dtype=torch.int32, device=cur.device)
     ws = _ws(ws, n_embd, n_ff, n_tok, cur.device)
     a = FfnArgs(arch=arch, type=w_type, n_embd=n_embd, n_ff=n_ff, m=m, n_tok=n_tok, flags=flags, thr=thr,
                 w_up=_p(up), w_gate=_p(gate), w_down_t=_p(down_t), b_up=_p(up_b), b_gate=_p(gate_b), b_down=_p(down_b),

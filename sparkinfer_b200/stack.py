@@ -1,0 +1,109 @@
+"""Per-token sparse-FFN stack: the host-side mirror of how the reference chains the path across layers.
+
+Reference: llm_graph_context::build_sparse_ffn + the look-ahead predictor (src/llama-graph.cpp:932-946): layer 0 predicts
+its own mask from x_0, and while layer l runs, the mask of layer l+1 is predicted from layer l's FFN input x_l.
+The attention blocks between the FFNs are out of scope, so the x_l are inputs.
+
+Sharding: with world_size G each rank holds the rows of n_ff / G neurons of every matrix (whole groups of
+`g` consecutive neurons, dealt by the placement in balancer.py), predicts / masks / computes only those, and the partial
+y_l is summed over ranks with ONE allreduce per layer.
+
+torch is plumbing only (device memory, streams, NCCL through torch.distributed); every compute step is a call into
+libspif_b200.so.  There is no CPU fallback.
+"""
+import torch
+
+from . import ops
+
+
+class LayerWeights:
+    """device-resident rows of one layer held by this rank (all byte tensors in ggml row layout)"""
+    __slots__ = ("up", "gate", "down_t", "pred_up", "pred_down", "pred_down_b", "m")
+
+    def __init__(self, up, gate, down_t, pred_up, pred_down, pred_down_b, m):
+        self.up, self.gate, self.down_t = up, gate, down_t
+        self.pred_up, self.pred_down, self.pred_down_b = pred_up, pred_down, pred_down_b
+        self.m = m
+
+
+class FfnStack:
+    """n_layer sparse FFNs + predictors for one decode step (n_tok tokens)"""
+
+    def __init__(self, arch, w_type, p_type, n_embd, n_ff_local, r, layers, n_tok=1, group=None, device="cuda",
+                 flags=0):
+        self.arch, self.w_type, self.p_type = arch, w_type, p_type
+        self.n_embd, self.m, self.r, self.n_tok = n_embd, n_ff_local, r, n_tok
+        self.layers = layers
+        self.L = len(layers)
+        self.group = group  # torch.distributed process group (None: single GPU)
+        self.flags = flags
+        self.ws = ops.Workspace(n_embd, n_ff_local, n_tok, device)
+        self.x = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)
+        self.y = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)
+        self.p = torch.zeros((self.L, n_tok, n_ff_local), dtype=torch.float32, device=device)
+        self.stats = torch.zeros((self.L, n_tok, 4), dtype=torch.int32, device=device)
+        self.graph = None
+        self.launches_per_step = 0
+
+    # -- single pieces ------------------------------------------------------------------------------------------
+    def predict(self, l, x_from):
+        w = self.layers[l]
+        ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
+                      flags=self.flags, ws=self.ws, out=self.p[l])
+        return 2  # kernels: predictor up GEMV, predictor down GEMV+sigmoid
+
+    def ffn(self, l, want_stats=False):
+        w = self.layers[l]
+        ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=self.flags,
+                       ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None)
+        return 2  # kernels: fused gate/up/act/down, partial reduction
+
+    def allreduce(self, l):
+        if self.group is not None:
+            torch.distributed.all_reduce(self.y[l], group=self.group)
+
+    # -- one decode step ----------------------------------------------------------------------------------------
+    def step_eager(self, want_stats=False):
+        n = self.predict(0, 0)
+        for l in range(self.L):
+            if l + 1 < self.L:
+                n += self.predict(l + 1, l)  # look-ahead, llama-graph.cpp:939-946
+            n += self.ffn(l, want_stats)
+            self.allreduce(l)
+        self.launches_per_step = n
+        return n
+
+    def ffn_only_eager(self, want_stats=False):
+        """the sparse FFNs alone, masks as left in self.p by the last full step"""
+        n = 0
+        for l in range(self.L):
+            n += self.ffn(l, want_stats)
+        return n
+
+    def predict_only_eager(self):
+        n = self.predict(0, 0)
+        for l in range(self.L - 1):
+            n += self.predict(l + 1, l)
+        return n
+
+    def capture(self, fn=None):
+        """capture fn (default: the full step) into a CUDA graph on a side stream; returns the graph"""
+        fn = fn or self.step_eager
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            fn()  # warm-up on the capture stream (sets kernel attributes, NCCL channels)
+            s.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                fn()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        if fn == self.step_eager:
+            self.graph = g
+        return g
+
+    def step(self):
+        if self.graph is None:
+            self.capture()
+        self.graph.replay()

@@ -67,6 +67,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
         : "memory");
 }
 
+// non-blocking probe of a phase: true if the phase with this parity has completed
+__device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 // L2 policy for streamed-once weights
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     uint64_t pol;
@@ -204,8 +219,6 @@ static inline size_t spif_ws_partials_bytes(int n_embd, int n_tok) {
     return (b + 255) & ~(size_t) 255;
 }
 
-// internal flag (never part of the ABI): GEMV over every row, no mask, bias + relu epilogue (predictor up projection)
-#define SPIF_INTERNAL_DENSE (1 << 30)
 
 int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,
                           const float * x, float * sparse_idx_out, float * logits_out, int n_embd, int r, int n_ff,

@@ -70,7 +70,14 @@ __device__ __forceinline__ unsigned long long gtime_ns() {
     } while (0)
 
 // ---------------------------------------------------------------------------------------------------------------
-// mask -> this CTA's share of the ascending active list.  All threads of the CTA take part.
+// mask -> this CTA's share of the active rows.  All threads of the CTA take part; every CTA scans the whole mask
+// (n_ff floats, L2-resident) and keeps the rows whose rank r satisfies r % gridDim.x == blockIdx.x.
+//
+// The rank order only has to be the SAME in every CTA (it decides ownership and the fixed summation order), it does
+// not have to be ascending in the row id.  Lane-major order (warp, lane, position in the lane's own rows) needs ONE
+// warp scan over per-lane totals instead of one per 32 rows: each warp owns a contiguous chunk, a lane reads the
+// chunk with coalesced 128-bit loads (float4 j of the lane = chunk + 32 j + lane) and packs its activity bits into
+// registers (4 bits per load).  ~200 instructions per warp at n_ff = 13824 instead of ~1500 for the ballot-per-row form.
 template <int MODE, typename WT>
 __device__ __forceinline__ void build_my_list(const FfnKParams & p, const float * mask, const float * hid, float * dense,
                                               int * warp_cnt, int * list_row, int * list_neu, float * list_alpha,
@@ -81,176 +88,107 @@ __device__ __forceinline__ void build_my_list(const FfnKParams & p, const float 
     const int nwarp = blockDim.x >> 5;
     const int P     = gridDim.x;
     const int c     = blockIdx.x;
-    if (p.flags & SPIF_INTERNAL_DENSE) {  // dense GEMV (predictor up projection): every row, round-robin over CTAs
-        const int cnt = (p.m > c) ? (p.m - c + P - 1) / P : 0;
-        for (int k = tid; k < cnt; k += blockDim.x) {
-            list_row[k] = c + k * P;
-            list_neu[k] = c + k * P;
-        }
-        if (tid == 0) {
-            s_counts[0] = cnt;
-            s_counts[1] = p.m;
-        }
-        __syncthreads();
-        return;
-    }
-    // Each warp owns a contiguous chunk of rows (a multiple of 128 long), so global ranks are ordered by
-    // (warp, position in chunk).  Two passes: count, then rank = warp base + running popcount.  All loads of a batch
-    // are unconditional (clamped addresses, no branches) so ptxas issues them back to back: a pass costs one memory
-    // round trip per batch, not one per 32 rows.  Pass 2 re-reads the mask from L1.
-    const int  chunk    = ((p.m + nwarp * 128 - 1) / (nwarp * 128)) * 128;
-    const int  r0       = min(warp * chunk, p.m);
-    const int  r1       = min(r0 + chunk, p.m);
     const bool indirect = (p.neuron_idx != nullptr);
     const bool by_row   = (p.flags & SPIF_FLAG_MASK_BY_ROW) != 0;
     const bool rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
     const bool vec_ok   = !indirect && (p.m % 4 == 0) && ((reinterpret_cast<uintptr_t>(mask) & 15) == 0) &&
                         (MODE != SPIF_MODE_AXPY || (reinterpret_cast<uintptr_t>(hid) & 15) == 0);
-
     auto alpha_of = [&](float h) -> float { return rounding ? round_through<WT>(h) : h; };
-    int  cnt = 0, before = 0, total = 0;
 
+    unsigned long long bits[2] = { 0ull, 0ull };
+    int                base    = 0;  // first float4 (vec) / first row (scalar) of my warp's chunk
     if (vec_ok) {
-        // ---- direct mask: 128-bit loads, lane l holds rows base + 4l .. 4l+3 of each 128-row group
-        constexpr int  VB   = (MODE == SPIF_MODE_AXPY) ? 5 : 10;  // 128 * VB rows per warp and batch
+        const int      n4   = p.m >> 2;
+        const int      q4   = (n4 + nwarp * 32 - 1) / (nwarp * 32);  // float4 per lane, <= 32 (checked by the launcher)
         const float4 * m4   = reinterpret_cast<const float4 *>(mask);
         const float4 * h4   = reinterpret_cast<const float4 *>(hid);
-        const int      last = p.m / 4 - 1;
-        auto bits_of = [&](const float4 & v, const float4 & h, int row) -> unsigned {
-            unsigned b = 0;
-            b |= (row + 0 < r1 && spif_is_active(v.x, p.thr)) ? 1u : 0u;
-            b |= (row + 1 < r1 && spif_is_active(v.y, p.thr)) ? 2u : 0u;
-            b |= (row + 2 < r1 && spif_is_active(v.z, p.thr)) ? 4u : 0u;
-            b |= (row + 3 < r1 && spif_is_active(v.w, p.thr)) ? 8u : 0u;
-            if (MODE == SPIF_MODE_AXPY) {  // axpy-sparse.cu:53, ggml-cpu.c:2208: alpha == 0 rows are skipped
-                b &= (alpha_of(h.x) == 0.0f ? 0u : 1u) | (alpha_of(h.y) == 0.0f ? 0u : 2u) |
-                     (alpha_of(h.z) == 0.0f ? 0u : 4u) | (alpha_of(h.w) == 0.0f ? 0u : 8u);
-            }
-            return b;
-        };
-        for (int base = r0; base < r1; base += 128 * VB) {
-            float4 v[VB], h[VB];
+        const int      last = n4 - 1;
+        base                = warp * q4 * 32;
 #pragma unroll
-            for (int j = 0; j < VB; ++j) {
-                const int f = min((base + 128 * j) / 4 + lane, last);
-                v[j]        = __ldg(m4 + f);
-                h[j]        = (MODE == SPIF_MODE_AXPY) ? __ldg(h4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int j = 0; j < VB; ++j) {
-                cnt += __popc(bits_of(v[j], h[j], base + 128 * j + 4 * lane));
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        }
-        if (lane == 0) {
-            warp_cnt[warp] = cnt;
-        }
-        __syncthreads();
-        for (int w = 0; w < nwarp; ++w) {
-            const int x = warp_cnt[w];
-            before += (w < warp) ? x : 0;
-            total += x;
-        }
-        int run = before;
-        for (int base = r0; base < r1; base += 128 * VB) {
-            float4 v[VB], h[VB];
-#pragma unroll
-            for (int j = 0; j < VB; ++j) {
-                const int f = min((base + 128 * j) / 4 + lane, last);
-                v[j]        = __ldg(m4 + f);
-                h[j]        = (MODE == SPIF_MODE_AXPY) ? __ldg(h4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-#pragma unroll
-            for (int j = 0; j < VB; ++j) {
-                const int      row0 = base + 128 * j + 4 * lane;
-                const unsigned b    = bits_of(v[j], h[j], row0);
-                const int      mine = __popc(b);
-                int            incl = mine;  // inclusive prefix of `mine` over lanes
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                    incl += (lane >= o) ? t : 0;
+        for (int h = 0; h < 2; ++h) {
+            const int jn = min(16, q4 - 16 * h);
+#pragma unroll 8
+            for (int j = 0; j < jn; ++j) {
+                const int    f  = base + (16 * h + j) * 32 + lane;
+                const float4 v  = __ldg(m4 + min(f, last));
+                unsigned     nb = (spif_is_active(v.x, p.thr) ? 1u : 0u) | (spif_is_active(v.y, p.thr) ? 2u : 0u) |
+                              (spif_is_active(v.z, p.thr) ? 4u : 0u) | (spif_is_active(v.w, p.thr) ? 8u : 0u);
+                if (MODE == SPIF_MODE_AXPY) {  // axpy-sparse.cu:53, ggml-cpu.c:2208: alpha == 0 rows are skipped
+                    const float4 a = __ldg(h4 + min(f, last));
+                    nb &= (alpha_of(a.x) == 0.0f ? 0u : 1u) | (alpha_of(a.y) == 0.0f ? 0u : 2u) |
+                          (alpha_of(a.z) == 0.0f ? 0u : 4u) | (alpha_of(a.w) == 0.0f ? 0u : 8u);
                 }
-                int         rank  = run + incl - mine;
-                const float hv[4] = { h[j].x, h[j].y, h[j].z, h[j].w };
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int row = row0 + e;
-                    if (b & (1u << e)) {
-                        const int k = (int) __umulhi((unsigned) rank, p.magic);  // rank / P without a divide
-                        if (rank - k * P == c) {
-                            list_row[k] = row;
-                            list_neu[k] = row;
-                            if (MODE == SPIF_MODE_AXPY) {
-                                list_alpha[k] = alpha_of(hv[e]);
-                            }
-                        }
-                        ++rank;
-                    } else if (MODE == SPIF_MODE_GEMV && p.zero_fill && row < r1 && (row - (int) __umulhi((unsigned) row, p.magic) * P) == c) {
-                        dense[row] = 0.0f;  // dst[neu] of inactive neurons (mm-sparse.cu:397)
-                    }
-                }
-                run += __shfl_sync(0xffffffffu, incl, 31);
+                nb = (f <= last) ? nb : 0u;
+                bits[h] |= (unsigned long long) nb << (4 * j);
             }
         }
     } else {
-        // ---- gathered mask (GPU cache / shard rows -> neuron ids) or unaligned: scalar loads, batches of 8
-        constexpr int SB    = 8;
-        const int     lastr = max(r1 - 1, 0);
-        for (int pass = 0; pass < 2; ++pass) {
-            int run = before;
-            for (int base = r0; base < r1; base += 32 * SB) {
-                int   neu[SB];
-                float v[SB], al[SB];
+        // gathered mask (GPU cache / shard rows -> neuron ids) or unaligned: scalar loads, one bit per load
+        const int q    = (p.m + nwarp * 32 - 1) / (nwarp * 32);  // rows per lane, <= 128
+        const int last = p.m - 1;
+        base           = warp * q * 32;
 #pragma unroll
-                for (int j = 0; j < SB; ++j) {
-                    const int row = min(base + j * 32 + lane, lastr);
-                    neu[j]        = indirect ? __ldg(p.neuron_idx + row) : row;
+        for (int h = 0; h < 2; ++h) {
+            const int jn = min(64, q - 64 * h);
+#pragma unroll 8
+            for (int j = 0; j < jn; ++j) {
+                const int   row = base + (64 * h + j) * 32 + lane;
+                const int   rc  = min(row, last);
+                const int   neu = indirect ? __ldg(p.neuron_idx + rc) : rc;
+                const float v   = __ldg(mask + (by_row ? rc : neu));
+                bool        a   = (row <= last) && spif_is_active(v, p.thr);
+                if (MODE == SPIF_MODE_AXPY) {
+                    a = a && !(alpha_of(__ldg(hid + neu)) == 0.0f);
                 }
+                bits[h] |= (unsigned long long) (a ? 1u : 0u) << j;
+            }
+        }
+    }
+    const int cnt  = __popcll(bits[0]) + __popcll(bits[1]);
+    int       incl = cnt;
 #pragma unroll
-                for (int j = 0; j < SB; ++j) {
-                    const int row = min(base + j * 32 + lane, lastr);
-                    v[j]          = __ldg(mask + (by_row ? row : neu[j]));
-                    al[j]         = (MODE == SPIF_MODE_AXPY) ? alpha_of(__ldg(hid + neu[j])) : 1.0f;
-                }
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        incl += (lane >= o) ? t : 0;
+    }
+    if (lane == 31) {
+        warp_cnt[warp] = incl;
+    }
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int w = 0; w < nwarp; ++w) {
+        const int x = warp_cnt[w];
+        before += (w < warp) ? x : 0;
+        total += x;
+    }
+    int rank = before + incl - cnt;
 #pragma unroll
-                for (int j = 0; j < SB; ++j) {
-                    const int      row  = base + j * 32 + lane;
-                    const bool     a    = (row < r1) && spif_is_active(v[j], p.thr) && !(al[j] == 0.0f);
-                    const unsigned ball = __ballot_sync(0xffffffffu, a);
-                    if (pass == 0) {
-                        cnt += __popc(ball);
-                    } else {
-                        if (a) {
-                            const int rank = run + __popc(ball & ((1u << lane) - 1u));
-                            const int k = (int) __umulhi((unsigned) rank, p.magic);
-                            if (rank - k * P == c) {
-                                list_row[k] = row;
-                                list_neu[k] = neu[j];
-                                if (MODE == SPIF_MODE_AXPY) {
-                                    list_alpha[k] = al[j];
-                                }
-                            }
-                        } else if (MODE == SPIF_MODE_GEMV && p.zero_fill && row < r1 && (row - (int) __umulhi((unsigned) row, p.magic) * P) == c) {
-                            dense[row] = 0.0f;
-                        }
-                        run += __popc(ball);
-                    }
+    for (int h = 0; h < 2; ++h) {
+        unsigned long long w = bits[h];
+        while (w) {
+            const int b = __ffsll((long long) w) - 1;
+            w &= w - 1;
+            const int k = (int) __umulhi((unsigned) rank, p.magic);  // rank / P without a divide
+            if (rank - k * P == c) {
+                const int row = vec_ok ? ((base + (16 * h + (b >> 2)) * 32 + lane) * 4 + (b & 3)) :
+                                         (base + (64 * h + b) * 32 + lane);
+                const int neu = indirect ? __ldg(p.neuron_idx + row) : row;
+                list_row[k]   = row;
+                list_neu[k]   = neu;
+                if (MODE == SPIF_MODE_AXPY) {
+                    list_alpha[k] = alpha_of(__ldg(hid + neu));
                 }
             }
-            if (pass == 0) {
-                if (lane == 0) {
-                    warp_cnt[warp] = cnt;
-                }
-                __syncthreads();
-                for (int w = 0; w < nwarp; ++w) {
-                    const int x = warp_cnt[w];
-                    before += (w < warp) ? x : 0;
-                    total += x;
-                }
+            ++rank;
+        }
+    }
+    if (MODE == SPIF_MODE_GEMV && p.zero_fill) {
+        // dst[neu] = 0 for inactive neurons (mm-sparse.cu:397): this CTA clears its contiguous slice of dst; active
+        // entries are written by the CTA that owns the row, so the two never touch the same element
+        const int lo = (int) ((long long) c * p.m / P), hi = (int) ((long long) (c + 1) * p.m / P);
+        for (int r = lo + tid; r < hi; r += blockDim.x) {
+            if (!spif_is_active(__ldg(mask + r), p.thr)) {
+                dense[r] = 0.0f;
             }
         }
     }
@@ -277,6 +215,18 @@ __device__ __forceinline__ void axpy_row(const uint4 * row, float alpha, float (
     }
 }
 
+// ring cursor: slot index + phase parity, advanced without integer division
+struct RingPos {
+    int      slot;
+    unsigned phase;
+    __device__ __forceinline__ void advance(int depth) {
+        if (++slot == depth) {
+            slot = 0;
+            phase ^= 1u;
+        }
+    }
+};
+
 template <typename WT, int VPT, int MODE>
 __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const FfnKParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -295,13 +245,15 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
     const int  stage_bytes = nmat * p.row_bytes;
 
     // ---- shared memory carve-up
-    unsigned char * ring  = smem;
-    unsigned char * dring = ring + (size_t) p.S * stage_bytes;
-    unsigned char * tail  = dring + (size_t) ((MODE == SPIF_MODE_FUSED) ? p.D : 0) * p.row_bytes;
-    uint64_t *      full  = reinterpret_cast<uint64_t *>(tail);
-    uint64_t *      empty = full + p.S;
-    uint64_t *      dfull = empty + p.S;
-    float *         red   = reinterpret_cast<float *>(dfull + p.D);      // [2][16][NB][2]
+    unsigned char * ring   = smem;
+    unsigned char * dring  = ring + (size_t) p.S * stage_bytes;
+    unsigned char * tail   = dring + (size_t) p.D * p.row_bytes;
+    uint64_t *      full   = reinterpret_cast<uint64_t *>(tail);
+    uint64_t *      empty  = full + p.S;
+    uint64_t *      dfull  = empty + p.S;
+    uint64_t *      dempty = dfull + p.D;
+    float *         dalpha = reinterpret_cast<float *>(dempty + p.D);    // [D] hidden value of the row in each down slot
+    float *         red    = dalpha + p.D;                               // [2][16 warps][NB][2]
     int *           warp_cnt   = reinterpret_cast<int *>(red + 2 * 16 * SPIF_NB * 2);  // [32]
     int *           s_counts   = warp_cnt + 32;                          // [4]
     int *           list_row   = s_counts + 4;
@@ -315,6 +267,7 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
         }
         for (int d = 0; d < p.D; ++d) {
             mbar_init(&dfull[d], 1);
+            mbar_init(&dempty[d], nwc);
         }
         mbar_fence_init();
     }
@@ -337,24 +290,23 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
         // ================= producer warp: stream weight rows of my active neurons =================
         if (lane == 0) {
             const uint64_t pol = l2_policy_evict_first();
+            RingPos        rp  = { 0, 1u };  // phase of the "empty" barrier to wait for (first lap: never waits)
             for (int i = 0; i < my_count; ++i) {
-                const int s = i % p.S;
                 if (i >= p.S) {
-                    mbar_wait(&empty[s], ((i / p.S) - 1) & 1);
+                    mbar_wait(&empty[rp.slot], rp.phase);
                 }
                 const size_t off = (size_t) list_row[i] * p.row_bytes;
-                mbar_arrive_expect_tx(&full[s], stage_bytes);
-                unsigned char * dst = ring + (size_t) s * stage_bytes;
+                mbar_arrive_expect_tx(&full[rp.slot], stage_bytes);
+                unsigned char * dst = ring + (size_t) rp.slot * stage_bytes;
                 if (MODE == SPIF_MODE_AXPY) {
-                    tma_load_1d(dst, p.w_down + off, p.row_bytes, &full[s], pol);
-                } else if (MODE == SPIF_MODE_GEMV) {
-                    tma_load_1d(dst, p.w_up + off, p.row_bytes, &full[s], pol);
+                    tma_load_1d(dst, p.w_down + off, p.row_bytes, &full[rp.slot], pol);
                 } else {
-                    tma_load_1d(dst, p.w_up + off, p.row_bytes, &full[s], pol);
+                    tma_load_1d(dst, p.w_up + off, p.row_bytes, &full[rp.slot], pol);
                     if (gated) {
-                        tma_load_1d(dst + p.row_bytes, p.w_gate + off, p.row_bytes, &full[s], pol);
+                        tma_load_1d(dst + p.row_bytes, p.w_gate + off, p.row_bytes, &full[rp.slot], pol);
                     }
                 }
+                rp.advance(p.S);
             }
         }
         return;
@@ -370,18 +322,19 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
     for (int j = 0; j < VPT * 8; ++j) {
         acc[j] = 0.f;
     }
-    int n_nonzero = 0;
+    int     n_nonzero = 0;
+    RingPos sp        = { 0, 0u };  // gate/up (or axpy) ring, consumer side
 
     if (MODE == SPIF_MODE_AXPY) {
         for (int i = 0; i < my_count; ++i) {
-            const int s = i % p.S;
-            mbar_wait(&full[s], (i / p.S) & 1);
-            axpy_row<WT, VPT>(reinterpret_cast<const uint4 *>(ring + (size_t) s * stage_bytes), list_alpha[i], acc, ctid,
-                              nc, V);
+            mbar_wait(&full[sp.slot], sp.phase);
+            axpy_row<WT, VPT>(reinterpret_cast<const uint4 *>(ring + (size_t) sp.slot * stage_bytes), list_alpha[i], acc,
+                              ctid, nc, V);
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive(&empty[s]);
+                mbar_arrive(&empty[sp.slot]);
             }
+            sp.advance(p.S);
         }
         n_nonzero = my_count;
     } else {
@@ -409,26 +362,38 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
         }
 
         const uint64_t pol = l2_policy_evict_first();
-        int   q_issued = 0, q_done = 0;  // down-row queue (FUSED): sequence numbers, identical in every thread
-        float pend_h[SPIF_NB];
-        int   n_pend = 0;
+        // down-row queue (FUSED): a ring of D slots filled by TMA as soon as a neuron's hidden value is known and
+        // drained lazily, always in issue order (-> fixed summation order).  The number of rows issued is identical in
+        // every consumer thread; each warp drains at its own pace, slot reuse is gated by dempty (one arrival per warp).
+        int     q_pending = 0;            // issued - drained (this warp's view)
+        int     q_total   = 0;            // issued so far
+        RingPos dq        = { 0, 0u };    // next slot to drain
+        RingPos iq        = { 0, 1u };    // next slot to issue into (+ phase of dempty to wait for once q_total >= D)
+        auto    drain_one = [&]() {
+            axpy_row<WT, VPT>(reinterpret_cast<const uint4 *>(dring + (size_t) dq.slot * p.row_bytes), dalpha[dq.slot], acc,
+                              ctid, nc, V);
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&dempty[dq.slot]);
+            }
+            dq.advance(p.D);
+            --q_pending;
+        };
 
-        const int nbatch = (my_count + SPIF_NB - 1) / SPIF_NB;
-        for (int b = 0; b < nbatch; ++b) {
-            const int nb = min(SPIF_NB, my_count - b * SPIF_NB);
+        int rbuf = 0;
+        for (int i0 = 0; i0 < my_count; i0 += SPIF_NB) {
+            const int nb = min(SPIF_NB, my_count - i0);
             float     pu[SPIF_NB], pg[SPIF_NB];
 #pragma unroll
             for (int j = 0; j < SPIF_NB; ++j) {
                 pu[j] = 0.f, pg[j] = 0.f;
                 if (j < nb) {
-                    const int i = b * SPIF_NB + j;
-                    const int s = i % p.S;
-                    mbar_wait(&full[s], (i / p.S) & 1);
-                    if (i == 0) {
+                    mbar_wait(&full[sp.slot], sp.phase);
+                    if (i0 == 0 && j == 0) {
                         SPIF_STAMP(3);
                     }
-                    const uint4 * ur = reinterpret_cast<const uint4 *>(ring + (size_t) s * stage_bytes);
-                    const uint4 * gr = reinterpret_cast<const uint4 *>(ring + (size_t) s * stage_bytes + p.row_bytes);
+                    const uint4 * ur = reinterpret_cast<const uint4 *>(ring + (size_t) sp.slot * stage_bytes);
+                    const uint4 * gr = reinterpret_cast<const uint4 *>(ring + (size_t) sp.slot * stage_bytes + p.row_bytes);
 #pragma unroll
                     for (int k = 0; k < VPT; ++k) {
                         const int v = ctid + k * nc;
@@ -450,12 +415,14 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
                     }
                     __syncwarp();
                     if (lane == 0) {
-                        mbar_arrive(&empty[s]);  // stage free for the producer
+                        mbar_arrive(&empty[sp.slot]);  // stage free for the producer
                     }
+                    sp.advance(p.S);
                 }
             }
-            // cross-warp reduction of the batch
-            float * rb = red + (size_t) (b & 1) * 16 * SPIF_NB * 2;
+            // cross-warp reduction of the batch: warp partials -> smem -> every warp re-sums them, one value per lane
+            float * rb = red + rbuf * (16 * SPIF_NB * 2);
+            rbuf ^= 1;
 #pragma unroll
             for (int j = 0; j < SPIF_NB; ++j) {
                 pu[j] = warp_sum(pu[j]);
@@ -466,30 +433,28 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
             if (lane == 0) {
 #pragma unroll
                 for (int j = 0; j < SPIF_NB; ++j) {
-                    rb[(warp * SPIF_NB + j) * 2 + 0] = pu[j];
-                    rb[(warp * SPIF_NB + j) * 2 + 1] = pg[j];
+                    rb[(j * 2 + 0) * 16 + warp] = pu[j];
+                    rb[(j * 2 + 1) * 16 + warp] = pg[j];
                 }
             }
             named_bar_sync(1, nc);
+            // lane q < 2*NB sums column q of the [2*NB][16] table in warp order (fixed order), then broadcast
+            float tot = 0.f;
+            if (lane < 2 * SPIF_NB) {
+                for (int w = 0; w < nwc; ++w) {
+                    tot += rb[lane * 16 + w];
+                }
+            }
             float hcur[SPIF_NB];
+            int   nq = 0;
 #pragma unroll
             for (int j = 0; j < SPIF_NB; ++j) {
+                float u = __shfl_sync(0xffffffffu, tot, 2 * j);
+                float g = __shfl_sync(0xffffffffu, tot, 2 * j + 1);
                 hcur[j] = 0.f;
                 if (j < nb) {
-                    float u = 0.f, g = 0.f;
-                    for (int w = 0; w < nwc; ++w) {
-                        u += rb[(w * SPIF_NB + j) * 2 + 0];
-                        g += rb[(w * SPIF_NB + j) * 2 + 1];
-                    }
-                    const int i   = b * SPIF_NB + j;
-                    const int neu = list_neu[i];
+                    const int neu = list_neu[i0 + j];
                     if (MODE == SPIF_MODE_GEMV) {
-                        if (p.flags & SPIF_INTERNAL_DENSE) {  // predictor up: + bias, relu (llama-graph.cpp:871-880)
-                            if (p.b_up) {
-                                u += __ldg(p.b_up + neu);
-                            }
-                            u = (u > 0.f) ? u : 0.f;
-                        }
                         if (ctid == 0) {
                             dense[neu] = u;
                         }
@@ -508,49 +473,52 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
                             h = round_through<WT>(h);
                         }
                         hcur[j] = h;
+                        nq += !(h == 0.0f) ? 1 : 0;  // axpy-sparse.cu:53: rows with hid == 0 are never read
                     }
                 }
             }
             if (MODE == SPIF_MODE_FUSED) {
-                // issue this batch's down rows (only where hid != 0), then consume the previous batch's
-                float hq[SPIF_NB];
-                int   nq = 0;
+                // make room: every warp drains (blocking) until this batch's rows fit -- the same rule in every warp, so
+                // the issuing thread's wait on dempty below never depends on a warp that is parked at the next barrier
+                while (q_pending + nq > p.D) {
+                    mbar_wait(&dfull[dq.slot], dq.phase);
+                    drain_one();
+                }
 #pragma unroll
                 for (int j = 0; j < SPIF_NB; ++j) {
                     if (j < nb && !(hcur[j] == 0.0f)) {
                         if (ctid == 0) {
-                            const int    slot = q_issued % p.D;
-                            const size_t off  = (size_t) list_row[b * SPIF_NB + j] * p.row_bytes;
-                            mbar_arrive_expect_tx(&dfull[slot], p.row_bytes);
-                            tma_load_1d(dring + (size_t) slot * p.row_bytes, p.w_down + off, p.row_bytes, &dfull[slot], pol);
+                            if (q_total >= p.D) {
+                                mbar_wait(&dempty[iq.slot], iq.phase);
+                            }
+                            dalpha[iq.slot]  = hcur[j];
+                            const size_t off = (size_t) list_row[i0 + j] * p.row_bytes;
+                            mbar_arrive_expect_tx(&dfull[iq.slot], p.row_bytes);
+                            tma_load_1d(dring + (size_t) iq.slot * p.row_bytes, p.w_down + off, p.row_bytes, &dfull[iq.slot], pol);
                         }
-                        ++q_issued;
-                        hq[nq++] = hcur[j];
+                        iq.advance(p.D);
+                        ++q_total;
+                        ++q_pending;
                     }
                 }
-                for (int j = 0; j < n_pend; ++j) {
-                    const int slot = q_done % p.D;
-                    mbar_wait(&dfull[slot], (q_done / p.D) & 1);
-                    axpy_row<WT, VPT>(reinterpret_cast<const uint4 *>(dring + (size_t) slot * p.row_bytes), pend_h[j], acc,
-                                      ctid, nc, V);
-                    ++q_done;
+                // opportunistic: rows that have already landed are folded in now instead of in the tail
+                while (q_pending > 0) {
+                    unsigned ok = (lane == 0 && mbar_test(&dfull[dq.slot], dq.phase)) ? 1u : 0u;
+                    ok          = __shfl_sync(0xffffffffu, ok, 0);  // warp-uniform decision
+                    if (!ok) {
+                        break;
+                    }
+                    mbar_wait(&dfull[dq.slot], dq.phase);  // returns at once; every lane gets its own acquire on the data
+                    drain_one();
                 }
-                n_pend = nq;
-#pragma unroll
-                for (int j = 0; j < SPIF_NB; ++j) {
-                    pend_h[j] = hq[j];
-                }
-                n_nonzero += nq;
             }
         }
         SPIF_STAMP(4);
         if (MODE == SPIF_MODE_FUSED) {
-            for (int j = 0; j < n_pend; ++j) {
-                const int slot = q_done % p.D;
-                mbar_wait(&dfull[slot], (q_done / p.D) & 1);
-                axpy_row<WT, VPT>(reinterpret_cast<const uint4 *>(dring + (size_t) slot * p.row_bytes), pend_h[j], acc, ctid,
-                                  nc, V);
-                ++q_done;
+            n_nonzero = q_total;
+            while (q_pending > 0) {
+                mbar_wait(&dfull[dq.slot], dq.phase);
+                drain_one();
             }
         }
     }
@@ -579,44 +547,55 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// y[t][col] = sum_p partials[t][p][col] (+ b_down[col]) in a fixed order.  block (32 column-vectors, 16 p-chunks):
-// every thread has all of its <= SPIF_RED_PER loads in flight at once (one L2 round trip), then a fixed-order smem sum.
-#define SPIF_RED_CHUNKS 16
-#define SPIF_RED_PER    20 /* ceil(P / 16) for P <= 320 CTAs */
-__global__ void __launch_bounds__(32 * SPIF_RED_CHUNKS) spif_reduce_partials_kernel(const float * __restrict__ partials,
-                                                                                     const float * __restrict__ b_down,
-                                                                                     float * __restrict__ y,
-                                                                                     const int32_t * __restrict__ cta_stats,
-                                                                                     int32_t * __restrict__ stats_out,
-                                                                                     int n_embd, int P) {
-    __shared__ float4 sm[SPIF_RED_CHUNKS][32];
+// y[t][col] = sum_p partials[t][p][col] (+ b_down[col]) in a fixed order.  Block = 8 column-vectors (128 B of every
+// partial row) x 32 partial lanes: thread (cx, py) loads partials py, py+32, ... (<= SPIF_RED_PER, all in flight at
+// once -> one L2 round trip), then a fixed-shape two-level sum through shared memory.  n_embd/32 CTAs (160 at 13B).
+#define SPIF_RED_COLS  8
+#define SPIF_RED_LANES 32
+#define SPIF_RED_PER   10 /* ceil(P / 32) for P <= 320 CTAs */
+__global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_partials_kernel(
+    const float * __restrict__ partials, const float * __restrict__ b_down, float * __restrict__ y,
+    const int32_t * __restrict__ cta_stats, int32_t * __restrict__ stats_out, int n_embd, int P) {
+    __shared__ float4 sm[SPIF_RED_LANES][SPIF_RED_COLS];
+    __shared__ float4 sm2[4][SPIF_RED_COLS];
     const int         tok  = blockIdx.y;
-    const int         col4 = blockIdx.x * 32 + threadIdx.x;
-    const int         ch   = threadIdx.y;
+    const int         cx   = threadIdx.x & (SPIF_RED_COLS - 1);
+    const int         py   = threadIdx.x / SPIF_RED_COLS;
+    const int         col4 = blockIdx.x * SPIF_RED_COLS + cx;
     const int         n4   = n_embd >> 2;
-    const int         per  = (P + SPIF_RED_CHUNKS - 1) / SPIF_RED_CHUNKS;
     pdl_wait_prior_grid();
+    pdl_launch_dependents();
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (col4 < n4) {
         const float4 * base = reinterpret_cast<const float4 *>(partials + (size_t) tok * P * n_embd) + col4;
-        const int      p0   = ch * per;
         float4         v[SPIF_RED_PER];
 #pragma unroll
         for (int q = 0; q < SPIF_RED_PER; ++q) {
-            v[q] = (q < per && p0 + q < P) ? base[(size_t) (p0 + q) * n4] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const int pp = py + q * SPIF_RED_LANES;
+            v[q]         = (pp < P) ? base[(size_t) pp * n4] : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int q = 0; q < SPIF_RED_PER; ++q) {
             s.x += v[q].x, s.y += v[q].y, s.z += v[q].z, s.w += v[q].w;
         }
     }
-    sm[ch][threadIdx.x] = s;
+    sm[py][cx] = s;
     __syncthreads();
-    if (ch == 0 && col4 < n4) {
-        float4 t = sm[0][threadIdx.x];
+    if (py < 4) {  // 4 x 8 threads: each sums 8 lanes in order
+        float4 t = sm[py * 8][cx];
 #pragma unroll
-        for (int k = 1; k < SPIF_RED_CHUNKS; ++k) {
-            const float4 v = sm[k][threadIdx.x];
+        for (int k = 1; k < 8; ++k) {
+            const float4 v = sm[py * 8 + k][cx];
+            t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
+        }
+        sm2[py][cx] = t;
+    }
+    __syncthreads();
+    if (py == 0 && col4 < n4) {
+        float4 t = sm2[0][cx];
+#pragma unroll
+        for (int k = 1; k < 4; ++k) {
+            const float4 v = sm2[k][cx];
             t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
         }
         if (b_down) {
@@ -625,15 +604,21 @@ __global__ void __launch_bounds__(32 * SPIF_RED_CHUNKS) spif_reduce_partials_ker
         }
         reinterpret_cast<float4 *>(y + (size_t) tok * n_embd)[col4] = t;
     }
-    if (stats_out && blockIdx.x == 0 && threadIdx.x == 0 && ch == 0) {
+    if (stats_out && blockIdx.x == 0 && threadIdx.x < 32) {
         int nz = 0;
-        for (int q = 0; q < P; ++q) {
+        for (int q = threadIdx.x; q < P; q += 32) {
             nz += cta_stats[((size_t) tok * P + q) * 2 + 1];
         }
-        stats_out[tok * 4 + 0] = cta_stats[((size_t) tok * P) * 2 + 0];
-        stats_out[tok * 4 + 1] = nz;
-        stats_out[tok * 4 + 2] = 0;
-        stats_out[tok * 4 + 3] = 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            nz += __shfl_xor_sync(0xffffffffu, nz, o);
+        }
+        if (threadIdx.x == 0) {
+            stats_out[tok * 4 + 0] = cta_stats[((size_t) tok * P) * 2 + 0];
+            stats_out[tok * 4 + 1] = nz;
+            stats_out[tok * 4 + 2] = 0;
+            stats_out[tok * 4 + 3] = 0;
+        }
     }
 }
 
@@ -698,7 +683,7 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     static const int k_ctas_per_sm = [] { const char * e = getenv("SPIF_CTAS_PER_SM"); int v = e ? atoi(e) : 1; return v < 1 ? 1 : (v > 2 ? 2 : v); }();
     static const int k_max_stages  = [] { const char * e = getenv("SPIF_STAGES"); int v = e ? atoi(e) : 8; return v < 2 ? 2 : (v > 8 ? 8 : v); }();
     const int P = ctx.sm_count * k_ctas_per_sm;
-    SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_CHUNKS * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_LANES * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
     FfnKParams kp = {};
     kp.w_up       = (const unsigned char *) a.w_up;
     kp.w_gate     = (const unsigned char *) a.w_gate;
@@ -721,9 +706,8 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     kp.dense_out  = (mode == SPIF_MODE_GEMV) ? dst_dense : a.hidden_out;
     kp.trace      = g_spif_trace;
     kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;
-    const bool dense_list = (a.flags & SPIF_INTERNAL_DENSE) != 0;
-    SPIF_REQUIRE(dense_list || a.sparse_idx != nullptr, SPIF_E_NULL);
-    kp.zero_fill  = (mode == SPIF_MODE_GEMV && a.neuron_idx == nullptr && !dense_list) ? 1 : 0;
+    SPIF_REQUIRE(a.sparse_idx != nullptr, SPIF_E_NULL);
+    kp.zero_fill  = (mode == SPIF_MODE_GEMV && a.neuron_idx == nullptr && !(a.flags & SPIF_FLAG_MASK_BY_ROW)) ? 1 : 0;
 
     // thread shape: VPT 16-byte vectors per consumer thread
     const int V   = kp.V;
@@ -735,16 +719,38 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     const bool gated = (mode == SPIF_MODE_FUSED) && (a.arch != SPIF_ARCH_RELU_UP);
     const int  nmat  = gated ? 2 : 1;
     kp.list_cap      = (a.m + P - 1) / P + 1;
-    kp.D             = (mode == SPIF_MODE_FUSED) ? 2 * SPIF_NB : 0;
-    const size_t fixed =
-        (size_t) 8 * (2 * 8 + kp.D) + sizeof(float) * 2 * 16 * SPIF_NB * 2 + sizeof(int) * (32 + 4) + (size_t) 12 * kp.list_cap + 256;
+    static const int k_dslots = [] { const char * e = getenv("SPIF_DSLOTS"); int v = e ? atoi(e) : 0; return v < 0 ? 0 : (v > 16 ? 16 : v); }();
+    const int    nwarp_all  = threads / 32;
+    SPIF_REQUIRE(a.m <= 4096 * nwarp_all, SPIF_E_SHAPE);  // activity bits kept in registers by build_my_list
+    const size_t stage_b    = (size_t) nmat * kp.row_bytes;
+    const size_t fixed      = (size_t) 8 * (2 * 8 + 2 * 16) + 4 * 16 + sizeof(float) * 2 * 16 * SPIF_NB * 2 + sizeof(int) * (32 + 4) +
+                         (size_t) 12 * kp.list_cap + 256;
     const size_t budget = ((size_t) ctx.max_smem_optin - 1024) / k_ctas_per_sm - (k_ctas_per_sm > 1 ? 1024 : 0);
-    const size_t dbytes = (size_t) kp.D * kp.row_bytes;
-    SPIF_REQUIRE(budget > fixed + dbytes + 2 * (size_t) nmat * kp.row_bytes, SPIF_E_SHAPE);
-    int S = (int) ((budget - fixed - dbytes) / ((size_t) nmat * kp.row_bytes));
-    S     = S > k_max_stages ? k_max_stages : S;
-    kp.S  = S;
-    const size_t smem = (size_t) S * nmat * kp.row_bytes + dbytes + fixed;
+    SPIF_REQUIRE(budget > fixed + 2 * stage_b + (mode == SPIF_MODE_FUSED ? 2 * (size_t) kp.row_bytes : 0), SPIF_E_SHAPE);
+    const size_t ring_budget = budget - fixed;
+    int          S, D = 0;
+    if (mode == SPIF_MODE_FUSED) {
+        // roughly half of the ring for gate/up stages (enough bytes in flight to cover HBM latency), the rest for down
+        // rows so that their fetch never has to wait for a slot at ~10% activity
+        S = (int) ((ring_budget * 45 / 100) / stage_b);
+        S = S < 2 ? 2 : (S > k_max_stages ? k_max_stages : S);
+        D = (int) ((ring_budget - (size_t) S * stage_b) / kp.row_bytes);
+        D = D > 16 ? 16 : D;
+        if (k_dslots >= 2 && k_dslots < D) {
+            D = k_dslots;
+        }
+        while (D < 2 && S > 2) {
+            --S;
+            D = (int) ((ring_budget - (size_t) S * stage_b) / kp.row_bytes);
+        }
+        SPIF_REQUIRE(D >= 2, SPIF_E_SHAPE);
+    } else {
+        S = (int) (ring_budget / stage_b);
+        S = S > k_max_stages ? k_max_stages : S;
+    }
+    kp.S = S;
+    kp.D = D;
+    const size_t smem = (size_t) S * stage_b + (size_t) D * kp.row_bytes + fixed;
 
     // workspace
     const size_t part_bytes = sizeof(float) * (size_t) a.n_tok * P * a.n_embd;
@@ -754,7 +760,7 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
         kp.partials  = (float *) ws;
         kp.cta_stats = (int32_t *) ((char *) ws + part_bytes);
     }
-    if (mode == SPIF_MODE_GEMV && !kp.zero_fill && !dense_list) {
+    if (mode == SPIF_MODE_GEMV && !kp.zero_fill) {
         SPIF_CUDA_TRY(cudaMemsetAsync(dst_dense, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
     }
     if (mode == SPIF_MODE_FUSED && a.hidden_out) {
@@ -770,8 +776,8 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     if (mode != SPIF_MODE_GEMV) {
         float *            y  = (mode == SPIF_MODE_AXPY) ? dst_dense : a.y;
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim            = dim3((a.n_embd / 4 + 31) / 32, a.n_tok);
-        cfg.blockDim           = dim3(32, SPIF_RED_CHUNKS);
+        cfg.gridDim            = dim3((a.n_embd / 4 + SPIF_RED_COLS - 1) / SPIF_RED_COLS, a.n_tok);
+        cfg.blockDim           = dim3(SPIF_RED_COLS * SPIF_RED_LANES);
         cfg.stream             = ctx.stream;
         cudaLaunchAttribute at[1];
         at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;

@@ -2,145 +2,161 @@
 //
 // Reference: llm_graph_context::build_predictor (src/llama-graph.cpp:865-894) = six stock ggml nodes
 // (MUL_MAT, ADD, RELU, MUL_MAT, ADD, SIGMOID; on CUDA bs=1: mul_mat_vec_f mmvf.cu:6, unary.cu:44-50).
-// Here: two kernels.
-//   up   : rows of Wpu are n_embd long -> the cooperative K-slice GEMV of spif_ffn.cu (SPIF_MODE_GEMV, dense list,
-//          bias + relu epilogue), x in registers, rows streamed by TMA.
-//   down : rows of Wpd are short (r elements, 2 KB at r = 1024) -> this file: chunks of 8 consecutive rows are one
-//          contiguous byte range, streamed by TMA bulk copies into a shared-memory ring; one warp per row, the hidden
-//          vector in registers, bias + sigmoid fused, logits optionally kept for flip accounting.
+// Here: two launches of ONE dense streaming GEMV kernel with fused epilogues
+//   up   : h1 = relu(Wpu . x + bpu)                 rows = r,    K = n_embd
+//   down : z = Wpd . h1 + bpd ; p = sigmoid(z)      rows = n_ff, K = r
+//
+// Both matrices are read exactly once per token and nothing about their addresses depends on data, so the kernel is
+// a pure HBM stream: every warp owns a fixed K-slice (its slice of the input vector stays in registers) and walks the
+// rows of its CTA's contiguous row block with U rows x VL 128-bit loads in flight per lane (ld.global.nc, L1 no-allocate).
+// No shared-memory staging: the kernel is deliberately light on registers and uses (almost) no shared memory so that it
+// can be co-resident on an SM with the TMA-ring sparse-FFN kernel of the previous layer (the look-ahead predictor of
+// layer l+1 only depends on x_l, llama-graph.cpp:939-946, so the two run on parallel graph branches).
+// The first batch of weight loads is issued BEFORE griddepcontrol.wait: weights never depend on the previous kernel.
 #include "spif_common.cuh"
 
-#define PD_ROWS   8   /* rows per chunk == consumer warps */
-#define PD_STAGES 6
+#define DG_MAX_WARPS 12
+#define DG_U         2 /* rows in flight per warp */
 
-struct PredDownParams {
-    const unsigned char * wpd;   // [n_ff][r]
-    const float *         bpd;   // nullable [n_ff]
-    const float *         h1;    // [n_tok][r]
-    float *               out;   // [n_tok][n_ff] sigmoid
-    float *               logits;// nullable [n_tok][n_ff]
-    int                   n_ff, r, row_bytes, flags;
+enum { DG_EPI_RELU = 0, DG_EPI_SIGMOID = 1 };
+
+struct DenseGemvParams {
+    const unsigned char * w;       // [rows][K] weight type
+    const float *         bias;    // nullable [rows]
+    const float *         x;       // [n_tok][K]
+    float *               out;     // [n_tok][rows]
+    float *               logits;  // nullable [n_tok][rows] (pre-activation, SIGMOID epilogue only)
+    int                   rows, K, V;  // V = K / 8 vectors per row
+    int                   ns, nrw;     // K-slices per row, row lanes per CTA
+    int                   rpc;         // rows per CTA (contiguous block)
+    int                   flags;
 };
 
-template <typename WT, int VL>
-__global__ void __launch_bounds__((PD_ROWS + 1) * 32, 1) spif_pred_down_kernel(const PredDownParams p) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int P = gridDim.x, c = blockIdx.x, tok = blockIdx.y;
-    const int chunk_bytes = PD_ROWS * p.row_bytes;
+template <typename WT, int VL, int EPI>
+__global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(const DenseGemvParams p) {
+    extern __shared__ float part[];  // [rpc][ns] partial dots (only when ns > 1)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tok  = blockIdx.y;
+    const int sl   = warp % p.ns;  // my K-slice
+    const int rl   = warp / p.ns;  // my row lane
+    const int r0   = blockIdx.x * p.rpc;
+    const int r1   = min(r0 + p.rpc, p.rows);
+    const int v0   = sl * (VL * 32);  // first vector of my slice
+    const size_t row_bytes = (size_t) p.K * 2;
 
-    unsigned char * ring  = smem;
-    uint64_t *      full  = reinterpret_cast<uint64_t *>(ring + (size_t) PD_STAGES * chunk_bytes);
-    uint64_t *      empty = full + PD_STAGES;
-
-    if (tid == 0) {
-        for (int s = 0; s < PD_STAGES; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], PD_ROWS);
-        }
-        mbar_fence_init();
-    }
-    __syncthreads();
-
-    const int n_chunks = (p.n_ff + PD_ROWS - 1) / PD_ROWS;
-    const int my_n     = (n_chunks > c) ? (n_chunks - c + P - 1) / P : 0;
-
-    if (warp == PD_ROWS) {
-        // producer: weights do not depend on the previous kernel -> start streaming before the PDL wait
-        if (lane == 0) {
-            const uint64_t pol = l2_policy_evict_first();
-            for (int i = 0; i < my_n; ++i) {
-                const int s = i % PD_STAGES;
-                if (i >= PD_STAGES) {
-                    mbar_wait(&empty[s], ((i / PD_STAGES) - 1) & 1);
-                }
-                const int      ch    = c + i * P;
-                const int      rows  = min(PD_ROWS, p.n_ff - ch * PD_ROWS);
-                const uint32_t bytes = (uint32_t) rows * p.row_bytes;
-                mbar_arrive_expect_tx(&full[s], bytes);
-                tma_load_1d(ring + (size_t) s * chunk_bytes, p.wpd + (size_t) ch * chunk_bytes, bytes, &full[s], pol);
-            }
-        }
-        return;
-    }
-
-    pdl_wait_prior_grid();  // h1 comes from the up kernel
-    pdl_launch_dependents();
-
-    // hidden vector slice in registers: vectors v = lane + 32*k
-    const int     Vr = p.r >> 3;
-    const float * h  = p.h1 + (size_t) tok * p.r;
-    float         hr[VL * 8];
+    // vector k of lane: v0 + lane + 32 k   (coalesced 512 B per warp instruction)
+    uint4 wv[DG_U][VL];
+    auto  load_rows = [&](int rbase) {
 #pragma unroll
-    for (int k = 0; k < VL; ++k) {
-        const int v = lane + 32 * k;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            hr[k * 8 + j] = 0.f;
-        }
-        if (v < Vr) {
-            const float4 a = __ldg(reinterpret_cast<const float4 *>(h) + 2 * v);
-            const float4 b = __ldg(reinterpret_cast<const float4 *>(h) + 2 * v + 1);
-            hr[k * 8 + 0] = a.x, hr[k * 8 + 1] = a.y, hr[k * 8 + 2] = a.z, hr[k * 8 + 3] = a.w;
-            hr[k * 8 + 4] = b.x, hr[k * 8 + 5] = b.y, hr[k * 8 + 6] = b.z, hr[k * 8 + 7] = b.w;
-            if (p.flags & SPIF_FLAG_CPU_ROUNDING) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    hr[k * 8 + j] = round_through<WT>(hr[k * 8 + j]);
-                }
-            }
-        }
-    }
-
-    for (int i = 0; i < my_n; ++i) {
-        const int s = i % PD_STAGES;
-        mbar_wait(&full[s], (i / PD_STAGES) & 1);
-        const int ch  = c + i * P;
-        const int row = ch * PD_ROWS + warp;
-        float     z   = 0.f;
-        if (row < p.n_ff) {
-            const uint4 * wr = reinterpret_cast<const uint4 *>(ring + (size_t) s * chunk_bytes + (size_t) warp * p.row_bytes);
+        for (int u = 0; u < DG_U; ++u) {
+            const int row = min(rbase + u * p.nrw, r1 - 1);
+            const unsigned char * rp = p.w + (size_t) row * row_bytes;
 #pragma unroll
             for (int k = 0; k < VL; ++k) {
-                const int v = lane + 32 * k;
-                if (v < Vr) {
+                const int v = min(v0 + lane + 32 * k, p.V - 1);
+                wv[u][k]    = ldg_stream_v4(rp + (size_t) v * 16);
+            }
+        }
+    };
+
+    const bool have_work = (rl < p.nrw) && (r0 + rl < r1);
+    if (have_work) {
+        load_rows(r0 + rl);  // in flight across the PDL wait
+    }
+    pdl_wait_prior_grid();  // x (h1) comes from the previous kernel
+    pdl_launch_dependents();
+
+    float xr[VL * 8];
+    {
+        const float * xt = p.x + (size_t) tok * p.K;
+#pragma unroll
+        for (int k = 0; k < VL; ++k) {
+            const int v = v0 + lane + 32 * k;
+            if (v < p.V) {
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(xt) + 2 * v);
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(xt) + 2 * v + 1);
+                xr[k * 8 + 0] = a.x, xr[k * 8 + 1] = a.y, xr[k * 8 + 2] = a.z, xr[k * 8 + 3] = a.w;
+                xr[k * 8 + 4] = b.x, xr[k * 8 + 5] = b.y, xr[k * 8 + 6] = b.z, xr[k * 8 + 7] = b.w;
+                if (p.flags & SPIF_FLAG_CPU_ROUNDING) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        xr[k * 8 + j] = round_through<WT>(xr[k * 8 + j]);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    xr[k * 8 + j] = 0.f;  // clamped (duplicate) vectors past the end contribute nothing
+                }
+            }
+        }
+    }
+
+    auto finish = [&](int row, float z) {
+        if (p.bias) {
+            z += __ldg(p.bias + row);
+        }
+        if (EPI == DG_EPI_RELU) {
+            p.out[(size_t) tok * p.rows + row] = (z > 0.f) ? z : 0.f;  // llama-graph.cpp:871-880
+        } else {
+            if (p.logits) {
+                p.logits[(size_t) tok * p.rows + row] = z;
+            }
+            p.out[(size_t) tok * p.rows + row] = 1.f / (1.f + expf(-z));  // unary-ops.cpp:31-33 / unary.cu:48-50
+        }
+    };
+
+    if (have_work) {
+        const int step = DG_U * p.nrw;
+        for (int rb = r0 + rl; rb < r1; rb += step) {
+            float acc[DG_U][2];
+#pragma unroll
+            for (int u = 0; u < DG_U; ++u) {
+                acc[u][0] = 0.f, acc[u][1] = 0.f;
+#pragma unroll
+                for (int k = 0; k < VL; ++k) {
                     float w[8];
-                    unpack8<WT>(wr[v], w);
+                    unpack8<WT>(wv[u][k], w);
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        z = fmaf(w[e], hr[k * 8 + e], z);
+                        acc[u][e & 1] = fmaf(w[e], xr[k * 8 + e], acc[u][e & 1]);
+                    }
+                }
+            }
+            if (rb + step < r1) {
+                load_rows(rb + step);  // next batch in flight while this one is reduced
+            }
+#pragma unroll
+            for (int u = 0; u < DG_U; ++u) {
+                const int   row = rb + u * p.nrw;
+                const float z   = warp_sum(acc[u][0] + acc[u][1]);
+                if (lane == 0 && row < r1) {
+                    if (p.ns == 1) {
+                        finish(row, z);
+                    } else {
+                        part[(row - r0) * p.ns + sl] = z;
                     }
                 }
             }
         }
-        __syncwarp();
-        if (lane == 0) {
-            mbar_arrive(&empty[s]);
-        }
-        z = warp_sum(z);
-        if (lane == 0 && row < p.n_ff) {
-            if (p.bpd) {
-                z += __ldg(p.bpd + row);
+    }
+    if (p.ns > 1) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < r1 - r0; i += blockDim.x) {
+            float z = 0.f;
+            for (int s = 0; s < p.ns; ++s) {  // fixed order -> run-to-run bit-stable
+                z += part[i * p.ns + s];
             }
-            if (p.logits) {
-                p.logits[(size_t) tok * p.n_ff + row] = z;
-            }
-            p.out[(size_t) tok * p.n_ff + row] = 1.f / (1.f + expf(-z));  // unary-ops.cpp:31-33 / unary.cu:48-50
+            finish(r0 + i, z);
         }
     }
 }
 
-template <typename WT, int VL>
-static int launch_pd(const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream, int device) {
-    auto                      kern = spif_pred_down_kernel<WT, VL>;
-    static unsigned long long done = 0;
-    int                       rc0  = spif_set_max_smem_once(kern, smem, device, done);
-    if (rc0) {
-        return rc0;
-    }
+template <typename WT, int VL, int EPI>
+static int launch_dg(const DenseGemvParams & p, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = grid;
-    cfg.blockDim           = dim3((PD_ROWS + 1) * 32);
+    cfg.blockDim           = dim3(threads);
     cfg.dynamicSmemBytes   = smem;
     cfg.stream             = stream;
     cudaLaunchAttribute at[1];
@@ -148,21 +164,58 @@ static int launch_pd(const PredDownParams & p, dim3 grid, size_t smem, cudaStrea
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs                                        = at;
     cfg.numAttrs                                     = 1;
-    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p));
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_dense_gemv_kernel<WT, VL, EPI>, p));
     return 0;
 }
 
-template <typename WT> static int launch_pd_v(int vl, const PredDownParams & p, dim3 grid, size_t smem, cudaStream_t stream, int device) {
+template <typename WT, int EPI>
+static int launch_dg_v(int vl, const DenseGemvParams & p, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
     switch (vl) {
         case 1:
-            return launch_pd<WT, 1>(p, grid, smem, stream, device);
+            return launch_dg<WT, 1, EPI>(p, grid, threads, smem, stream);
         case 2:
-            return launch_pd<WT, 2>(p, grid, smem, stream, device);
-        case 4:
-            return launch_pd<WT, 4>(p, grid, smem, stream, device);
+            return launch_dg<WT, 2, EPI>(p, grid, threads, smem, stream);
         default:
-            return launch_pd<WT, 8>(p, grid, smem, stream, device);
+            return launch_dg<WT, 4, EPI>(p, grid, threads, smem, stream);
     }
+}
+
+// out[t][row] = epi(W[row] . x[t] + bias[row])
+static int dense_gemv(int type, int epi, const void * w, const float * bias, const float * x, float * out, float * logits,
+                      int rows, int K, int n_tok, int flags, const spif_launch_ctx & ctx) {
+    DenseGemvParams p = {};
+    p.w      = (const unsigned char *) w;
+    p.bias   = bias;
+    p.x      = x;
+    p.out    = out;
+    p.logits = logits;
+    p.rows   = rows;
+    p.K      = K;
+    p.V      = K / 8;
+    p.flags  = flags;
+    // slice width: VL*32 vectors of 8 elements per warp pass
+    const int vl = (p.V >= 128) ? 4 : (p.V >= 64 ? 2 : 1);
+    p.ns = (p.V + vl * 32 - 1) / (vl * 32);
+    SPIF_REQUIRE(p.ns <= DG_MAX_WARPS, SPIF_E_SHAPE);  // K <= 12 * 1024 elements
+    p.nrw             = DG_MAX_WARPS / p.ns;
+    const int threads = p.ns * p.nrw * 32;
+    const int per_sm  = (2 * DG_MAX_WARPS * 32) / threads;  // CTAs that fit the 2 x 384-thread register budget
+    const int G       = ctx.sm_count * (per_sm < 1 ? 1 : per_sm);
+    p.rpc             = (rows + G - 1) / G;
+    // keep every row lane busy: at least nrw rows per CTA when there are enough rows
+    if (p.rpc < p.nrw) {
+        p.rpc = p.nrw;
+    }
+    const int    grid_x = (rows + p.rpc - 1) / p.rpc;
+    const size_t smem   = (p.ns > 1) ? sizeof(float) * (size_t) p.rpc * p.ns : 0;
+    SPIF_REQUIRE(smem <= 48 * 1024, SPIF_E_SHAPE);
+    const dim3 grid(grid_x, n_tok);
+    if (type == SPIF_TYPE_F16) {
+        return epi == DG_EPI_RELU ? launch_dg_v<spif_f16, DG_EPI_RELU>(vl, p, grid, threads, smem, ctx.stream) :
+                                    launch_dg_v<spif_f16, DG_EPI_SIGMOID>(vl, p, grid, threads, smem, ctx.stream);
+    }
+    return epi == DG_EPI_RELU ? launch_dg_v<spif_bf16, DG_EPI_RELU>(vl, p, grid, threads, smem, ctx.stream) :
+                                launch_dg_v<spif_bf16, DG_EPI_SIGMOID>(vl, p, grid, threads, smem, ctx.stream);
 }
 
 int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,
@@ -176,40 +229,10 @@ int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const 
     const size_t h1_bytes = sizeof(float) * (size_t) n_tok * r;
     SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= h1_off + h1_bytes, SPIF_E_WORKSPACE);
     float * h1 = (float *) ((char *) ws + h1_off);
-
-    // up: dense GEMV + bias + relu through the FFN kernel template
-    spif_ffn_args a = {};
-    a.arch          = SPIF_ARCH_RELU_UP;
-    a.type          = ptype;
-    a.n_embd        = n_embd;
-    a.n_ff          = r;
-    a.m             = r;
-    a.n_tok         = n_tok;
-    a.flags         = (flags & SPIF_FLAG_CPU_ROUNDING) | (1 << 30);  // bit 30: dense list + bias/relu epilogue
-    a.thr           = 0.5f;
-    a.w_up          = wpu;
-    a.b_up          = bpu;
-    a.x             = x;
-    a.sparse_idx    = nullptr;
-    int rc          = spif_launch_ffn(a, SPIF_MODE_GEMV, nullptr, h1, nullptr, 0, ctx);
+    const int fl = flags & SPIF_FLAG_CPU_ROUNDING;
+    int       rc = dense_gemv(ptype, DG_EPI_RELU, wpu, bpu, x, h1, nullptr, r, n_embd, n_tok, fl, ctx);
     if (rc) {
         return rc;
     }
-
-    PredDownParams p = {};
-    p.wpd            = (const unsigned char *) wpd;
-    p.bpd            = bpd;
-    p.h1             = h1;
-    p.out            = sparse_idx_out;
-    p.logits         = logits_out;
-    p.n_ff           = n_ff;
-    p.r              = r;
-    p.row_bytes      = r * 2;
-    p.flags          = flags;
-    const int    Vr  = r / 8;
-    const int    vl  = Vr <= 32 ? 1 : (Vr <= 64 ? 2 : (Vr <= 128 ? 4 : 8));
-    const size_t smem = (size_t) PD_STAGES * PD_ROWS * p.row_bytes + 16 * PD_STAGES + 64;
-    const dim3   grid(ctx.sm_count, n_tok);
-    return (ptype == SPIF_TYPE_F16) ? launch_pd_v<spif_f16>(vl, p, grid, smem, ctx.stream, ctx.device) :
-                                      launch_pd_v<spif_bf16>(vl, p, grid, smem, ctx.stream, ctx.device);
+    return dense_gemv(ptype, DG_EPI_SIGMOID, wpd, bpd, h1, sparse_idx_out, logits_out, n_ff, r, n_tok, fl, ctx);
 }

@@ -53,6 +53,9 @@ def parse_args():
     ap.add_argument("--cpu-layers", type=int, default=4, help="layers in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
+    ap.add_argument("--schedule", default="two-streams", choices=["serial", "two-streams"],
+                    help="serial: the reference's node order on one stream; two-streams: predictor chain || FFN chain")
+    ap.add_argument("--no-early-mask", action="store_true", help="do not use SPIF_FLAG_MASK_STABLE")
     return ap.parse_args()
 
 
@@ -206,7 +209,8 @@ def run_ours(a):
         A_pool.append(s[:, 0].astype(np.int64))
         Z_pool.append(s[:, 1].astype(np.int64))
     launches_per_step = st.launches_per_step
-    g_step = st.capture()
+    st.early_mask = not a.no_early_mask
+    g_step = st.capture(st.step_two_streams if a.schedule == "two-streams" else st.step_eager)
     g_ffn = st.capture(st.ffn_only_eager)
     g_pred = st.capture(st.predict_only_eager)
 
@@ -285,7 +289,7 @@ def run_ours(a):
                    "nonzero_hidden_per_layer": Z_mean * world if world > 1 else Z_mean,
                    "sharding": f"neuron groups of {GROUP} over {world} GPU(s), one allreduce of y per layer"
                    if world > 1 else "all neurons resident on 1 GPU",
-                   "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
+                   "schedule": a.schedule, "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
                          ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool},
         "e2e": {"value": 1e3 / (ms_e2e / a.steps), "unit": "tok/s", "h2d_bytes_per_step": 4 * L * E,
                 "d2h_bytes_per_step": 4 * L * E},

@@ -58,6 +58,12 @@ enum spif_flags {
     /* accumulate the down projection with float atomics (fast, run-to-run unstable, like axpy-sparse.cu:84).
      * Default is the deterministic two-level reduction. */
     SPIF_FLAG_ATOMIC_DOWN  = 1 << 2,
+    /* Caller's promise (spif_sparse_ffn only): sparse_idx was produced at least TWO kernel launches before this call on
+     * `stream` (or is otherwise known to be complete), as in the reference's look-ahead order where the mask of layer l
+     * is predicted one whole layer earlier (src/llama-graph.cpp:939-946).  The kernel then scans the mask and starts
+     * streaming weight rows BEFORE its programmatic-dependent-launch wait, i.e. under the tail of the previous kernel;
+     * only x, y and the workspace wait.  Without the flag everything waits (always safe). */
+    SPIF_FLAG_MASK_STABLE  = 1 << 3,
 };
 
 enum spif_error {

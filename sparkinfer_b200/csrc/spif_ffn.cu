@@ -272,8 +272,12 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
         mbar_fence_init();
     }
     SPIF_STAMP(0);
-    // everything above overlaps the previous kernel's tail under programmatic dependent launch
-    pdl_wait_prior_grid();
+    // everything above overlaps the previous kernel's tail under programmatic dependent launch; with
+    // SPIF_FLAG_MASK_STABLE so do the mask scan and the first ring-fill of weight rows (only x has to wait)
+    const bool early = (p.flags & SPIF_FLAG_MASK_STABLE) != 0 && MODE == SPIF_MODE_FUSED;  // the single ops write dst early
+    if (!early) {
+        pdl_wait_prior_grid();
+    }
     SPIF_STAMP(1);
 
     const float * mask  = p.mask + (size_t) tok * p.mask_len;
@@ -283,7 +287,6 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
 
     build_my_list<MODE, WT>(p, mask, hid, dense, warp_cnt, list_row, list_neu, list_alpha, s_counts);  // ends with __syncthreads
     const int my_count = s_counts[0];
-    pdl_launch_dependents();
     SPIF_STAMP(2);
 
     if (warp == nwc) {
@@ -314,6 +317,10 @@ __global__ void __launch_bounds__(SPIF_MAX_WARPS * 32, 1) spif_ffn_kernel(const 
     if (warp > nwc) {
         return;
     }
+    if (early) {
+        pdl_wait_prior_grid();  // x, y and the partials workspace belong to the previous kernels until here
+    }
+    pdl_launch_dependents();    // always after this CTA's wait: keeps "my start => my predecessor's predecessor is done"
 
     // ================= consumer warps =================
     const int ctid = tid;  // consumer thread id == tid (< nc)
@@ -725,7 +732,14 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
     const size_t stage_b    = (size_t) nmat * kp.row_bytes;
     const size_t fixed      = (size_t) 8 * (2 * 8 + 2 * 16) + 4 * 16 + sizeof(float) * 2 * 16 * SPIF_NB * 2 + sizeof(int) * (32 + 4) +
                          (size_t) 12 * kp.list_cap + 256;
-    const size_t budget = ((size_t) ctx.max_smem_optin - 1024) / k_ctas_per_sm - (k_ctas_per_sm > 1 ? 1024 : 0);
+    // Half of the SM's shared memory per CTA (SPIF_SMEM_SPLIT, default 2): the NEXT layer's CTA can then be co-resident
+    // and fill its ring under this layer's tail (SPIF_FLAG_MASK_STABLE), and the register-only predictor kernel fits too.
+    static const int k_split = [] { const char * e = getenv("SPIF_SMEM_SPLIT"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 2 ? 2 : v); }();
+    const int        n_share = k_ctas_per_sm > k_split ? k_ctas_per_sm : k_split;
+    size_t           budget  = ((size_t) ctx.max_smem_optin - 1024) / n_share - (n_share > 1 ? 1024 : 0);
+    if (budget < fixed + 2 * stage_b + (mode == SPIF_MODE_FUSED ? 2 * (size_t) kp.row_bytes : 0) + 1) {
+        budget = (size_t) ctx.max_smem_optin - 1024;  // rows too long to share the SM: take all of it
+    }
     SPIF_REQUIRE(budget > fixed + 2 * stage_b + (mode == SPIF_MODE_FUSED ? 2 * (size_t) kp.row_bytes : 0), SPIF_E_SHAPE);
     const size_t ring_budget = budget - fixed;
     int          S, D = 0;

@@ -44,17 +44,22 @@ class FfnStack:
         self.stats = torch.zeros((self.L, n_tok, 4), dtype=torch.int32, device=device)
         self.graph = None
         self.launches_per_step = 0
+        self.early_mask = True
+        self._side = torch.cuda.Stream(device=device)
+        # the predictor's hidden vector lives in the workspace: a predictor running concurrently with an FFN needs its own
+        self.ws_pred = ops.Workspace(n_embd, n_ff_local, n_tok, device)
 
     # -- single pieces ------------------------------------------------------------------------------------------
     def predict(self, l, x_from):
         w = self.layers[l]
         ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
-                      flags=self.flags, ws=self.ws, out=self.p[l])
+                      flags=self.flags, ws=self.ws_pred, out=self.p[l])
         return 2  # kernels: predictor up GEMV, predictor down GEMV+sigmoid
 
-    def ffn(self, l, want_stats=False):
+    def ffn(self, l, want_stats=False, mask_stable=False):
         w = self.layers[l]
-        ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=self.flags,
+        fl = self.flags | (ops.FLAG_MASK_STABLE if mask_stable else 0)
+        ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=fl,
                        ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None)
         return 2  # kernels: fused gate/up/act/down, partial reduction
 
@@ -68,8 +73,36 @@ class FfnStack:
         for l in range(self.L):
             if l + 1 < self.L:
                 n += self.predict(l + 1, l)  # look-ahead, llama-graph.cpp:939-946
-            n += self.ffn(l, want_stats)
+            # the mask of layer l was written >= 2 launches ago (the look-ahead predictor of l+1 sits in between)
+            n += self.ffn(l, want_stats, mask_stable=(l + 1 < self.L) and self.early_mask)
             self.allreduce(l)
+        self.launches_per_step = n
+        return n
+
+    def step_two_streams(self):
+        """same work as step_eager, issued as two chains that only meet where the data does: the predictor chain
+        (needs x only) runs on a side stream, FFN l waits for the event of predictor l.  Captured into one CUDA graph
+        the two chains become parallel branches and share the SMs (the predictor kernel is register-light and uses no
+        shared memory so that it fits next to the FFN kernel's TMA ring)."""
+        main = torch.cuda.current_stream()
+        side = self._side
+        side.wait_stream(main)
+        evs = []
+        with torch.cuda.stream(side):
+            n = self.predict(0, 0)
+            e = torch.cuda.Event()
+            e.record(side)
+            evs.append(e)
+            for l in range(self.L - 1):
+                n += self.predict(l + 1, l)
+                e = torch.cuda.Event()
+                e.record(side)
+                evs.append(e)
+        for l in range(self.L):
+            main.wait_event(evs[l])
+            n += self.ffn(l, False, mask_stable=self.early_mask)  # full edge from predictor l: the mask is complete
+            self.allreduce(l)
+        main.wait_stream(side)
         self.launches_per_step = n
         return n
 
@@ -77,7 +110,7 @@ class FfnStack:
         """the sparse FFNs alone, masks as left in self.p by the last full step"""
         n = 0
         for l in range(self.L):
-            n += self.ffn(l, want_stats)
+            n += self.ffn(l, want_stats, mask_stable=self.early_mask)
         return n
 
     def predict_only_eager(self):

@@ -114,3 +114,73 @@ def test_predictor(oracle, ptype, n_embd, r, n_ff, n_tok):
     # north_star: flips are only allowed where |logit - threshold| < 1e-4 (threshold 0.5 on the sigmoid <=> logit 0)
     assert np.all(np.abs(z_ref[flips]) < 1e-4), f"{flips.sum()} flips, worst |logit| {np.abs(z_ref[flips]).max()}"
     assert np.abs(p_gpu - p_ref).max() < 1e-5
+
+
+# ---- quantised weights (Q8_0 pinned by the reference CPU ops; Q4_0 gate/up pinned, Q4_0 down axpy UNPINNED: the
+# reference aborts for it, ggml-cpu.c:2225-2226, so the oracle restates it by analogy with the Q8_0 axpy)
+QSHAPES = [(512, 1024, 1), (4096, 1536, 1), (5120, 1408, 1), (512, 1024, 3), (8192, 640, 2), (256, 96, 1)]
+# SPIF_FLAG_CPU_ROUNDING: x is quantised exactly like the CPU backend (id = 127/amax, round-half-even), the integer dots
+# are exact, only the FP32 summation order differs.  Default: the CUDA reference's quantiser (roundf(x/d), quantize.cu).
+TOL_Q_CPU = 3e-5
+TOL_Q_DEFAULT = 5e-3
+
+
+@pytest.mark.parametrize("wtype", [Q8_0, Q4_0])
+@pytest.mark.parametrize("n_embd,n_ff,n_tok", QSHAPES)
+def test_quant_single_ops(oracle, wtype, n_embd, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + 3 * n_embd + n_ff + wtype
+    Wu, _, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qd = oracle.quantize(wtype, Wu), oracle.quantize(wtype, Wd)
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, 0.15, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    ref_u = oracle.mul_mat_sparse(wtype, qu, x, p, n_embd, n_ff)
+    hid = (ref_u * np.random.default_rng(seed + 3).normal(0, 1, ref_u.shape)).astype(np.float32)
+    hid[:, ::7] = 0.0
+    ref_y = oracle.axpy_sparse(wtype, qd, hid, p, n_embd, n_ff)
+    for flags, tol in ((sp.FLAG_CPU_ROUNDING, TOL_Q_CPU), (0, TOL_Q_DEFAULT)):
+        got_u = sp.mul_mat_sparse(dev(qu), wtype, dev(x), dev(p), flags=flags, ws=ws).cpu().numpy()
+        assert rel_err(got_u, ref_u) < tol, (TYPE_NAMES[wtype], flags, rel_err(got_u, ref_u))
+        assert np.all(got_u[p < 0.5] == 0.0)
+        got_y = sp.axpy_sparse(dev(qd), wtype, dev(hid), dev(p), n_embd=n_embd, flags=flags, ws=ws).cpu().numpy()
+        assert rel_err(got_y, ref_y) < TOL_Q_CPU, (TYPE_NAMES[wtype], flags, rel_err(got_y, ref_y))  # alpha stays F32
+
+
+@pytest.mark.parametrize("arch", [ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP])
+@pytest.mark.parametrize("wtype", [Q8_0, Q4_0])
+@pytest.mark.parametrize("n_embd,n_ff,n_tok", QSHAPES[:5])
+def test_quant_sparse_ffn_fused(oracle, arch, wtype, n_embd, n_ff, n_tok):
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + 11 * n_embd + n_ff + arch + wtype
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(wtype, w) for w in (Wu, Wg, Wd))
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, 0.12, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    y_ref, _, _, hid_ref = oracle.sparse_ffn(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)
+    y64, _ = oracle.sparse_ffn_f64(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)
+    gate = None if arch == ARCH_RELU_UP else dev(qg)
+    for flags, tol in ((sp.FLAG_CPU_ROUNDING, 2e-4), (0, TOL_DEFAULT[wtype])):
+        y, hid, stats = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, flags=flags,
+                                      want_hidden=True, want_stats=True, ws=ws)
+        y, hid, stats = y.cpu().numpy(), hid.cpu().numpy(), stats.cpu().numpy()
+        # a gate value within rounding of the 0.01 / 0 activation threshold may land on the other side: compare y
+        # with the oracle, and bound it by the format's own error against the FP64 restatement on the same weights
+        assert rel_err(y, y_ref) < tol, (TYPE_NAMES[wtype], arch, flags, rel_err(y, y_ref))
+        assert rel_err(y, y64.astype(np.float32)) < TOL_DEFAULT[wtype]
+        act = ~(p < 0.5)
+        assert np.array_equal(stats[:, 0], act.sum(axis=1))
+    y1 = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, ws=ws)
+    y2 = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, ws=ws)
+    assert torch.equal(y1, y2)
+
+
+def test_quant_rejects_unaligned_rows(oracle):
+    """Q8_0/Q4_0 rows must be 16-byte multiples for the TMA ring (n_embd % 256 == 0): a clean error, no fallback"""
+    import sparkinfer_b200 as sp
+    from sparkinfer_b200._lib import SpifError
+    n_embd, n_ff = 1376, 256
+    qu = oracle.quantize(Q8_0, synth.ffn_weights(n_embd, n_ff, 1, nmat=1)[0])
+    with pytest.raises(SpifError):
+        sp.mul_mat_sparse(dev(qu), Q8_0, dev(synth.activations(n_embd, 1, 2)), dev(synth.direct_mask(n_ff, 1, 0.2, 3)))

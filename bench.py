@@ -168,6 +168,11 @@ def build_stack(a, wl, rank, world, device):
     return st, expect
 
 
+def log(msg):
+    if os.environ.get("SPIF_BENCH_VERBOSE"):
+        print(f"[bench rank {os.environ.get('RANK', '0')} t={time.time() % 1000:.1f}] {msg}", file=sys.stderr, flush=True)
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -185,7 +190,9 @@ def run_ours(a):
 
     wl = WORKLOADS[a.workload]
     E, F, L, R = wl["n_embd"], wl["n_ff"], wl["n_layer"], a.rank
+    log('init done')
     st, expect = build_stack(a, wl, rank, world, device)
+    log('stack built')
     row_bytes = 2 * E
 
     # x pool: identical on all ranks (x is replicated), pinned on the host for the e2e leg
@@ -209,8 +216,10 @@ def run_ours(a):
         A_pool.append(s[:, 0].astype(np.int64))
         Z_pool.append(s[:, 1].astype(np.int64))
     launches_per_step = st.launches_per_step
+    log('eager warm-up done')
     st.early_mask = not a.no_early_mask
     g_step = st.capture(st.step_two_streams if a.schedule == "two-streams" else st.step_eager)
+    log('step graph captured')
     g_ffn = st.capture(st.ffn_only_eager)
     g_pred = st.capture(st.predict_only_eager)
 
@@ -241,11 +250,14 @@ def run_ours(a):
         y_host.copy_(st.y, non_blocking=True)
         torch.cuda.current_stream().synchronize()   # a decode step's result is needed on the host before the next
 
+    log('all graphs captured')
     sampler = ClockSampler(physical_gpu_index(local))
     sampler.start()
     ms_value = timed(step_resident, a.steps, max(a.warmup, 3))
     clocks = sampler.stop()
+    log('value leg done')
     ms_e2e = timed(step_e2e, a.steps, max(a.warmup, 3))
+    log('e2e leg done')
 
     # ---- roofline leg: the sparse FFNs alone (fused kernel + fixed-order partial reduction per layer), masks of pool[0]
     st.x.copy_(x_pool[0])

@@ -283,9 +283,18 @@ def run_ours(a):
     except Exception:
         pass
 
-    if rank != 0:
+    def leave():
+        # NCCL communicators that were captured into CUDA graphs can hang in destroy_process_group / interpreter
+        # teardown: synchronise, flush, and leave without running destructors
         if world > 1:
-            dist.destroy_process_group()
+            del_graphs = (g_step, g_ffn, g_pred)  # noqa: F841 (keep alive until the barrier has passed)
+            barrier()
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
+
+    if rank != 0:
+        leave()
         return
     ms_step = ms_value / a.steps
     A_mean = float(np.mean([x.mean() for x in A_pool]))
@@ -319,8 +328,7 @@ def run_ours(a):
     if world == 1 and not a.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(a, wl, iters=8, warmup=2)
     print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    leave()
 
 
 # ---------------------------------------------------------------------------------------------------------------------

@@ -64,6 +64,9 @@ enum spif_flags {
      * streaming weight rows BEFORE its programmatic-dependent-launch wait, i.e. under the tail of the previous kernel;
      * only x, y and the workspace wait.  Without the flag everything waits (always safe). */
     SPIF_FLAG_MASK_STABLE  = 1 << 3,
+    /* spif_sparse_ffn with n_tok >= 2: keep the reference's per-(row, token) schedule (mm-sparse.cu:107-210: every token
+     * re-streams its active rows) instead of the default union-of-masks gathered GEMM on tensor cores. */
+    SPIF_FLAG_PER_TOKEN    = 1 << 4,
 };
 
 enum spif_error {

@@ -7,6 +7,8 @@
 
 int spif_launch_ffn_q(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,
                       size_t ws_bytes, const spif_launch_ctx & ctx);
+int    spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx);
+size_t spif_batch_workspace_bytes(int n_embd, int n_ff, int n_tok);
 
 static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
     int dev = 0;
@@ -107,6 +109,8 @@ size_t spif_workspace_size(int n_embd, int n_ff, int n_tok) {
     need += sizeof(float) * (size_t) n_tok * 2048;                    // predictor hidden (r <= 2048)
     need += (size_t) n_tok * ((size_t) n_embd / 32 * 40 + 64);        // quantised activations
     need += (size_t) n_tok * (size_t) n_ff * 4;                       // spare dense vector
+    const size_t batch = spif_batch_workspace_bytes(n_embd, n_ff, n_tok);  // union-of-masks GEMM path (n_tok >= 2)
+    need = need > batch ? need : batch;
     return (need + 4095) & ~(size_t) 4095;
 }
 
@@ -262,6 +266,13 @@ int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif
     rc = make_ctx(ctx, stream);
     if (rc) {
         return rc;
+    }
+    if (a.n_tok >= 2 && !(a.flags & SPIF_FLAG_PER_TOKEN)) {
+        // batched / prefill: union of the per-token masks -> gathered GEMM on tensor cores, each row read once
+        rc = spif_launch_ffn_batch(a, ws, ws_bytes, ctx);
+        if (rc != SPIF_E_UNSUPPORTED) {
+            return rc;
+        }
     }
     return is_float_type(a.type) ? spif_launch_ffn(a, SPIF_MODE_FUSED, nullptr, nullptr, ws, ws_bytes, ctx) :
                                    spif_launch_ffn_q(a, SPIF_MODE_FUSED, nullptr, nullptr, ws, ws_bytes, ctx);

@@ -206,7 +206,8 @@ int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_
     if (mode == SPIF_MODE_FUSED) {
         // roughly half of the ring for gate/up stages (enough bytes in flight to cover HBM latency), the rest for down
         // rows so that their fetch never has to wait for a slot at ~10% activity
-        S = (int) ((ring_budget * 45 / 100) / stage_b);
+        static const int k_gu_pct = [] { const char * e = getenv("SPIF_GU_PCT"); int v = e ? atoi(e) : 45; return v < 10 ? 10 : (v > 90 ? 90 : v); }();
+        S = (int) ((ring_budget * k_gu_pct / 100) / stage_b);
         S = S < 2 ? 2 : (S > k_max_stages ? k_max_stages : S);
         D = (int) ((ring_budget - (size_t) S * stage_b) / kp.row_bytes);
         D = D > 16 ? 16 : D;

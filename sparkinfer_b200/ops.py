@@ -22,7 +22,7 @@ from ._lib import FfnArgs, check
 
 GGML_TYPE_F32, GGML_TYPE_F16, GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_BF16 = 0, 1, 2, 8, 30
 ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
-FLAG_CPU_ROUNDING, FLAG_MASK_BY_ROW, FLAG_ATOMIC_DOWN, FLAG_MASK_STABLE = 1, 2, 4, 8
+FLAG_CPU_ROUNDING, FLAG_MASK_BY_ROW, FLAG_ATOMIC_DOWN, FLAG_MASK_STABLE, FLAG_PER_TOKEN = 1, 2, 4, 8, 16
 SPARSE_THRESHOLD = 0.5  # SPIF_SPARSE_THRESHOLD, mm-sparse.cu:5-7
 
 

@@ -8,12 +8,14 @@
 //   gate/up: CTA c owns a contiguous slice of the union; D[128 rows x T] = W[rows,:] . X^T with tcgen05.mma
 //            (A = gathered weight rows, K-major, cp.async into SWIZZLE_128B tiles; B = X; accumulators in TMEM),
 //            epilogue applies the per-token mask bits + bias + activation and writes H[t][slot] (weight float type)
-//   down   : Y[T x n_embd] = H . Wdown^T[union rows, :] as a stream-K GEMM over (128-column tile, 128-row chunk) items;
-//            A = gathered 256-byte row segments of W_down^T (MN-major operand), B = H (K-major); each CTA accumulates a
+//   down   : Y[T x n_embd] = H . Wdown^T[union rows, :] as a stream-K GEMM over (512-column tile, 64-row chunk) items;
+//            A = gathered 1 KB row segments of W_down^T (MN-major operand), B = H (K-major); each CTA accumulates a
 //            contiguous item range in TMEM and writes <= 2 partial tiles, summed in a fixed order by the last kernel.
 // x and the hidden values are rounded to the weight float type (what the reference CPU backend does: ggml-cpu.c:1832-1856,
 // 2196-2207); accumulation is FP32 in tensor memory.
 #include "spif_batch.cuh"
+
+#include <cstdlib>
 
 #define SPIF_B_ROWS_MAX 1024 /* union rows one CTA may own (m <= 1024 * SMs) */
 
@@ -36,11 +38,12 @@ struct BatchParams {
     int32_t *  union_count;  // [4]: {U, rows with a non-zero hidden value, 0, 0}
     uint16_t * xh;           // [TP][n_embd]
     uint16_t * hh;           // [TP][m_pad]
-    float *    part;         // [P][2][TP][128]
+    float *    part;         // [P][2][TP][512]
     int        n_embd, n_ff, m, m_pad, mask_len, n_tok;
     int        row_bytes;
     int        arch, gated, by_row;
     float      thr;
+    int        debug;  // timing experiments only (SPIF_BATCH_DEBUG): 1 = no MMAs, 2 = no weight loads
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -48,6 +51,8 @@ struct BatchParams {
 template <typename WT>
 __global__ void __launch_bounds__(256) spif_batch_bits_kernel(const BatchParams p, int nb_bits, int TP) {
     const int tid = threadIdx.x;
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
     if ((int) blockIdx.x < nb_bits) {
         const int row = blockIdx.x * 256 + tid;
         if (row < p.m) {
@@ -78,17 +83,35 @@ __global__ void __launch_bounds__(256) spif_batch_bits_kernel(const BatchParams 
     }
 }
 
-// prep 2: union list (one CTA; warps own contiguous row chunks, two passes of ballot + popc -> ascending order)
+// prep 2: union list (one CTA).  Warp w owns a contiguous row chunk; a lane keeps the ballots of up to 32 iterations in
+// registers (all loads in flight at once), so the list comes out ascending after ONE pass + a cross-warp prefix.
 __global__ void __launch_bounds__(1024) spif_batch_union_kernel(const BatchParams p) {
     __shared__ int warp_cnt[32];
     const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
     const int      chunk = ((p.m + nwarp * 32 - 1) / (nwarp * 32)) * 32;
     const int      r0 = warp * chunk, r1 = min(r0 + chunk, p.m);
-    int            cnt = 0;
-    for (int base = r0; base < r1; base += 32) {
-        const int  row = base + lane;
-        const bool a   = (row < r1) && (p.bits[row] != 0u);
-        cnt += __popc(__ballot_sync(0xffffffffu, a));
+    const int      n_it = chunk >> 5;
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
+    unsigned ball[32];
+    int      cnt = 0;
+    if (n_it <= 32) {
+        uint32_t v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            const int row = r0 + i * 32 + lane;
+            v[i]          = (i < n_it && row < r1) ? p.bits[row] : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            ball[i] = __ballot_sync(0xffffffffu, v[i] != 0u);
+            cnt += __popc(ball[i]);
+        }
+    } else {
+        for (int base = r0; base < r1; base += 32) {
+            const int row = base + lane;
+            cnt += __popc(__ballot_sync(0xffffffffu, (row < r1) && (p.bits[row] != 0u)));
+        }
     }
     if (lane == 0) {
         warp_cnt[warp] = cnt;
@@ -101,14 +124,24 @@ __global__ void __launch_bounds__(1024) spif_batch_union_kernel(const BatchParam
         total += v;
     }
     int run = before;
-    for (int base = r0; base < r1; base += 32) {
-        const int      row  = base + lane;
-        const bool     a    = (row < r1) && (p.bits[row] != 0u);
-        const unsigned ball = __ballot_sync(0xffffffffu, a);
-        if (a) {
-            p.union_idx[run + __popc(ball & ((1u << lane) - 1u))] = row;
+    if (n_it <= 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if (ball[i] & (1u << lane)) {
+                p.union_idx[run + __popc(ball[i] & ((1u << lane) - 1u))] = r0 + i * 32 + lane;
+            }
+            run += __popc(ball[i]);
         }
-        run += __popc(ball);
+    } else {
+        for (int base = r0; base < r1; base += 32) {
+            const int      row = base + lane;
+            const bool     a   = (row < r1) && (p.bits[row] != 0u);
+            const unsigned b   = __ballot_sync(0xffffffffu, a);
+            if (a) {
+                p.union_idx[run + __popc(b & ((1u << lane) - 1u))] = row;
+            }
+            run += __popc(b);
+        }
     }
     if (tid == 0) {
         p.union_count[0] = total;
@@ -120,14 +153,22 @@ __global__ void __launch_bounds__(1024) spif_batch_union_kernel(const BatchParam
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// gate/up gathered GEMM.  160 threads: warps 0-3 = cp.async producers, then epilogue; warp 4 = TMEM owner + MMA issuer.
-// Stage = [up tile 128 rows x 128 B][gate tile][x tile TP rows x 128 B], K block = 64 elements, SWIZZLE_128B K-major.
-#define K1_NST   5
-#define K1_LAG   3
-#define K1_ATILE 16384
-#define K1_STAGE (2 * K1_ATILE + 4096)
-#define K1_TAIL  (256 + 4 * SPIF_B_ROWS_MAX)
-#define K1_SMEM  (K1_NST * K1_STAGE + K1_TAIL + 1024)
+// gate/up gathered GEMM.  160 threads: warps 0-3 = cp.async producers (warps 0-1 also run the epilogue); warp 4 = TMEM
+// owner + MMA issuer.  K block = 64 elements (one 128-byte swizzle row).  A stage holds
+//   [up tile][gate tile][x tile TP x 128 B]      (K-major SWIZZLE_128B, 8-row atoms of 1 KB)
+// for one K block; a weight tile only occupies ceil(rows / 8) atoms, so a CTA with few rows gets a deep ring (up to 32
+// K blocks in flight).
+// MMA orientation: D[64 tokens x N] = X[64 x 64] . W[N x 64]^T with N = up rows followed by gate rows (the two tiles are
+// adjacent in shared memory, so ONE instruction per K = 16 step covers both matrices).  Measured on B200: a tcgen05.mma
+// with both operands in shared memory costs ~1 cycle per A-operand row whatever N is (M = 128 weight rows x N = 16 tokens:
+// ~135 cycles per instruction, 8 per K block -> the kernel was MMA-issue bound at 45 us); with the tokens as the (M = 64)
+// A operand the weight rows ride in the cheap N dimension.  Rows 32..63 of the x tile are whatever follows it in shared
+// memory: they only produce accumulator lanes nobody reads (K1_SLACK keeps those reads inside the allocation).
+#define K1_MAXST 32
+#define K1_RING  (190 * 1024)
+#define K1_SLACK (16 * 1024)
+#define K1_TAIL  (1024 + 4 * SPIF_B_ROWS_MAX + 2 * 128 * 16 + 256)
+#define K1_SMEM  (K1_RING + K1_SLACK + K1_TAIL + 1024)
 
 template <typename WT, int TP>
 __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchParams p) {
@@ -137,13 +178,34 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
     const uint32_t raw0  = smem_u32(smem_raw);
     const uint32_t sbase = (raw0 + 1023u) & ~1023u;
     unsigned char * sm   = smem_raw + (sbase - raw0);
-    unsigned char * tail = sm + K1_NST * K1_STAGE;
+    unsigned char * tail = sm + K1_RING + K1_SLACK;
     uint64_t *      full       = reinterpret_cast<uint64_t *>(tail);
-    uint64_t *      empty      = full + K1_NST;
-    uint64_t *      accum_full = empty + K1_NST;
+    uint64_t *      empty      = full + K1_MAXST;
+    uint64_t *      accum_full = empty + K1_MAXST;
     uint64_t *      tmem_empty = accum_full + 1;
     uint32_t *      tmem_slot  = reinterpret_cast<uint32_t *>(tmem_empty + 1);
-    int *           s_rows     = reinterpret_cast<int *>(tail + 256);
+    int *           s_rows     = reinterpret_cast<int *>(tail + 1024);
+    // per-tile row metadata for the epilogue, double-buffered by tile parity: [2][128] x {bits, neuron, b_up, b_gate}
+    uint32_t *      s_bits     = reinterpret_cast<uint32_t *>(tail + 1024 + 4 * SPIF_B_ROWS_MAX);
+    int *           s_neu      = reinterpret_cast<int *>(s_bits + 256);
+    float *         s_bu       = reinterpret_cast<float *>(s_neu + 256);
+    float *         s_bg       = s_bu + 256;
+    uint32_t *      s_nz       = reinterpret_cast<uint32_t *>(s_bg + 256);  // [2 warps][8 chunks] rows with a non-zero hidden
+
+    if (tid == 0) {
+        for (int s = 0; s < K1_MAXST; ++s) {
+            mbar_init(&full[s], 128);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(accum_full, 1);
+        mbar_init(tmem_empty, 64);
+        mbar_fence_init();
+    }
+    if (warp == 4) {
+        tmem_alloc(tmem_slot, 256);
+    }
+    pdl_wait_prior_grid();  // union list, bits, xh
+    pdl_launch_dependents();
 
     const int U   = p.union_count[0];
     const int q   = (U + P - 1) / P;
@@ -152,158 +214,158 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
     if (c == 0 && tid < p.n_tok && p.stats_out) {
         p.stats_out[tid * 4 + 2] = U;
     }
-    if (cnt == 0) {
-        return;
-    }
     for (int i = tid; i < cnt; i += blockDim.x) {
         s_rows[i] = p.union_idx[s0 + i];
     }
-    if (tid == 0) {
-        for (int s = 0; s < K1_NST; ++s) {
-            mbar_init(&full[s], 128);
-            mbar_init(&empty[s], 1);
+    if (cnt > 0 && s0 + cnt == U) {
+        // owner of the last slice: slots U .. roundup(U, 8) feed the down GEMM's 16-byte H chunks and must be finite
+        const int pad = ((U + 7) & ~7) - U;
+        for (int i = tid; i < pad * TP; i += blockDim.x) {
+            p.hh[(size_t) (i / pad) * p.m_pad + U + (i % pad)] = 0;
         }
-        mbar_init(accum_full, 1);
-        mbar_init(tmem_empty, 128);
-        mbar_fence_init();
-    }
-    if (warp == 4) {
-        tmem_alloc(tmem_slot, 64);
     }
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int  KB      = p.n_embd >> 6;
-    const int  n_tiles = (cnt + 127) >> 7;
-    const bool gated   = p.gated != 0;
+    const int      KB      = p.n_embd >> 6;
+    const int      n_tiles = (cnt + 127) >> 7;
+    const bool     gated   = p.gated != 0;
+    const int      R8      = (min(cnt, 128) + 7) >> 3;          // 8-row atoms per weight tile
+    const uint32_t a_bytes = (uint32_t) R8 * 1024u;
+    const uint32_t x_off   = a_bytes * (gated ? 2u : 1u);
+    const uint32_t stage_b = x_off + TP * 128;
+    const uint32_t NST     = min((uint32_t) K1_MAXST, (uint32_t) K1_RING / stage_b);
+    const int      ncol_up = R8 * 8;                            // accumulator columns: [up rows][gate rows]
 
-    if (warp < 4) {
+    if (cnt > 0 && warp < 4) {
         const int cc = tid & 7, rsub = tid >> 3;
-        uint32_t  it = 0;
+        uint32_t  st = 0, lap = 0;
         for (int tile = 0; tile < n_tiles; ++tile) {
             const int cnt_t = min(128, cnt - tile * 128);
-            int       rows[8];
+            const int buf   = (tile & 1) * 128;
+            if (tid < cnt_t) {
+                const int row    = s_rows[tile * 128 + tid];
+                const int neu    = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
+                s_bits[buf + tid] = p.bits[row];
+                s_neu[buf + tid]  = neu;
+                s_bu[buf + tid]   = p.b_up ? __ldg(p.b_up + neu) : 0.f;
+                s_bg[buf + tid]   = (gated && p.b_gate) ? __ldg(p.b_gate + neu) : 0.f;
+            }
+            named_bar_sync(1, 128);
+            int rows[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int r = rsub + 16 * j;
                 rows[j]     = (r < cnt_t) ? s_rows[tile * 128 + r] : -1;
             }
-            for (int kb = 0; kb < KB; ++kb, ++it) {
-                const uint32_t st = it % K1_NST;
-                if (it >= K1_NST) {
-                    mbar_wait(&empty[st], ((it / K1_NST) - 1u) & 1u);
+            // CTAs walk K in rotated order so that they do not all read the same slice of x at the same moment
+            int kb = (int) (((unsigned) c * 29u) % (unsigned) KB);
+            for (int ki = 0; ki < KB; ++ki, kb = (kb + 1 == KB) ? 0 : kb + 1) {
+                if (lap > 0) {
+                    mbar_wait(&empty[st], (lap - 1u) & 1u);
                 }
-                const uint32_t sA = sbase + st * K1_STAGE;
+                const uint32_t sA = sbase + st * stage_b;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    if (rows[j] >= 0) {
+                    if (rows[j] >= 0 && p.debug != 2) {
                         const uint32_t off = swz_kmajor(rsub + 16 * j, cc);
                         const size_t   go  = (size_t) rows[j] * p.row_bytes + (size_t) kb * 128 + cc * 16;
                         cp_async16(sA + off, p.w_up + go);
                         if (gated) {
-                            cp_async16(sA + K1_ATILE + off, p.w_gate + go);
+                            cp_async16(sA + a_bytes + off, p.w_gate + go);
                         }
                     }
                 }
 #pragma unroll
                 for (int h = 0; h < TP * 8 / 128; ++h) {
                     const int idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
-                    cp_async16(sA + 2 * K1_ATILE + swz_kmajor(t, c8), p.xh + (size_t) t * p.n_embd + kb * 64 + c8 * 8);
+                    cp_async16(sA + x_off + swz_kmajor(t, c8), p.xh + (size_t) t * p.n_embd + kb * 64 + c8 * 8);
                 }
-                cp_async_commit();
-                if (kb >= K1_LAG) {
-                    cp_async_wait<K1_LAG>();
-                    fence_proxy_async_smem();
-                    mbar_arrive(&full[(it - K1_LAG) % K1_NST]);
+                cp_async_mbar_arrive_noinc(&full[st]);
+                if (++st == NST) {
+                    st = 0;
+                    ++lap;
                 }
             }
-            cp_async_wait<0>();
-            fence_proxy_async_smem();
-            for (int d = min(K1_LAG, KB); d >= 1; --d) {
-                mbar_arrive(&full[(it - d) % K1_NST]);
+            if (warp >= 2) {
+                continue;
             }
-
-            // ---- epilogue of this tile: TMEM -> registers -> mask bits, bias, activation -> H
+            // ---- epilogue (warps 0-1): token t lives in TMEM lane (t % 16) + 32 * (t / 16); thread = token, loop over rows
             mbar_wait(accum_full, tile & 1);
             tc_fence_after_sync();
-            float          up[TP], gt[TP];
-            const uint32_t taddr = tmem_base + ((uint32_t) (warp * 32) << 16);
-#pragma unroll
-            for (int h = 0; h < TP / 16; ++h) {
-                tmem_ld16(taddr + h * 16, *reinterpret_cast<float(*)[16]>(up + h * 16));
+            const int      t       = warp * 16 + lane;
+            const bool     tok_ok  = lane < 16 && t < p.n_tok;
+            const uint32_t taddr   = tmem_base + ((uint32_t) (warp * 32) << 16);
+            const int      slot0   = s0 + tile * 128;
+            int            n_act = 0, n_nz = 0;
+            for (int r0 = 0; r0 < cnt_t; r0 += 16) {
+                float up[16], gt[16];
+                tmem_ld16(taddr + r0, up);
                 if (gated) {
-                    tmem_ld16(taddr + TP + h * 16, *reinterpret_cast<float(*)[16]>(gt + h * 16));
+                    tmem_ld16(taddr + ncol_up + r0, gt);
+                }
+                uint32_t nzmask = 0;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const int r = r0 + j;
+                    if (r < cnt_t) {
+                        const bool act = tok_ok && ((s_bits[buf + r] >> t) & 1u);
+                        float      h   = 0.f;
+                        if (act) {
+                            h = spif_activation(p.arch, gated ? gt[j] + s_bg[buf + r] : 0.f, up[j] + s_bu[buf + r]);
+                            if (p.hidden_out) {
+                                p.hidden_out[(size_t) t * p.n_ff + s_neu[buf + r]] = h;
+                            }
+                        }
+                        const uint16_t hb = f32_to_wt_bits<WT>(h);
+                        const bool     nz = (hb & 0x7fffu) != 0;
+                        if (lane < 16 && t < TP) {
+                            p.hh[(size_t) t * p.m_pad + slot0 + r] = hb;
+                        }
+                        n_act += act ? 1 : 0;
+                        n_nz += (act && nz) ? 1 : 0;
+                        nzmask |= nz ? (1u << j) : 0u;
+                    }
+                }
+                nzmask = __reduce_or_sync(0xffffffffu, nzmask);
+                if (lane == 0) {
+                    s_nz[warp * 8 + (r0 >> 4)] = nzmask;
                 }
             }
             tc_fence_before_sync();
             mbar_arrive(tmem_empty);
-            const int  r     = tid;
-            const bool valid = r < cnt_t;
-            const int  row   = valid ? s_rows[tile * 128 + r] : 0;
-            const int  neu   = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
-            const uint32_t bits = valid ? p.bits[row] : 0u;
-            const float    bu   = (valid && p.b_up) ? __ldg(p.b_up + neu) : 0.f;
-            const float    bg   = (valid && gated && p.b_gate) ? __ldg(p.b_gate + neu) : 0.f;
-            const int      slot = s0 + tile * 128 + r;
-            bool           any_nz = false;
-#pragma unroll
-            for (int t = 0; t < TP; ++t) {
-                float      h   = 0.f;
-                const bool act = (t < p.n_tok) && ((bits >> t) & 1u);
-                if (act) {
-                    h = spif_activation(p.arch, gated ? gt[t] + bg : 0.f, up[t] + bu);
-                    if (p.hidden_out) {
-                        p.hidden_out[(size_t) t * p.n_ff + neu] = h;
-                    }
-                }
-                const uint16_t hb = f32_to_wt_bits<WT>(h);
-                const bool     nz = (hb & 0x7fffu) != 0;
-                if (valid) {
-                    p.hh[(size_t) t * p.m_pad + slot] = hb;
-                }
-                any_nz = any_nz || nz;
-                if (p.stats_out && t < p.n_tok) {
-                    const unsigned ba = __ballot_sync(0xffffffffu, act);
-                    const unsigned bz = __ballot_sync(0xffffffffu, act && nz);
-                    if (lane == 0) {
-                        if (ba) {
-                            atomicAdd(p.stats_out + t * 4 + 0, __popc(ba));
-                        }
-                        if (bz) {
-                            atomicAdd(p.stats_out + t * 4 + 1, __popc(bz));
-                        }
-                    }
+            if (p.stats_out && tok_ok) {
+                atomicAdd(p.stats_out + t * 4 + 0, n_act);
+                atomicAdd(p.stats_out + t * 4 + 1, n_nz);
+            }
+            named_bar_sync(2, 64);
+            if (tid < ((cnt_t + 15) >> 4)) {
+                const int z = __popc(s_nz[tid] | s_nz[8 + tid]);
+                if (z) {
+                    atomicAdd(p.union_count + 1, z);
                 }
             }
-            const unsigned bn = __ballot_sync(0xffffffffu, any_nz);
-            if (lane == 0 && bn) {
-                atomicAdd(p.union_count + 1, __popc(bn));
-            }
+            named_bar_sync(2, 64);
         }
-    } else {
-        constexpr uint32_t idesc = umma_idesc_f16(wt_fmt<WT>::id, 0, 0, 128, TP);
-        uint32_t           it    = 0;
+    } else if (cnt > 0) {
+        const uint32_t idesc = umma_idesc_f16(wt_fmt<WT>::id, 0, 0, 64, gated ? 2 * ncol_up : ncol_up);
+        uint32_t       st = 0, lap = 0;
         for (int tile = 0; tile < n_tiles; ++tile) {
             if (tile > 0) {
                 mbar_wait(tmem_empty, (tile - 1) & 1);
                 tc_fence_after_sync();
             }
-            for (int kb = 0; kb < KB; ++kb, ++it) {
-                const uint32_t st = it % K1_NST;
-                mbar_wait(&full[st], (it / K1_NST) & 1u);
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&full[st], lap & 1u);
                 tc_fence_after_sync();
                 if (lane == 0) {
-                    const uint32_t sA = sbase + st * K1_STAGE;
+                    const uint32_t sA = sbase + st * stage_b;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint64_t db  = umma_smem_desc(sA + 2 * K1_ATILE + k * 32, 16, 1024);
-                        const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
-                        umma_f16(tmem_base, umma_smem_desc(sA + k * 32, 16, 1024), db, idesc, acc);
-                        if (gated) {
-                            umma_f16(tmem_base + TP, umma_smem_desc(sA + K1_ATILE + k * 32, 16, 1024), db, idesc, acc);
-                        }
+                    for (int k = 0; k < (p.debug == 1 ? 0 : 4); ++k) {
+                        umma_f16(tmem_base, umma_smem_desc(sA + x_off + k * 32, 16, 1024), umma_smem_desc(sA + k * 32, 16, 1024),
+                                 idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty[st]);
                     if (kb == KB - 1) {
@@ -311,26 +373,29 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                     }
                 }
                 __syncwarp();
+                if (++st == NST) {
+                    st = 0;
+                    ++lap;
+                }
             }
         }
     }
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 4) {
-        tmem_dealloc(tmem_base, 64);
+        tmem_dealloc(tmem_base, 256);
     }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// down projection: stream-K over items (ct = 128-column tile of n_embd, kc = chunk of 128 union rows), item id = ct * n_kc + kc.
-// CTA c owns items [c * ipc, (c + 1) * ipc): at most two column tiles ("segments"), one TMEM accumulator each.
-//   A tile  : W_down^T[union rows of the chunk][256-byte column segment], MN-major SWIZZLE_128B: k-row = 128 B of 64 columns,
-//             8 k-rows per 1024-byte atom, atoms of one 64-column half contiguous along k (SBO 1024), halves LBO = 16 KB apart
-//   B tile  : H[t][128 slots], K-major SWIZZLE_128B, two 64-slot atoms of TP rows
-#define K2_NST   5
-#define K2_LAG   3
-#define K2_ATILE 32768
-#define K2_STAGE (K2_ATILE + 8192)
+// down projection: stream-K over items (ct = 512-column tile of n_embd, kc = chunk of 64 union rows), item id = ct * n_kc + kc.
+// CTA c owns items [c * ipc, (c + 1) * ipc): at most two column tiles ("segments"), four M = 128 accumulators each.
+//   A tile  : W_down^T[64 union rows][1 KB column segment], MN-major SWIZZLE_128B.  Column block b (128 columns) = two
+//             64-column halves (LBO 8 KB apart), each half = 8 atoms of 8 k-rows x 128 B (SBO 1 KB)  -> 16 KB per block
+//   B tile  : H[t][64 slots], K-major SWIZZLE_128B, TP rows of 128 B
+#define K2_NST   3
+#define K2_ATILE 65536
+#define K2_STAGE (K2_ATILE + 4096)
 #define K2_SMEM  (K2_NST * K2_STAGE + 256 + 1024)
 
 template <typename WT, int TP>
@@ -347,19 +412,6 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
     uint64_t *      accum_full = empty + K2_NST;  // [2]
     uint32_t *      tmem_slot  = reinterpret_cast<uint32_t *>(accum_full + 2);
 
-    const int U    = p.union_count[0];
-    const int n_kc = (U + 127) >> 7;
-    const int n_ct = p.n_embd >> 7;
-    const int I    = n_ct * n_kc;
-    const int ipc  = (I + P - 1) / P;
-    const int i0   = c * ipc;
-    const int i1   = min(I, i0 + ipc);
-    if (i0 >= i1) {
-        return;
-    }
-    const int ct0  = i0 / n_kc;
-    const int nseg = (i1 - 1) / n_kc - ct0 + 1;  // 1 or 2 (launcher guarantees n_ct <= P)
-
     if (tid == 0) {
         for (int s = 0; s < K2_NST; ++s) {
             mbar_init(&full[s], 128);
@@ -370,86 +422,102 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
         mbar_fence_init();
     }
     if (warp == 4) {
-        tmem_alloc(tmem_slot, 64);
+        tmem_alloc(tmem_slot, 256);
     }
+    pdl_wait_prior_grid();  // H, union list
+    pdl_launch_dependents();
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < 4) {
-        const int ch = tid & 15, ksub = tid >> 4;
-        uint32_t  it = 0;
-        for (int i = i0; i < i1; ++i, ++it) {
-            const int      ct = i / n_kc, kc = i - ct * n_kc;
-            const uint32_t st = it % K2_NST;
-            if (it >= K2_NST) {
-                mbar_wait(&empty[st], ((it / K2_NST) - 1u) & 1u);
+    const int  U    = p.union_count[0];
+    const int  U8   = (U + 7) & ~7;
+    const int  n_kc = (U + 63) >> 6;
+    const int  n_ct = p.n_embd >> 9;
+    const int  I    = n_ct * n_kc;
+    const int  ipc  = (I + P - 1) / P;
+    const int  i0   = c * ipc;
+    const int  i1   = min(I, i0 + ipc);
+    const bool work = i0 < i1;
+    const int  ct0  = work ? i0 / n_kc : 0;
+    const int  nseg = work ? (i1 - 1) / n_kc - ct0 + 1 : 0;  // 1 or 2 (launcher guarantees n_ct <= P)
+
+    if (work && warp < 4) {
+        const int ch = tid & 63, ksub = tid >> 6;
+        // byte offset of this thread's 16-byte column chunk inside a k-row's swizzle atom set
+        const uint32_t ch_off = (uint32_t) ((ch >> 4) * 16384 + ((ch >> 3) & 1) * 8192);
+        uint32_t       st = 0, lap = 0;
+        for (int i = i0; i < i1; ++i) {
+            const int ct = i / n_kc, kc = i - ct * n_kc;
+            if (lap > 0) {
+                mbar_wait(&empty[st], (lap - 1u) & 1u);
             }
-            const uint32_t sA = sbase + st * K2_STAGE;
-#pragma unroll 4
-            for (int j = 0; j < 16; ++j) {
-                const int      k     = ksub + 8 * j;
-                const int      slot  = kc * 128 + k;
+            const uint32_t        sA   = sbase + st * K2_STAGE;
+            const unsigned char * wcol = p.w_down + (size_t) ct * 1024 + ch * 16;
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {
+                const int      k     = ksub + 2 * j;
+                const int      slot  = kc * 64 + k;
                 const bool     valid = slot < U;
                 const int      row   = valid ? __ldg(p.union_idx + slot) : 0;
-                const uint32_t off   = (uint32_t) ((ch >> 3) * 16384 + (k >> 3) * 1024 + (k & 7) * 128 + (((ch & 7) ^ (k & 7)) << 4));
-                cp_async16_zfill(sA + off, p.w_down + (size_t) row * p.row_bytes + (size_t) ct * 256 + ch * 16, valid ? 16u : 0u);
+                const uint32_t off   = ch_off + (uint32_t) ((k >> 3) * 1024 + (k & 7) * 128 + (((ch & 7) ^ (k & 7)) << 4));
+                cp_async16_zfill(sA + off, wcol + (size_t) row * p.row_bytes, valid ? 16u : 0u);
             }
 #pragma unroll
-            for (int h = 0; h < TP * 16 / 128; ++h) {
-                const int idx = tid + 128 * h, t = idx >> 4, c16 = idx & 15;
-                cp_async16(sA + K2_ATILE + (c16 >> 3) * (TP * 128) + swz_kmajor(t, c16 & 7),
-                           p.hh + (size_t) t * p.m_pad + kc * 128 + c16 * 8);
+            for (int h = 0; h < TP * 8 / 128; ++h) {
+                const int  idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
+                const int  s8  = kc * 64 + c8 * 8;
+                cp_async16_zfill(sA + K2_ATILE + swz_kmajor(t, c8), p.hh + (size_t) t * p.m_pad + s8, s8 < U8 ? 16u : 0u);
             }
-            cp_async_commit();
-            if (it >= K2_LAG) {
-                cp_async_wait<K2_LAG>();
-                fence_proxy_async_smem();
-                mbar_arrive(&full[(it - K2_LAG) % K2_NST]);
+            cp_async_mbar_arrive_noinc(&full[st]);
+            if (++st == K2_NST) {
+                st = 0;
+                ++lap;
             }
         }
-        cp_async_wait<0>();
-        fence_proxy_async_smem();
-        for (int d = min((uint32_t) K2_LAG, it); d >= 1; --d) {
-            mbar_arrive(&full[(it - d) % K2_NST]);
-        }
-        // ---- epilogue: one partial tile per segment, part[c][seg][t][col]
+        // ---- epilogue: one partial tile per segment, part[c][seg][t][512 columns]
         for (int seg = 0; seg < nseg; ++seg) {
             mbar_wait(&accum_full[seg], 0);
             tc_fence_after_sync();
-            float          v[TP];
-            const uint32_t taddr = tmem_base + ((uint32_t) (warp * 32) << 16) + seg * TP;
 #pragma unroll
-            for (int h = 0; h < TP / 16; ++h) {
-                tmem_ld16(taddr + h * 16, *reinterpret_cast<float(*)[16]>(v + h * 16));
-            }
-            float * o = p.part + ((size_t) (c * 2 + seg) * TP) * 128 + tid;
+            for (int b = 0; b < 4; ++b) {
+                float          v[TP];
+                const uint32_t taddr = tmem_base + ((uint32_t) (warp * 32) << 16) + (seg * 4 + b) * TP;
 #pragma unroll
-            for (int t = 0; t < TP; ++t) {
-                if (t < p.n_tok) {
-                    o[t * 128] = v[t];
+                for (int h = 0; h < TP / 16; ++h) {
+                    tmem_ld16(taddr + h * 16, *reinterpret_cast<float(*)[16]>(v + h * 16));
+                }
+                float * o = p.part + ((size_t) (c * 2 + seg) * TP) * 512 + b * 128 + tid;
+#pragma unroll
+                for (int t = 0; t < TP; ++t) {
+                    if (t < p.n_tok) {
+                        o[t * 512] = v[t];
+                    }
                 }
             }
         }
-    } else {
+    } else if (work) {
         constexpr uint32_t idesc = umma_idesc_f16(wt_fmt<WT>::id, 1, 0, 128, TP);
-        uint32_t           it    = 0;
-        for (int i = i0; i < i1; ++i, ++it) {
-            const int      ct = i / n_kc, kc = i - ct * n_kc;
-            const int      seg = ct - ct0;
-            const uint32_t st  = it % K2_NST;
-            const bool     first = (i == i0) || (kc == 0);
-            const bool     last  = (i == i1 - 1) || (kc == n_kc - 1);
-            mbar_wait(&full[st], (it / K2_NST) & 1u);
+        uint32_t           st = 0, lap = 0;
+        for (int i = i0; i < i1; ++i) {
+            const int  ct = i / n_kc, kc = i - ct * n_kc;
+            const int  seg   = ct - ct0;
+            const bool first = (i == i0) || (kc == 0);
+            const bool last  = (i == i1 - 1) || (kc == n_kc - 1);
+            mbar_wait(&full[st], lap & 1u);
+            fence_proxy_async_smem();
             tc_fence_after_sync();
             if (lane == 0) {
                 const uint32_t sA = sbase + st * K2_STAGE;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
-                    const uint64_t da = umma_smem_desc(sA + k * 2048, 16384, 1024);
-                    const uint64_t db = umma_smem_desc(sA + K2_ATILE + (k >> 2) * (TP * 128) + (k & 3) * 32, 16, 1024);
-                    umma_f16(tmem_base + seg * TP, da, db, idesc, (first && k == 0) ? 0u : 1u);
+                for (int k = 0; k < 4; ++k) {
+                    const uint64_t db = umma_smem_desc(sA + K2_ATILE + k * 32, 16, 1024);
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const uint64_t da = umma_smem_desc(sA + b * 16384 + k * 2048, 8192, 1024);
+                        umma_f16(tmem_base + (seg * 4 + b) * TP, da, db, idesc, (first && k == 0) ? 0u : 1u);
+                    }
                 }
                 umma_commit(&empty[st]);
                 if (last) {
@@ -457,21 +525,27 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
                 }
             }
             __syncwarp();
+            if (++st == K2_NST) {
+                st = 0;
+                ++lap;
+            }
         }
     }
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 4) {
-        tmem_dealloc(tmem_base, 64);
+        tmem_dealloc(tmem_base, 256);
     }
 }
 
-// y[t][col] = sum over the CTAs whose item range touched column tile ct, ascending CTA order (fixed) (+ b_down)
+// y[t][col] = sum over the CTAs whose item range touched the column's 512-wide tile, ascending CTA order (fixed) (+ b_down)
 __global__ void __launch_bounds__(128) spif_batch_reduce_kernel(const BatchParams p, int P, int TP) {
-    const int ct = blockIdx.x, t = blockIdx.y, col = threadIdx.x;
+    const int ct = blockIdx.x >> 2, t = blockIdx.y, col = (blockIdx.x & 3) * 128 + threadIdx.x;
+    pdl_wait_prior_grid();
+    pdl_launch_dependents();
     const int U    = p.union_count[0];
-    const int n_kc = (U + 127) >> 7;
-    const int n_ct = p.n_embd >> 7;
+    const int n_kc = (U + 63) >> 6;
+    const int n_ct = p.n_embd >> 9;
     const int I    = n_ct * n_kc;
     float     s    = 0.f;
     if (I > 0) {
@@ -479,14 +553,14 @@ __global__ void __launch_bounds__(128) spif_batch_reduce_kernel(const BatchParam
         const int lo = ct * n_kc, hi = lo + n_kc - 1;
         for (int c = lo / ipc; c <= hi / ipc; ++c) {
             const int seg = ct - (c * ipc) / n_kc;
-            s += p.part[((size_t) (c * 2 + seg) * TP + t) * 128 + col];
+            s += p.part[((size_t) (c * 2 + seg) * TP + t) * 512 + col];
         }
     }
     if (p.b_down) {
-        s += __ldg(p.b_down + ct * 128 + col);
+        s += __ldg(p.b_down + ct * 512 + col);
     }
-    p.y[(size_t) t * p.n_embd + ct * 128 + col] = s;
-    if (p.stats_out && ct == 0 && col == 0) {
+    p.y[(size_t) t * p.n_embd + ct * 512 + col] = s;
+    if (p.stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
         p.stats_out[t * 4 + 3] = p.union_count[1];
     }
 }
@@ -502,7 +576,23 @@ size_t spif_batch_workspace_bytes(int n_embd, int n_ff, int n_tok) {
         return 0;
     }
     const size_t TP = 32, P = 320, m_pad = ((size_t) n_ff + 127) / 128 * 128;
-    return al256(4 * (size_t) n_ff) * 2 + 256 + al256(TP * (size_t) n_embd * 2) + al256(TP * m_pad * 2) + al256(P * 2 * TP * 128 * 4);
+    return al256(4 * (size_t) n_ff) * 2 + 256 + al256(TP * (size_t) n_embd * 2) + al256(TP * m_pad * 2) + al256(P * 2 * TP * 512 * 4);
+}
+
+// every kernel of the chain opts into programmatic dependent launch and starts with griddepcontrol.wait
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = grid;
+    cfg.blockDim           = block;
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
 template <typename WT, int TP>
@@ -521,12 +611,11 @@ static int launch_batch_t(const BatchParams & bp, int P, const spif_launch_ctx &
     const int nb_bits = (bp.m + 255) / 256;
     const int nvec    = TP * (bp.n_embd >> 3);
     const int nb_cvt  = min(64, (nvec + 255) / 256);
-    spif_batch_bits_kernel<WT><<<nb_bits + nb_cvt, 256, 0, ctx.stream>>>(bp, nb_bits, TP);
-    spif_batch_union_kernel<<<1, 1024, 0, ctx.stream>>>(bp);
-    k1<<<P, 160, K1_SMEM, ctx.stream>>>(bp);
-    k2<<<P, 160, K2_SMEM, ctx.stream>>>(bp);
-    spif_batch_reduce_kernel<<<dim3(bp.n_embd >> 7, bp.n_tok), 128, 0, ctx.stream>>>(bp, P, TP);
-    SPIF_CUDA_TRY(cudaGetLastError());
+    SPIF_CUDA_TRY(launch_pdl(spif_batch_bits_kernel<WT>, dim3(nb_bits + nb_cvt), dim3(256), 0, ctx.stream, bp, nb_bits, (int) TP));
+    SPIF_CUDA_TRY(launch_pdl(spif_batch_union_kernel, dim3(1), dim3(1024), 0, ctx.stream, bp));
+    SPIF_CUDA_TRY(launch_pdl(k1, dim3(P), dim3(160), K1_SMEM, ctx.stream, bp));
+    SPIF_CUDA_TRY(launch_pdl(k2, dim3(P), dim3(160), K2_SMEM, ctx.stream, bp));
+    SPIF_CUDA_TRY(launch_pdl(spif_batch_reduce_kernel, dim3(bp.n_embd >> 7, bp.n_tok), dim3(128), 0, ctx.stream, bp, P, (int) TP));
     return 0;
 }
 
@@ -535,7 +624,7 @@ int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, c
     SPIF_REQUIRE(a.type == SPIF_TYPE_F16 || a.type == SPIF_TYPE_BF16, SPIF_E_UNSUPPORTED);
     SPIF_REQUIRE(a.n_tok >= 2 && a.n_tok <= 32, SPIF_E_UNSUPPORTED);
     const int P = ctx.sm_count;
-    SPIF_REQUIRE(a.n_embd % 128 == 0 && (a.n_embd >> 7) <= P && a.m <= SPIF_B_ROWS_MAX * P, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE(a.n_embd % 512 == 0 && (a.n_embd >> 9) <= P && a.m <= SPIF_B_ROWS_MAX * P, SPIF_E_UNSUPPORTED);
     SPIF_REQUIRE(ctx.max_smem_optin >= K1_SMEM && ctx.max_smem_optin >= K2_SMEM, SPIF_E_UNSUPPORTED);
     const int    TP    = a.n_tok <= 16 ? 16 : 32;
     const size_t m_pad = ((size_t) a.m + 127) / 128 * 128;
@@ -564,6 +653,8 @@ int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, c
     bp.arch       = a.arch;
     bp.gated      = (a.arch != SPIF_ARCH_RELU_UP) ? 1 : 0;
     bp.thr        = a.thr;
+    static const int k_debug = [] { const char * e = getenv("SPIF_BATCH_DEBUG"); return e ? atoi(e) : 0; }();
+    bp.debug      = k_debug;
 
     SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0, SPIF_E_WORKSPACE);
     char * w = (char *) ws;
@@ -577,13 +668,11 @@ int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, c
     bp.xh = (uint16_t *) (w + o);
     o += al256((size_t) TP * a.n_embd * 2);
     bp.hh = (uint16_t *) (w + o);
-    const size_t hh_bytes = (size_t) TP * m_pad * 2;
-    o += al256(hh_bytes);
+    o += al256((size_t) TP * m_pad * 2);
     bp.part = (float *) (w + o);
-    o += al256((size_t) P * 2 * TP * 128 * 4);
+    o += al256((size_t) P * 2 * TP * 512 * 4);
     SPIF_REQUIRE(ws_bytes >= o, SPIF_E_WORKSPACE);
 
-    SPIF_CUDA_TRY(cudaMemsetAsync(bp.hh, 0, hh_bytes, ctx.stream));
     if (a.hidden_out) {
         SPIF_CUDA_TRY(cudaMemsetAsync(a.hidden_out, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
     }

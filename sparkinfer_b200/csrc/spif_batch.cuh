@@ -22,6 +22,11 @@ __device__ __forceinline__ void cp_async_commit() {
 template <int N> __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
+// asynchronous arrive on `bar` once all cp.async issued so far by this thread have landed; does not change the barrier's
+// pending count, so the expected count has to include this arrival
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t * bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 // generic-proxy writes to shared memory (st.shared, cp.async) -> visible to the async proxy (tcgen05.mma operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -43,13 +48,14 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t base, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(base), "r"(cols) : "memory");
 }
 
-__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout = 2 /* SWIZZLE_128B; 6 = SWIZZLE_32B */) {
     uint64_t d = 0;
     d |= (uint64_t) ((saddr >> 4) & 0x3FFFu);
     d |= (uint64_t) ((lbo_bytes >> 4) & 0x3FFFu) << 16;
     d |= (uint64_t) ((sbo_bytes >> 4) & 0x3FFFu) << 32;
     d |= (uint64_t) 1 << 46;  // descriptor version (Blackwell)
-    d |= (uint64_t) 2 << 61;  // SWIZZLE_128B
+    d |= (uint64_t) layout << 61;
     return d;
 }
 
@@ -93,6 +99,11 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 // 8-row atoms of 1024 B stacked along M/N)
 __device__ __forceinline__ uint32_t swz_kmajor(int r, int c) {
     return (uint32_t) ((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+}
+
+// K-major SWIZZLE_32B tile: rows of 32 B (one K = 16 MMA step), 8-row atoms of 256 B; 16-byte half `h` of row `r`
+__device__ __forceinline__ uint32_t swz32_kmajor(int r, int h) {
+    return (uint32_t) ((r >> 3) * 256 + (r & 7) * 32 + ((h ^ ((r >> 2) & 1)) << 4));
 }
 
 template <typename WT> struct wt_fmt;

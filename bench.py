@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=8, help="distinct x stacks cycled through (distinct masks per token)")
     ap.add_argument("--cpu-layers", type=int, default=4, help="layers in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
     ap.add_argument("--schedule", default="two-streams", choices=["serial", "two-streams"],
                     help="serial: the reference's node order on one stream; two-streams: predictor chain || FFN chain")
@@ -325,10 +326,66 @@ def run_ours(a):
                      "layer": {"achieved": (ffn_bytes + pred_bytes + 4 * L * (2 * E + st.m)) / (ms_step * 1e-3) / 1e9,
                                "us_per_layer": ms_step * 1e3 / L}},
     }
+    if world == 1 and not a.no_batched:
+        out["batched"] = batched_legs(a, st, wl, device)
     if world == 1 and not a.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(a, wl, iters=8, warmup=2)
     print(json.dumps(out), flush=True)
     leave()
+
+
+def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
+    """decode at batch T > 1 (BASELINE.json configs[2] shape, on this run's weights): per-token masks from the synthetic
+    predictor, then one spif_sparse_ffn call per layer -- the union-of-masks gathered GEMM on tcgen05 tensor cores (every
+    union row read once) next to the reference's per-(row, token) schedule (mm-sparse.cu:107-210, T x the row traffic).
+    Bytes = (2 A_u + Z_u) * row_bytes with A_u / Z_u the union rows / union rows with a non-zero hidden value."""
+    import torch
+    import sparkinfer_b200 as sp
+    E, F = wl["n_embd"], st.m
+    nl = min(n_layers, st.L)
+    res = []
+    gen = torch.Generator(device=device).manual_seed(a.seed + 77)
+    for T in batches:
+        x = torch.randn((T, E), device=device, generator=gen)
+        ws = sp.Workspace(E, F, T)
+        y = torch.empty((T, E), device=device)
+        masks = [sp.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, x, st.p_type, st.r, F, ws=ws).clone()
+                 for w in st.layers[:nl]]
+        stats = [torch.zeros((T, 4), dtype=torch.int32, device=device) for _ in range(nl)]
+        leg = {"n_tok": T, "layers_timed": nl}
+        for name, flags in (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN)):
+            def run():
+                for l, w in enumerate(st.layers[:nl]):
+                    sp.sparse_ffn(st.arch, st.w_type, w.up, w.gate, w.down_t, x, masks[l], F, flags=flags, ws=ws, out=y,
+                                  stats=stats[l], want_stats=True)
+            run()
+            torch.cuda.synchronize()
+            sn = torch.stack(stats).cpu().numpy()
+            g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream(device=device)
+            with torch.cuda.stream(side):
+                run()
+                side.synchronize()
+                with torch.cuda.graph(g, stream=side):
+                    run()
+            torch.cuda.synchronize()
+            for _ in range(3):
+                g.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / reps / nl
+            if name == "union_gemm":
+                rows = float((2 * sn[:, 0, 2] + sn[:, 0, 3]).mean())
+                leg["union_rows"] = float(sn[:, 0, 2].mean())
+            else:
+                rows = float((2 * sn[:, :, 0] + sn[:, :, 1]).sum(axis=1).mean())
+            leg[name] = {"us_per_layer": us, "ffn_tok_s": T / (us * st.L) * 1e6,
+                         "algorithmic_GBps": rows * 2 * E / us / 1e3}
+        res.append(leg)
+    return res
 
 
 # ---------------------------------------------------------------------------------------------------------------------

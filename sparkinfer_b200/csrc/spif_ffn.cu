@@ -20,6 +20,7 @@
 //   * each CTA writes one partial y; a tiny second kernel (launched with programmatic dependent launch) adds the
 //     partials in a fixed order -> run-to-run bit-stable, unlike axpy-sparse.cu:84.
 #include "spif_ffn_kernel.cuh"
+#include "spif_ffn_direct.cuh"
 
 unsigned long long * g_spif_trace = nullptr;  // debug only; see tools/trace_ffn.py
 extern "C" void spif_debug_set_trace(void * dev_ptr) {
@@ -140,6 +141,22 @@ static int launch_float(int type, int mode, int vpt, const FfnKParams & kp, dim3
                                      launch_v<spif_bf16>(mode, vpt, kp, grid, threads, smem, stream, device);
 }
 
+static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y, int32_t * stats_out, int n_embd, int n_tok,
+                         int P, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3((n_embd / 4 + SPIF_RED_COLS - 1) / SPIF_RED_COLS, n_tok);
+    cfg.blockDim           = dim3(SPIF_RED_COLS * SPIF_RED_LANES);
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel, (const float *) kp.partials, b_down, y,
+                                     (const int32_t *) kp.cta_stats, stats_out, n_embd, P));
+    return 0;
+}
+
 // workspace layout shared with spif_api.cu: [partials n_tok*P*n_embd f32][cta_stats n_tok*P*2 i32]
 // `row_bytes` / `nc` (consumer threads) / `variant` come from the weight format; `launch` instantiates the kernel.
 int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,
@@ -248,21 +265,86 @@ int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_
         return rc;
     }
     if (mode != SPIF_MODE_GEMV) {
-        float *            y  = (mode == SPIF_MODE_AXPY) ? dst_dense : a.y;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim            = dim3((a.n_embd / 4 + SPIF_RED_COLS - 1) / SPIF_RED_COLS, a.n_tok);
-        cfg.blockDim           = dim3(SPIF_RED_COLS * SPIF_RED_LANES);
-        cfg.stream             = ctx.stream;
-        cudaLaunchAttribute at[1];
-        at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
-        at[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs                                        = at;
-        cfg.numAttrs                                     = 1;
-        SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel, (const float *) kp.partials,
-                                         (mode == SPIF_MODE_FUSED) ? a.b_down : (const float *) nullptr, y,
-                                         (const int32_t *) kp.cta_stats, a.stats_out, a.n_embd, P));
+        return launch_reduce(kp, (mode == SPIF_MODE_FUSED) ? a.b_down : (const float *) nullptr,
+                             (mode == SPIF_MODE_AXPY) ? dst_dense : a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream);
     }
     return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// register-streaming fused layer (spif_ffn_direct.cuh)
+template <typename WT, int VPT, int NB, int MAXT>
+static int launch_direct_t(const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = grid;
+    cfg.blockDim           = dim3(threads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_ffn_direct_kernel<WT, VPT, NB, MAXT>, kp));
+    return 0;
+}
+
+// returns SPIF_E_UNSUPPORTED when the shape does not qualify (the ring kernel handles it then)
+static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
+    const int V = a.n_embd / 8;
+    SPIF_REQUIRE(V <= 1024, SPIF_E_UNSUPPORTED);
+    const int vpt     = V <= 640 ? 1 : 2;
+    const int threads = ((V + vpt - 1) / vpt + 31) / 32 * 32;
+    SPIF_REQUIRE(a.m <= 4096 * (threads / 32), SPIF_E_UNSUPPORTED);  // activity bits kept in registers by build_my_list
+    const int P = ctx.sm_count;
+    SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_LANES * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE(a.neuron_idx != nullptr || a.m == a.n_ff, SPIF_E_SHAPE);
+    SPIF_REQUIRE(a.sparse_idx != nullptr, SPIF_E_NULL);
+    FfnKParams kp = {};
+    kp.w_up       = (const unsigned char *) a.w_up;
+    kp.w_gate     = (const unsigned char *) a.w_gate;
+    kp.w_down     = (const unsigned char *) a.w_down_t;
+    kp.b_up       = a.b_up;
+    kp.b_gate     = a.b_gate;
+    kp.x          = a.x;
+    kp.mask       = a.sparse_idx;
+    kp.neuron_idx = a.neuron_idx;
+    kp.n_embd     = a.n_embd;
+    kp.n_ff       = a.n_ff;
+    kp.m          = a.m;
+    kp.mask_len   = (a.flags & SPIF_FLAG_MASK_BY_ROW) ? a.m : a.n_ff;
+    kp.V          = V;
+    kp.row_bytes  = a.n_embd * 2;
+    kp.thr        = a.thr;
+    kp.arch       = a.arch;
+    kp.flags      = a.flags;
+    kp.dense_out  = a.hidden_out;
+    kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;
+    kp.list_cap   = (a.m + P - 1) / P + 1;
+    const size_t part_bytes = sizeof(float) * (size_t) a.n_tok * P * a.n_embd;
+    const size_t stat_bytes = sizeof(int32_t) * (size_t) a.n_tok * P * 2;
+    SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= part_bytes + stat_bytes, SPIF_E_WORKSPACE);
+    kp.partials  = (float *) ws;
+    kp.cta_stats = (int32_t *) ((char *) ws + part_bytes);
+    const size_t smem = sizeof(float) * 2 * 2 * 2 * 32 + sizeof(int) * 36 + (size_t) 12 * kp.list_cap + 64;
+    SPIF_REQUIRE(smem <= 48 * 1024, SPIF_E_UNSUPPORTED);
+    if (a.hidden_out) {
+        SPIF_CUDA_TRY(cudaMemsetAsync(a.hidden_out, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
+    }
+    const dim3 grid(P, a.n_tok);
+    const bool f16 = a.type == SPIF_TYPE_F16;
+    int        rc;
+    if (vpt == 1) {
+        rc = f16 ? launch_direct_t<spif_f16, 1, 2, 640>(kp, grid, threads, smem, ctx.stream) :
+                   launch_direct_t<spif_bf16, 1, 2, 640>(kp, grid, threads, smem, ctx.stream);
+    } else {
+        rc = f16 ? launch_direct_t<spif_f16, 2, 1, 512>(kp, grid, threads, smem, ctx.stream) :
+                   launch_direct_t<spif_bf16, 2, 1, 512>(kp, grid, threads, smem, ctx.stream);
+    }
+    if (rc) {
+        return rc;
+    }
+    return launch_reduce(kp, a.b_down, a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream);
 }
 
 // F16 / BF16 entry: thread shape = VPT 16-byte vectors per consumer thread
@@ -270,6 +352,13 @@ int spif_launch_ffn(const spif_ffn_args & a, int mode, const float * hid_in, flo
                     const spif_launch_ctx & ctx) {
     SPIF_REQUIRE(a.type == SPIF_TYPE_F16 || a.type == SPIF_TYPE_BF16, SPIF_E_TYPE);
     SPIF_REQUIRE(a.n_embd > 0 && a.n_embd % 8 == 0, SPIF_E_SHAPE);
+    static const int k_direct = [] { const char * e = getenv("SPIF_DIRECT"); return e ? atoi(e) : 1; }();
+    if (mode == SPIF_MODE_FUSED && k_direct) {
+        const int rc = spif_launch_ffn_direct(a, ws, ws_bytes, ctx);
+        if (rc != SPIF_E_UNSUPPORTED) {
+            return rc;
+        }
+    }
     const int V   = a.n_embd / 8;
     const int vpt = (V <= 128) ? 1 : (V <= 768 ? 2 : 4);
     const int nc  = ((V + vpt - 1) / vpt + 31) / 32 * 32;

@@ -72,7 +72,8 @@ def test_sparse_ffn_fused(oracle, arch, wtype, n_embd, n_ff, n_tok):
         assert rel_err(y, y_ref) < tol, (TYPE_NAMES[wtype], arch, flags, rel_err(y, y_ref))
         # hidden: compare on active rows (the oracle's dense hidden also holds act(bias) on inactive rows: none here)
         act = ~(p < 0.5)
-        assert rel_err(hid * act, hid_ref * act) < (2e-5 if flags else TOL_DEFAULT[wtype])
+        # (n_tok > 1 runs the tensor-core path: FP32 accumulation in a different order than the oracle's lanes)
+        assert rel_err(hid * act, hid_ref * act) < ((2e-5 if n_tok == 1 else 5e-5) if flags else TOL_DEFAULT[wtype])
         assert np.array_equal(stats[:, 0], act.sum(axis=1))
     # determinism: two runs are bit-identical (the reference CUDA axpy is not, axpy-sparse.cu:9-11)
     y1 = sp.sparse_ffn(arch, wtype, dev(qu), None if arch == ARCH_RELU_UP else dev(qg), dev(qd), dev(x), dev(p), n_ff, ws=ws)

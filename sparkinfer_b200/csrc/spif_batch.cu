@@ -5,9 +5,9 @@
 // the per-token masks becomes a dense gathered GEMM, every union row is read from HBM exactly once per matrix:
 //   prep   : bits[row] = OR_t active(row, t) << t                 (spif_batch_bits_kernel, also x F32 -> F16/BF16)
 //            union_idx = ascending rows with bits != 0            (spif_batch_union_kernel, ballot + prefix scan)
-//   gate/up: CTA c owns a contiguous slice of the union; D[128 rows x T] = W[rows,:] . X^T with tcgen05.mma
-//            (A = gathered weight rows, K-major, cp.async into SWIZZLE_128B tiles; B = X; accumulators in TMEM),
-//            epilogue applies the per-token mask bits + bias + activation and writes H[t][slot] (weight float type)
+//   gate/up: CTA c owns a contiguous slice of the union; D[64 tokens x (up rows | gate rows)] = X . W[rows,:]^T with
+//            tcgen05.mma (A = x tile, B = gathered weight rows, both K-major, cp.async into SWIZZLE_128B tiles;
+//            accumulators in TMEM), epilogue applies the per-token mask bits + bias + activation and writes H[t][slot]
 //   down   : Y[T x n_embd] = H . Wdown^T[union rows, :] as a stream-K GEMM over (512-column tile, 64-row chunk) items;
 //            A = gathered 1 KB row segments of W_down^T (MN-major operand), B = H (K-major); each CTA accumulates a
 //            contiguous item range in TMEM and writes <= 2 partial tiles, summed in a fixed order by the last kernel.

@@ -170,8 +170,11 @@ __global__ void __launch_bounds__(1024) spif_batch_union_kernel(const BatchParam
 #define K1_TAIL  (1024 + 4 * SPIF_B_ROWS_MAX + 2 * 128 * 16 + 256)
 #define K1_SMEM  (K1_RING + K1_SLACK + K1_TAIL + 1024)
 
-template <typename WT, int TP>
+// QT = 0: F16/BF16 rows copied as they are; QT = Q8_0 / Q4_0: raw blocks are staged in shared memory (cp.async, groups of
+// 4 K blocks = 8 quant blocks per row, double-buffered) and dequantised to F16 operand tiles by the producer warps.
+template <typename WT, int TP, int QT>
 __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchParams p) {
+    constexpr int TR = (QT == SPIF_TYPE_Q8_0) ? 64 : ((QT == SPIF_TYPE_Q4_0) ? 96 : 128);  // rows per tile
     extern __shared__ unsigned char smem_raw[];
     const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int      P = gridDim.x, c = blockIdx.x;
@@ -230,23 +233,31 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
     const uint32_t tmem_base = *tmem_slot;
 
     const int      KB      = p.n_embd >> 6;
-    const int      n_tiles = (cnt + 127) >> 7;
+    const int      n_tiles = (cnt + TR - 1) / TR;
     const bool     gated   = p.gated != 0;
-    const int      R8      = (min(cnt, 128) + 7) >> 3;          // 8-row atoms per weight tile
+    const int      R8      = (min(cnt, TR) + 7) >> 3;          // 8-row atoms per weight tile
     const uint32_t a_bytes = (uint32_t) R8 * 1024u;
     const uint32_t x_off   = a_bytes * (gated ? 2u : 1u);
     const uint32_t stage_b = x_off + TP * 128;
-    const uint32_t NST     = min((uint32_t) K1_MAXST, (uint32_t) K1_RING / stage_b);
+    // quantised weights: [raw ring: 2 buffers x {up, gate} x TR rows x GB bytes][operand ring]
+    constexpr int  GB      = (QT == SPIF_TYPE_Q8_0) ? 272 : ((QT == SPIF_TYPE_Q4_0) ? 144 : 0);  // 8 quant blocks
+    constexpr uint32_t RAWB = (uint32_t) (2 * TR * GB);                                         // one raw buffer
+    constexpr uint32_t RAW_ALL = (2 * RAWB + 1023u) & ~1023u;
+    const uint32_t ring0   = sbase + RAW_ALL;
+    uint32_t       NST     = min((uint32_t) K1_MAXST, ((uint32_t) K1_RING - RAW_ALL) / stage_b);
+    if (QT != 0) {
+        NST &= ~1u;  // the dequantiser fills stages in pairs
+    }
     const int      ncol_up = R8 * 8;                            // accumulator columns: [up rows][gate rows]
 
     if (cnt > 0 && warp < 4) {
         const int cc = tid & 7, rsub = tid >> 3;
         uint32_t  st = 0, lap = 0;
         for (int tile = 0; tile < n_tiles; ++tile) {
-            const int cnt_t = min(128, cnt - tile * 128);
+            const int cnt_t = min(TR, cnt - tile * TR);
             const int buf   = (tile & 1) * 128;
             if (tid < cnt_t) {
-                const int row    = s_rows[tile * 128 + tid];
+                const int row    = s_rows[tile * TR + tid];
                 const int neu    = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
                 s_bits[buf + tid] = p.bits[row];
                 s_neu[buf + tid]  = neu;
@@ -258,35 +269,110 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int r = rsub + 16 * j;
-                rows[j]     = (r < cnt_t) ? s_rows[tile * 128 + r] : -1;
+                rows[j]     = (r < cnt_t) ? s_rows[tile * TR + r] : -1;
             }
+            if constexpr (QT == 0) {
             // CTAs walk K in rotated order so that they do not all read the same slice of x at the same moment
-            int kb = (int) (((unsigned) c * 29u) % (unsigned) KB);
-            for (int ki = 0; ki < KB; ++ki, kb = (kb + 1 == KB) ? 0 : kb + 1) {
-                if (lap > 0) {
-                    mbar_wait(&empty[st], (lap - 1u) & 1u);
-                }
-                const uint32_t sA = sbase + st * stage_b;
+                int kb = (int) (((unsigned) c * 29u) % (unsigned) KB);
+                for (int ki = 0; ki < KB; ++ki, kb = (kb + 1 == KB) ? 0 : kb + 1) {
+                    if (lap > 0) {
+                        mbar_wait(&empty[st], (lap - 1u) & 1u);
+                    }
+                    const uint32_t sA = ring0 + st * stage_b;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    if (rows[j] >= 0 && p.debug != 2) {
-                        const uint32_t off = swz_kmajor(rsub + 16 * j, cc);
-                        const size_t   go  = (size_t) rows[j] * p.row_bytes + (size_t) kb * 128 + cc * 16;
-                        cp_async16(sA + off, p.w_up + go);
-                        if (gated) {
-                            cp_async16(sA + a_bytes + off, p.w_gate + go);
+                    for (int j = 0; j < 8; ++j) {
+                        if (rows[j] >= 0 && p.debug != 2) {
+                            const uint32_t off = swz_kmajor(rsub + 16 * j, cc);
+                            const size_t   go  = (size_t) rows[j] * p.row_bytes + (size_t) kb * 128 + cc * 16;
+                            cp_async16(sA + off, p.w_up + go);
+                            if (gated) {
+                                cp_async16(sA + a_bytes + off, p.w_gate + go);
+                            }
                         }
                     }
-                }
 #pragma unroll
-                for (int h = 0; h < TP * 8 / 128; ++h) {
-                    const int idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
-                    cp_async16(sA + x_off + swz_kmajor(t, c8), p.xh + (size_t) t * p.n_embd + kb * 64 + c8 * 8);
+                    for (int h = 0; h < TP * 8 / 128; ++h) {
+                        const int idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
+                        cp_async16(sA + x_off + swz_kmajor(t, c8), p.xh + (size_t) t * p.n_embd + kb * 64 + c8 * 8);
+                    }
+                    cp_async_mbar_arrive_noinc(&full[st]);
+                    if (++st == NST) {
+                        st = 0;
+                        ++lap;
+                    }
                 }
-                cp_async_mbar_arrive_noinc(&full[st]);
-                if (++st == NST) {
-                    st = 0;
-                    ++lap;
+            } else {
+                using QP = qpair<QT>;
+                const int      nmat = gated ? 2 : 1;
+                const int      NG   = KB >> 2;
+                const int      RP   = (cnt_t + 31) & ~31;
+                constexpr int  NCH  = GB / 16;
+                const uint32_t raw0s = sbase;
+                auto issue_raw = [&](int g, int buf) {
+                    const int total = nmat * cnt_t * NCH;
+                    for (int idx = tid; idx < total; idx += 128) {
+                        const int unit = idx / NCH, ch = idx - unit * NCH;
+                        const int mt = unit >= cnt_t ? 1 : 0, r = unit - mt * cnt_t;
+                        const unsigned char * src = (mt ? p.w_gate : p.w_up) + (size_t) s_rows[tile * TR + r] * p.row_bytes +
+                                                    (size_t) g * GB + ch * 16;
+                        cp_async16(raw0s + buf * RAWB + (uint32_t) ((mt * TR + r) * GB + ch * 16), src);
+                    }
+                    cp_async_commit();
+                };
+                int g = (int) (((unsigned) c * 7u) % (unsigned) NG);
+                issue_raw(g, 0);
+                for (int gi = 0; gi < NG; ++gi) {
+                    const int buf = gi & 1, gn = (g + 1 == NG) ? 0 : g + 1;
+                    if (gi + 1 < NG) {
+                        issue_raw(gn, buf ^ 1);
+                    } else {
+                        cp_async_commit();
+                    }
+                    cp_async_wait<1>();
+                    named_bar_sync(1, 128);  // everybody's share of group gi has landed
+                    const unsigned char * rawp = sm + buf * RAWB;
+                    for (int h = 0; h < 2; ++h) {
+                        if (lap > 0) {
+                            mbar_wait(&empty[st], (lap - 1u) & 1u);
+                            mbar_wait(&empty[st + 1], (lap - 1u) & 1u);
+                        }
+                        const uint32_t sA0 = ring0 + st * stage_b;
+                        // x tiles of the two K blocks
+                        for (int idx = tid; idx < 2 * TP * 8; idx += 128) {
+                            const int s = idx / (TP * 8), rem = idx - s * (TP * 8), t = rem >> 3, c8 = rem & 7;
+                            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p.xh + (size_t) t * p.n_embd + (g * 4 + h * 2 + s) * 64) + c8);
+                            *reinterpret_cast<uint4 *>(sm + (sA0 - sbase) + s * stage_b + x_off + swz_kmajor(t, c8)) = v;
+                        }
+                        // weights: task = (row, matrix, K block of the pair): 2 quant blocks -> 64 F16 = one 128-byte tile row
+                        for (int id = tid; id < RP * nmat * 2; id += 128) {
+                            const int r = id % RP, rest = id / RP, mt = rest % nmat, s = rest / nmat;
+                            if (r < cnt_t) {
+                                const uint32_t * wp = reinterpret_cast<const uint32_t *>(rawp + (size_t) (mt * TR + r) * GB + (h * 2 + s) * (2 * QP::BS));
+                                uint32_t w[QP::NW];
+#pragma unroll
+                                for (int i = 0; i < QP::NW; ++i) {
+                                    w[i] = wp[i];
+                                }
+                                uint4 out[8];
+                                QP::dequant(w, out);
+                                unsigned char * dst = sm + (sA0 - sbase) + s * stage_b + mt * a_bytes;
+#pragma unroll
+                                for (int c8 = 0; c8 < 8; ++c8) {
+                                    *reinterpret_cast<uint4 *>(dst + swz_kmajor(r, c8)) = out[c8];
+                                }
+                            }
+                        }
+                        fence_proxy_async_smem();
+                        mbar_arrive(&full[st]);
+                        mbar_arrive(&full[st + 1]);
+                        st += 2;
+                        if (st == NST) {
+                            st = 0;
+                            ++lap;
+                        }
+                    }
+                    named_bar_sync(1, 128);  // raw[buf] may be overwritten by the copy issued in the next iteration
+                    g = gn;
                 }
             }
             if (warp >= 2) {
@@ -298,7 +384,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
             const int      t       = warp * 16 + lane;
             const bool     tok_ok  = lane < 16 && t < p.n_tok;
             const uint32_t taddr   = tmem_base + ((uint32_t) (warp * 32) << 16);
-            const int      slot0   = s0 + tile * 128;
+            const int      slot0   = s0 + tile * TR;
             int            n_act = 0, n_nz = 0;
             for (int r0 = 0; r0 < cnt_t; r0 += 16) {
                 float up[16], gt[16];
@@ -361,7 +447,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                 mbar_wait(&full[st], lap & 1u);
                 tc_fence_after_sync();
                 if (lane == 0) {
-                    const uint32_t sA = sbase + st * stage_b;
+                    const uint32_t sA = ring0 + st * stage_b;
 #pragma unroll
                     for (int k = 0; k < (p.debug == 1 ? 0 : 4); ++k) {
                         umma_f16(tmem_base, umma_smem_desc(sA + x_off + k * 32, 16, 1024), umma_smem_desc(sA + k * 32, 16, 1024),
@@ -398,8 +484,14 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
 #define K2_STAGE (K2_ATILE + 4096)
 #define K2_SMEM  (K2_NST * K2_STAGE + 256 + 1024)
 
-template <typename WT, int TP>
+// QT = Q8_0 / Q4_0: the 64 x 1 KB-of-columns item is 64 x 16 quant blocks; raw blocks are staged (cp.async, two buffers in
+// place of the third operand stage) and dequantised by the producer warps into the same MN-major operand tile.
+template <typename WT, int TP, int QT>
 __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchParams p) {
+    constexpr uint32_t NSTK = QT ? 2 : K2_NST;
+    constexpr int      SEGB = (QT == SPIF_TYPE_Q8_0) ? 544 : ((QT == SPIF_TYPE_Q4_0) ? 288 : 0);  // 16 quant blocks
+    constexpr uint32_t RAWB = 64u * SEGB;
+    constexpr uint32_t RAW_ALL = QT ? (uint32_t) K2_STAGE : 0u;  // raw ring lives where the third stage would be
     extern __shared__ unsigned char smem_raw[];
     const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int      P = gridDim.x, c = blockIdx.x;
@@ -430,6 +522,8 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t ring0     = sbase + RAW_ALL;
+    static_assert(2 * RAWB <= K2_STAGE, "raw ring does not fit");
 
     const int  U    = p.union_count[0];
     const int  U8   = (U + 7) & ~7;
@@ -448,32 +542,106 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
         // byte offset of this thread's 16-byte column chunk inside a k-row's swizzle atom set
         const uint32_t ch_off = (uint32_t) ((ch >> 4) * 16384 + ((ch >> 3) & 1) * 8192);
         uint32_t       st = 0, lap = 0;
+        if constexpr (QT == 0) {
         for (int i = i0; i < i1; ++i) {
-            const int ct = i / n_kc, kc = i - ct * n_kc;
-            if (lap > 0) {
-                mbar_wait(&empty[st], (lap - 1u) & 1u);
-            }
-            const uint32_t        sA   = sbase + st * K2_STAGE;
-            const unsigned char * wcol = p.w_down + (size_t) ct * 1024 + ch * 16;
+                const int ct = i / n_kc, kc = i - ct * n_kc;
+                if (lap > 0) {
+                    mbar_wait(&empty[st], (lap - 1u) & 1u);
+                }
+                const uint32_t        sA   = ring0 + st * K2_STAGE;
+                const unsigned char * wcol = p.w_down + (size_t) ct * 1024 + ch * 16;
 #pragma unroll 8
-            for (int j = 0; j < 32; ++j) {
-                const int      k     = ksub + 2 * j;
-                const int      slot  = kc * 64 + k;
-                const bool     valid = slot < U;
-                const int      row   = valid ? __ldg(p.union_idx + slot) : 0;
-                const uint32_t off   = ch_off + (uint32_t) ((k >> 3) * 1024 + (k & 7) * 128 + (((ch & 7) ^ (k & 7)) << 4));
-                cp_async16_zfill(sA + off, wcol + (size_t) row * p.row_bytes, valid ? 16u : 0u);
-            }
+                for (int j = 0; j < 32; ++j) {
+                    const int      k     = ksub + 2 * j;
+                    const int      slot  = kc * 64 + k;
+                    const bool     valid = slot < U;
+                    const int      row   = valid ? __ldg(p.union_idx + slot) : 0;
+                    const uint32_t off   = ch_off + (uint32_t) ((k >> 3) * 1024 + (k & 7) * 128 + (((ch & 7) ^ (k & 7)) << 4));
+                    cp_async16_zfill(sA + off, wcol + (size_t) row * p.row_bytes, valid ? 16u : 0u);
+                }
 #pragma unroll
-            for (int h = 0; h < TP * 8 / 128; ++h) {
-                const int  idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
-                const int  s8  = kc * 64 + c8 * 8;
-                cp_async16_zfill(sA + K2_ATILE + swz_kmajor(t, c8), p.hh + (size_t) t * p.m_pad + s8, s8 < U8 ? 16u : 0u);
+                for (int h = 0; h < TP * 8 / 128; ++h) {
+                    const int  idx = tid + 128 * h, t = idx >> 3, c8 = idx & 7;
+                    const int  s8  = kc * 64 + c8 * 8;
+                    cp_async16_zfill(sA + K2_ATILE + swz_kmajor(t, c8), p.hh + (size_t) t * p.m_pad + s8, s8 < U8 ? 16u : 0u);
+                }
+                cp_async_mbar_arrive_noinc(&full[st]);
+                if (++st == NSTK) {
+                    st = 0;
+                    ++lap;
+                }
             }
-            cp_async_mbar_arrive_noinc(&full[st]);
-            if (++st == K2_NST) {
-                st = 0;
-                ++lap;
+        } else {
+            using QP = qpair<QT>;
+            constexpr int NCH = SEGB / 16;
+            auto issue_raw = [&](int i, int buf) {
+                const int ct = i / n_kc, kc = i - ct * n_kc;
+                for (int idx = tid; idx < 64 * NCH; idx += 128) {
+                    const int kr = idx / NCH, chk = idx - kr * NCH;
+                    const int slot = kc * 64 + kr;
+                    if (slot < U) {
+                        cp_async16(sbase + buf * RAWB + (uint32_t) (kr * SEGB + chk * 16),
+                                   p.w_down + (size_t) __ldg(p.union_idx + slot) * p.row_bytes + (size_t) ct * SEGB + chk * 16);
+                    }
+                }
+                cp_async_commit();
+            };
+            issue_raw(i0, 0);
+            for (int i = i0; i < i1; ++i) {
+                const int ct = i / n_kc, kc = i - ct * n_kc;
+                const int buf = (i - i0) & 1;
+                if (i + 1 < i1) {
+                    issue_raw(i + 1, buf ^ 1);
+                } else {
+                    cp_async_commit();
+                }
+                cp_async_wait<1>();
+                named_bar_sync(1, 128);
+                if (lap > 0) {
+                    mbar_wait(&empty[st], (lap - 1u) & 1u);
+                }
+                unsigned char *       dstA = sm + RAW_ALL + st * K2_STAGE;
+                const unsigned char * rawp = sm + buf * RAWB;
+                // H tile
+                for (int idx = tid; idx < TP * 8; idx += 128) {
+                    const int t = idx >> 3, c8 = idx & 7, s8 = kc * 64 + c8 * 8;
+                    uint4     v = make_uint4(0u, 0u, 0u, 0u);
+                    if (s8 < U8) {
+                        v = *reinterpret_cast<const uint4 *>(p.hh + (size_t) t * p.m_pad + s8);
+                    }
+                    *reinterpret_cast<uint4 *>(dstA + K2_ATILE + swz_kmajor(t, c8)) = v;
+                }
+                // weights: task = (k-row, pair of quant blocks = 64 columns = one 128-byte MN-major row of one half)
+                for (int id = tid; id < 64 * 8; id += 128) {
+                    const int kr = id & 63, pp = id >> 6;
+                    uint4     out[8];
+                    if (kc * 64 + kr < U) {
+                        const uint32_t * wp = reinterpret_cast<const uint32_t *>(rawp + kr * SEGB + pp * (2 * QP::BS));
+                        uint32_t         w[QP::NW];
+#pragma unroll
+                        for (int q = 0; q < QP::NW; ++q) {
+                            w[q] = wp[q];
+                        }
+                        QP::dequant(w, out);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            out[q] = make_uint4(0u, 0u, 0u, 0u);
+                        }
+                    }
+                    unsigned char * d = dstA + (pp >> 1) * 16384 + (pp & 1) * 8192 + (kr >> 3) * 1024 + (kr & 7) * 128;
+#pragma unroll
+                    for (int c8 = 0; c8 < 8; ++c8) {
+                        *reinterpret_cast<uint4 *>(d + ((c8 ^ (kr & 7)) << 4)) = out[c8];
+                    }
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(&full[st]);
+                if (++st == NSTK) {
+                    st = 0;
+                    ++lap;
+                }
+                named_bar_sync(1, 128);
             }
         }
         // ---- epilogue: one partial tile per segment, part[c][seg][t][512 columns]
@@ -509,7 +677,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
             fence_proxy_async_smem();
             tc_fence_after_sync();
             if (lane == 0) {
-                const uint32_t sA = sbase + st * K2_STAGE;
+                const uint32_t sA = ring0 + st * K2_STAGE;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const uint64_t db = umma_smem_desc(sA + K2_ATILE + k * 32, 16, 1024);
@@ -525,7 +693,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
                 }
             }
             __syncwarp();
-            if (++st == K2_NST) {
+            if (++st == NSTK) {
                 st = 0;
                 ++lap;
             }
@@ -595,11 +763,11 @@ static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
     return cudaLaunchKernelEx(&cfg, kern, args...);
 }
 
-template <typename WT, int TP>
+template <typename WT, int TP, int QT>
 static int launch_batch_t(const BatchParams & bp, int P, const spif_launch_ctx & ctx) {
     static unsigned long long done1 = 0, done2 = 0;
-    auto k1 = spif_batch_gateup_kernel<WT, TP>;
-    auto k2 = spif_batch_down_kernel<WT, TP>;
+    auto k1 = spif_batch_gateup_kernel<WT, TP, QT>;
+    auto k2 = spif_batch_down_kernel<WT, TP, QT>;
     int  rc = spif_set_max_smem_once(k1, K1_SMEM, ctx.device, done1);
     if (rc) {
         return rc;
@@ -621,7 +789,8 @@ static int launch_batch_t(const BatchParams & bp, int P, const spif_launch_ctx &
 
 // returns SPIF_E_UNSUPPORTED when the shape does not qualify: the caller then uses the per-token kernel
 int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
-    SPIF_REQUIRE(a.type == SPIF_TYPE_F16 || a.type == SPIF_TYPE_BF16, SPIF_E_UNSUPPORTED);
+    const bool quant = a.type == SPIF_TYPE_Q8_0 || a.type == SPIF_TYPE_Q4_0;
+    SPIF_REQUIRE(a.type == SPIF_TYPE_F16 || a.type == SPIF_TYPE_BF16 || quant, SPIF_E_UNSUPPORTED);
     SPIF_REQUIRE(a.n_tok >= 2 && a.n_tok <= 32, SPIF_E_UNSUPPORTED);
     const int P = ctx.sm_count;
     SPIF_REQUIRE(a.n_embd % 512 == 0 && (a.n_embd >> 9) <= P && a.m <= SPIF_B_ROWS_MAX * P, SPIF_E_UNSUPPORTED);
@@ -649,7 +818,7 @@ int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, c
     bp.by_row     = (a.flags & SPIF_FLAG_MASK_BY_ROW) ? 1 : 0;
     bp.mask_len   = bp.by_row ? a.m : a.n_ff;
     bp.n_tok      = a.n_tok;
-    bp.row_bytes  = a.n_embd * 2;
+    bp.row_bytes  = quant ? (a.n_embd / 32) * (a.type == SPIF_TYPE_Q8_0 ? 34 : 18) : a.n_embd * 2;
     bp.arch       = a.arch;
     bp.gated      = (a.arch != SPIF_ARCH_RELU_UP) ? 1 : 0;
     bp.thr        = a.thr;
@@ -676,9 +845,16 @@ int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, c
     if (a.hidden_out) {
         SPIF_CUDA_TRY(cudaMemsetAsync(a.hidden_out, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
     }
+    // quantised weights are dequantised to F16 operand tiles, so x and H are F16 as well
+    if (a.type == SPIF_TYPE_Q8_0) {
+        return TP == 16 ? launch_batch_t<spif_f16, 16, SPIF_TYPE_Q8_0>(bp, P, ctx) : launch_batch_t<spif_f16, 32, SPIF_TYPE_Q8_0>(bp, P, ctx);
+    }
+    if (a.type == SPIF_TYPE_Q4_0) {
+        return TP == 16 ? launch_batch_t<spif_f16, 16, SPIF_TYPE_Q4_0>(bp, P, ctx) : launch_batch_t<spif_f16, 32, SPIF_TYPE_Q4_0>(bp, P, ctx);
+    }
     const bool f16 = a.type == SPIF_TYPE_F16;
     if (TP == 16) {
-        return f16 ? launch_batch_t<spif_f16, 16>(bp, P, ctx) : launch_batch_t<spif_bf16, 16>(bp, P, ctx);
+        return f16 ? launch_batch_t<spif_f16, 16, 0>(bp, P, ctx) : launch_batch_t<spif_bf16, 16, 0>(bp, P, ctx);
     }
-    return f16 ? launch_batch_t<spif_f16, 32>(bp, P, ctx) : launch_batch_t<spif_bf16, 32>(bp, P, ctx);
+    return f16 ? launch_batch_t<spif_f16, 32, 0>(bp, P, ctx) : launch_batch_t<spif_bf16, 32, 0>(bp, P, ctx);
 }

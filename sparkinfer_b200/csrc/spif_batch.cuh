@@ -117,3 +117,70 @@ template <> __device__ __forceinline__ uint16_t f32_to_wt_bits<spif_f16>(float v
 template <> __device__ __forceinline__ uint16_t f32_to_wt_bits<spif_bf16>(float v) {
     return __bfloat16_as_ushort(__float2bfloat16_rn(v));
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Q8_0 / Q4_0 block PAIRS (64 consecutive weights) -> 64 F16 values = 8 x 16-byte operand chunks.
+// Layouts: block_q8_0 {half d; int8 qs[32]} (34 B), block_q4_0 {half d; uint8 qs[16]} (18 B, element j = low nibble of
+// qs[j], element j + 16 = high nibble; value = (nibble - 8) * d)   -- ggml/src/ggml-common.h:170-174,211-215.
+// A pair starts 4-byte aligned (68 / 36 bytes), the second block of a pair does not: bytes are re-aligned with prmt.
+// Conversion without int->float instructions: byte u -> half bits 0x6400 | u == 1024 + u exactly; subtracting the bias
+// (1152 for int8 ^ 0x80, 1032 for nibbles) is exact in F16, the product with d rounds once: w16 = RN_f16(q * d).
+template <int QT> struct qpair;  // QT = ggml type id
+
+__device__ __forceinline__ uint32_t h2_sub_mul(uint32_t biased, uint32_t bias2, uint32_t d2) {
+    __half2 v = *reinterpret_cast<__half2 *>(&biased);
+    v         = __hmul2(__hsub2(v, *reinterpret_cast<__half2 *>(&bias2)), *reinterpret_cast<__half2 *>(&d2));
+    return *reinterpret_cast<uint32_t *>(&v);
+}
+
+template <> struct qpair<SPIF_TYPE_Q8_0> {
+    static constexpr int BS = 34, NW = 17;
+    // 4 int8 -> two half2
+    static __device__ __forceinline__ void cvt4(uint32_t q, uint32_t d2, uint32_t & lo, uint32_t & hi) {
+        const uint32_t x = q ^ 0x80808080u;
+        lo               = h2_sub_mul(__byte_perm(x, 0x64646464u, 0x4140), 0x64806480u /* 1152 */, d2);
+        hi               = h2_sub_mul(__byte_perm(x, 0x64646464u, 0x4342), 0x64806480u, d2);
+    }
+    static __device__ __forceinline__ void dequant(const uint32_t (&w)[NW], uint4 (&out)[8]) {
+        const uint32_t d0 = (w[0] & 0xffffu) * 0x10001u, d1 = (w[8] >> 16) * 0x10001u;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t qa = __byte_perm(w[2 * c], w[2 * c + 1], 0x5432), qb = __byte_perm(w[2 * c + 1], w[2 * c + 2], 0x5432);
+            cvt4(qa, d0, out[c].x, out[c].y);
+            cvt4(qb, d0, out[c].z, out[c].w);
+            cvt4(w[9 + 2 * c], d1, out[4 + c].x, out[4 + c].y);
+            cvt4(w[10 + 2 * c], d1, out[4 + c].z, out[4 + c].w);
+        }
+    }
+};
+
+template <> struct qpair<SPIF_TYPE_Q4_0> {
+    static constexpr int BS = 18, NW = 9;
+    // one 4-byte q word -> low nibbles of its 4 bytes (lo0, lo1) and high nibbles (hi0, hi1), each a half2
+    static __device__ __forceinline__ void cvt8(uint32_t q, uint32_t d2, uint32_t & lo0, uint32_t & lo1, uint32_t & hi0, uint32_t & hi1) {
+        const uint32_t t01 = __byte_perm(q, 0u, 0x4140), t23 = __byte_perm(q, 0u, 0x4342);
+        const uint32_t bias = 0x64086408u;  // 1032
+        lo0                 = h2_sub_mul((t01 & 0x000F000Fu) | 0x64006400u, bias, d2);
+        lo1                 = h2_sub_mul((t23 & 0x000F000Fu) | 0x64006400u, bias, d2);
+        hi0                 = h2_sub_mul(((t01 >> 4) & 0x000F000Fu) | 0x64006400u, bias, d2);
+        hi1                 = h2_sub_mul(((t23 >> 4) & 0x000F000Fu) | 0x64006400u, bias, d2);
+    }
+    static __device__ __forceinline__ void block(const uint32_t (&q)[4], uint32_t d2, uint4 * out) {
+        // chunk 0 = elements 0..7 (low nibbles of q words 0,1), chunk 1 = 8..15, chunk 2 = 16..23 (high nibbles), chunk 3
+        cvt8(q[0], d2, out[0].x, out[0].y, out[2].x, out[2].y);
+        cvt8(q[1], d2, out[0].z, out[0].w, out[2].z, out[2].w);
+        cvt8(q[2], d2, out[1].x, out[1].y, out[3].x, out[3].y);
+        cvt8(q[3], d2, out[1].z, out[1].w, out[3].z, out[3].w);
+    }
+    static __device__ __forceinline__ void dequant(const uint32_t (&w)[NW], uint4 (&out)[8]) {
+        const uint32_t d0 = (w[0] & 0xffffu) * 0x10001u, d1 = (w[4] >> 16) * 0x10001u;
+        uint32_t       q0[4], q1[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            q0[k] = __byte_perm(w[k], w[k + 1], 0x5432);
+            q1[k] = w[5 + k];
+        }
+        block(q0, d0, out);
+        block(q1, d1, out + 4);
+    }
+};

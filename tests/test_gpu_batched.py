@@ -83,3 +83,38 @@ def test_batched_shard_rows_and_empty_union(oracle):
     assert rel_err(y.cpu().numpy(), y_ref) < TOL[F16]
     y0 = sp.sparse_ffn(ARCH_PROSPARSE, F16, dev(fu), dev(fg), dev(fd), dev(x), dev(np.full_like(p, 0.1)), n_ff, ws=ws)
     assert float(y0.abs().max()) == 0.0
+
+
+QSHAPES = [(512, 1024, 2, 0.12), (1024, 2048, 8, 0.12), (4096, 1536, 17, 0.3), (5120, 13824, 32, 0.10), (1024, 30000, 5, 0.9)]
+
+
+@pytest.mark.parametrize("arch", [ARCH_PROSPARSE, ARCH_RELU_UP])
+@pytest.mark.parametrize("wtype", [8, 2])  # Q8_0, Q4_0 (ggml type ids)
+@pytest.mark.parametrize("n_embd,n_ff,n_tok,rho", QSHAPES)
+def test_batched_quant_sparse_ffn(oracle, arch, wtype, n_embd, n_ff, n_tok, rho):
+    """Q8_0 / Q4_0 union GEMM: raw blocks dequantised to F16 operand tiles in shared memory (w16 = RN(q * d)), F16 x.
+    The reference quantises x to 8 bit instead (mmq-sparse.cu, ggml-cpu.c:1832-1856), so the bar is the quant format's
+    own bound against both the oracle and the FP64 restatement on the same stored weights (Q4_0 axpy: parity unpinned,
+    the reference aborts for it, ggml-cpu.c:2225-2226)."""
+    import sparkinfer_b200 as sp
+    if n_ff > 20000 and arch != ARCH_PROSPARSE:
+        pytest.skip("large case once")
+    seed = synth.SEED0 + 13 * n_embd + n_ff + arch + n_tok + wtype
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(wtype, w) for w in (Wu, Wg, Wd))
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, rho, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    y_ref = oracle.sparse_ffn(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)[0]
+    y64 = oracle.sparse_ffn_f64(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)[0].astype(np.float32)
+    gate = None if arch == ARCH_RELU_UP else dev(qg)
+    y, stats = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, want_stats=True, ws=ws)
+    y, stats = y.cpu().numpy(), stats.cpu().numpy()
+    act = ~(p < 0.5)
+    assert rel_err(y, y64) < 2e-2, (wtype, arch, rel_err(y, y64))
+    assert rel_err(y, y_ref) < 2e-2, (wtype, arch, rel_err(y, y_ref))
+    assert rel_err(y, y64) <= rel_err(y_ref, y64) + 1e-3      # F16 activations are no worse than the 8-bit ones
+    assert np.array_equal(stats[:, 0], act.sum(axis=1))
+    assert np.all(stats[:, 2] == int(act.any(axis=0).sum()))
+    y2 = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, ws=ws)
+    assert np.array_equal(y, y2.cpu().numpy())

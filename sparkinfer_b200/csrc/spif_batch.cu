@@ -18,6 +18,8 @@
 #include <cstdlib>
 
 #define SPIF_B_ROWS_MAX 1024 /* union rows one CTA may own (m <= 1024 * SMs) */
+// producer threads of the two GEMM kernels: copying F16 rows needs few, dequantising Q8_0/Q4_0 blocks is ALU work
+#define BATCH_NP(QT) ((QT) ? 384 : 128)
 
 struct BatchParams {
     const unsigned char * w_up;
@@ -173,7 +175,8 @@ __global__ void __launch_bounds__(1024) spif_batch_union_kernel(const BatchParam
 // QT = 0: F16/BF16 rows copied as they are; QT = Q8_0 / Q4_0: raw blocks are staged in shared memory (cp.async, groups of
 // 4 K blocks = 8 quant blocks per row, double-buffered) and dequantised to F16 operand tiles by the producer warps.
 template <typename WT, int TP, int QT>
-__global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchParams p) {
+__global__ void __launch_bounds__(BATCH_NP(QT) + 32, 1) spif_batch_gateup_kernel(const BatchParams p) {
+    constexpr int NP = BATCH_NP(QT);  // producer threads; warp NP / 32 owns TMEM and issues the MMAs
     constexpr int TR = (QT == SPIF_TYPE_Q8_0) ? 64 : ((QT == SPIF_TYPE_Q4_0) ? 96 : 128);  // rows per tile
     extern __shared__ unsigned char smem_raw[];
     const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -197,14 +200,14 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
 
     if (tid == 0) {
         for (int s = 0; s < K1_MAXST; ++s) {
-            mbar_init(&full[s], 128);
+            mbar_init(&full[s], NP);
             mbar_init(&empty[s], 1);
         }
         mbar_init(accum_full, 1);
         mbar_init(tmem_empty, 64);
         mbar_fence_init();
     }
-    if (warp == 4) {
+    if (warp == NP / 32) {
         tmem_alloc(tmem_slot, 256);
     }
     pdl_wait_prior_grid();  // union list, bits, xh
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
     }
     const int      ncol_up = R8 * 8;                            // accumulator columns: [up rows][gate rows]
 
-    if (cnt > 0 && warp < 4) {
+    if (cnt > 0 && warp < NP / 32) {
         const int cc = tid & 7, rsub = tid >> 3;
         uint32_t  st = 0, lap = 0;
         for (int tile = 0; tile < n_tiles; ++tile) {
@@ -264,7 +267,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                 s_bu[buf + tid]   = p.b_up ? __ldg(p.b_up + neu) : 0.f;
                 s_bg[buf + tid]   = (gated && p.b_gate) ? __ldg(p.b_gate + neu) : 0.f;
             }
-            named_bar_sync(1, 128);
+            named_bar_sync(1, NP);
             int rows[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -310,7 +313,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                 const uint32_t raw0s = sbase;
                 auto issue_raw = [&](int g, int buf) {
                     const int total = nmat * cnt_t * NCH;
-                    for (int idx = tid; idx < total; idx += 128) {
+                    for (int idx = tid; idx < total; idx += NP) {
                         const int unit = idx / NCH, ch = idx - unit * NCH;
                         const int mt = unit >= cnt_t ? 1 : 0, r = unit - mt * cnt_t;
                         const unsigned char * src = (mt ? p.w_gate : p.w_up) + (size_t) s_rows[tile * TR + r] * p.row_bytes +
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                         cp_async_commit();
                     }
                     cp_async_wait<1>();
-                    named_bar_sync(1, 128);  // everybody's share of group gi has landed
+                    named_bar_sync(1, NP);  // everybody's share of group gi has landed
                     const unsigned char * rawp = sm + buf * RAWB;
                     for (int h = 0; h < 2; ++h) {
                         if (lap > 0) {
@@ -338,13 +341,13 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                         }
                         const uint32_t sA0 = ring0 + st * stage_b;
                         // x tiles of the two K blocks
-                        for (int idx = tid; idx < 2 * TP * 8; idx += 128) {
+                        for (int idx = tid; idx < 2 * TP * 8; idx += NP) {
                             const int s = idx / (TP * 8), rem = idx - s * (TP * 8), t = rem >> 3, c8 = rem & 7;
                             const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p.xh + (size_t) t * p.n_embd + (g * 4 + h * 2 + s) * 64) + c8);
                             *reinterpret_cast<uint4 *>(sm + (sA0 - sbase) + s * stage_b + x_off + swz_kmajor(t, c8)) = v;
                         }
                         // weights: task = (row, matrix, K block of the pair): 2 quant blocks -> 64 F16 = one 128-byte tile row
-                        for (int id = tid; id < RP * nmat * 2; id += 128) {
+                        for (int id = tid; id < RP * nmat * 2; id += NP) {
                             const int r = id % RP, rest = id / RP, mt = rest % nmat, s = rest / nmat;
                             if (r < cnt_t) {
                                 const uint32_t * wp = reinterpret_cast<const uint32_t *>(rawp + (size_t) (mt * TR + r) * GB + (h * 2 + s) * (2 * QP::BS));
@@ -371,7 +374,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
                             ++lap;
                         }
                     }
-                    named_bar_sync(1, 128);  // raw[buf] may be overwritten by the copy issued in the next iteration
+                    named_bar_sync(1, NP);  // raw[buf] may be overwritten by the copy issued in the next iteration
                     g = gn;
                 }
             }
@@ -468,7 +471,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
     }
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == NP / 32) {
         tmem_dealloc(tmem_base, 256);
     }
 }
@@ -487,7 +490,8 @@ __global__ void __launch_bounds__(160, 1) spif_batch_gateup_kernel(const BatchPa
 // QT = Q8_0 / Q4_0: the 64 x 1 KB-of-columns item is 64 x 16 quant blocks; raw blocks are staged (cp.async, two buffers in
 // place of the third operand stage) and dequantised by the producer warps into the same MN-major operand tile.
 template <typename WT, int TP, int QT>
-__global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchParams p) {
+__global__ void __launch_bounds__(BATCH_NP(QT) + 32, 1) spif_batch_down_kernel(const BatchParams p) {
+    constexpr int NP = BATCH_NP(QT);
     constexpr uint32_t NSTK = QT ? 2 : K2_NST;
     constexpr int      SEGB = (QT == SPIF_TYPE_Q8_0) ? 544 : ((QT == SPIF_TYPE_Q4_0) ? 288 : 0);  // 16 quant blocks
     constexpr uint32_t RAWB = 64u * SEGB;
@@ -506,14 +510,14 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
 
     if (tid == 0) {
         for (int s = 0; s < K2_NST; ++s) {
-            mbar_init(&full[s], 128);
+            mbar_init(&full[s], NP);
             mbar_init(&empty[s], 1);
         }
         mbar_init(&accum_full[0], 1);
         mbar_init(&accum_full[1], 1);
         mbar_fence_init();
     }
-    if (warp == 4) {
+    if (warp == NP / 32) {
         tmem_alloc(tmem_slot, 256);
     }
     pdl_wait_prior_grid();  // H, union list
@@ -537,7 +541,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
     const int  ct0  = work ? i0 / n_kc : 0;
     const int  nseg = work ? (i1 - 1) / n_kc - ct0 + 1 : 0;  // 1 or 2 (launcher guarantees n_ct <= P)
 
-    if (work && warp < 4) {
+    if (work && warp < NP / 32) {
         const int ch = tid & 63, ksub = tid >> 6;
         // byte offset of this thread's 16-byte column chunk inside a k-row's swizzle atom set
         const uint32_t ch_off = (uint32_t) ((ch >> 4) * 16384 + ((ch >> 3) & 1) * 8192);
@@ -576,7 +580,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
             constexpr int NCH = SEGB / 16;
             auto issue_raw = [&](int i, int buf) {
                 const int ct = i / n_kc, kc = i - ct * n_kc;
-                for (int idx = tid; idx < 64 * NCH; idx += 128) {
+                for (int idx = tid; idx < 64 * NCH; idx += NP) {
                     const int kr = idx / NCH, chk = idx - kr * NCH;
                     const int slot = kc * 64 + kr;
                     if (slot < U) {
@@ -596,14 +600,14 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
                     cp_async_commit();
                 }
                 cp_async_wait<1>();
-                named_bar_sync(1, 128);
+                named_bar_sync(1, NP);
                 if (lap > 0) {
                     mbar_wait(&empty[st], (lap - 1u) & 1u);
                 }
                 unsigned char *       dstA = sm + RAW_ALL + st * K2_STAGE;
                 const unsigned char * rawp = sm + buf * RAWB;
                 // H tile
-                for (int idx = tid; idx < TP * 8; idx += 128) {
+                for (int idx = tid; idx < TP * 8; idx += NP) {
                     const int t = idx >> 3, c8 = idx & 7, s8 = kc * 64 + c8 * 8;
                     uint4     v = make_uint4(0u, 0u, 0u, 0u);
                     if (s8 < U8) {
@@ -612,7 +616,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
                     *reinterpret_cast<uint4 *>(dstA + K2_ATILE + swz_kmajor(t, c8)) = v;
                 }
                 // weights: task = (k-row, pair of quant blocks = 64 columns = one 128-byte MN-major row of one half)
-                for (int id = tid; id < 64 * 8; id += 128) {
+                for (int id = tid; id < 64 * 8; id += NP) {
                     const int kr = id & 63, pp = id >> 6;
                     uint4     out[8];
                     if (kc * 64 + kr < U) {
@@ -641,11 +645,11 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
                     st = 0;
                     ++lap;
                 }
-                named_bar_sync(1, 128);
+                named_bar_sync(1, NP);
             }
         }
         // ---- epilogue: one partial tile per segment, part[c][seg][t][512 columns]
-        for (int seg = 0; seg < nseg; ++seg) {
+        for (int seg = 0; seg < (warp < 4 ? nseg : 0); ++seg) {
             mbar_wait(&accum_full[seg], 0);
             tc_fence_after_sync();
 #pragma unroll
@@ -701,7 +705,7 @@ __global__ void __launch_bounds__(160, 1) spif_batch_down_kernel(const BatchPara
     }
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == NP / 32) {
         tmem_dealloc(tmem_base, 256);
     }
 }
@@ -781,8 +785,8 @@ static int launch_batch_t(const BatchParams & bp, int P, const spif_launch_ctx &
     const int nb_cvt  = min(64, (nvec + 255) / 256);
     SPIF_CUDA_TRY(launch_pdl(spif_batch_bits_kernel<WT>, dim3(nb_bits + nb_cvt), dim3(256), 0, ctx.stream, bp, nb_bits, (int) TP));
     SPIF_CUDA_TRY(launch_pdl(spif_batch_union_kernel, dim3(1), dim3(1024), 0, ctx.stream, bp));
-    SPIF_CUDA_TRY(launch_pdl(k1, dim3(P), dim3(160), K1_SMEM, ctx.stream, bp));
-    SPIF_CUDA_TRY(launch_pdl(k2, dim3(P), dim3(160), K2_SMEM, ctx.stream, bp));
+    SPIF_CUDA_TRY(launch_pdl(k1, dim3(P), dim3(BATCH_NP(QT) + 32), K1_SMEM, ctx.stream, bp));
+    SPIF_CUDA_TRY(launch_pdl(k2, dim3(P), dim3(BATCH_NP(QT) + 32), K2_SMEM, ctx.stream, bp));
     SPIF_CUDA_TRY(launch_pdl(spif_batch_reduce_kernel, dim3(bp.n_embd >> 7, bp.n_tok), dim3(128), 0, ctx.stream, bp, P, (int) TP));
     return 0;
 }

@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=8, help="distinct x stacks cycled through (distinct masks per token)")
     ap.add_argument("--cpu-layers", type=int, default=4, help="layers in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="per-layer sum over GPU shards: fused peer-memory exchange (default) or ncclAllReduce")
     ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
     ap.add_argument("--schedule", default="two-streams", choices=["serial", "two-streams"],
@@ -165,7 +167,8 @@ def build_stack(a, wl, rank, world, device):
         layers.append(LayerWeights(up=half(m, E, 0.02), gate=half(m, E, 0.02), down_t=half(m, E, 0.02), pred_up=wpu,
                                    pred_down=half(m, R, R ** -0.5), pred_down_b=bpd, m=m))
     group = torch.distributed.group.WORLD if world > 1 else None
-    st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device)
+    st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device,
+                  exchange=a.exchange)
     return st, expect
 
 
@@ -309,7 +312,7 @@ def run_ours(a):
         "config": {"workload": wl["label"], "n_embd": E, "n_ff": F, "n_layer": L, "pred_rank": R, "rho": a.rho,
                    "active_rows_per_layer": A_mean * world if world > 1 else A_mean,
                    "nonzero_hidden_per_layer": Z_mean * world if world > 1 else Z_mean,
-                   "sharding": f"neuron groups of {GROUP} over {world} GPU(s), one allreduce of y per layer"
+                   "sharding": f"neuron groups of {GROUP} over {world} GPU(s), one sum of y over shards per layer ({st.exchange})"
                    if world > 1 else "all neurons resident on 1 GPU",
                    "schedule": a.schedule, "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
                          ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool},

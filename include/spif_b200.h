@@ -163,6 +163,30 @@ typedef struct spif_ffn_args {
 
 int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif_stream_t stream);
 
+/* ---- neuron-sharded layers: the per-layer exchange (the reference is single-GPU, src/llama-sparkinfer.cpp:129)
+ * Each GPU holds the rows of a subset of neurons and produces a partial y; the sum over GPUs is a one-shot exchange over
+ * NVLink peer memory: every rank stores its chunk, as 8-byte {value, sequence number} words, into its slot of every peer's
+ * exchange buffer; the receiver polls the words themselves (no flag, no fence, one NVLink hop) and adds the slots in RANK
+ * ORDER (bit-identical on all ranks, run-to-run stable).  In spif_sparse_ffn_sharded this is the epilogue of the kernel
+ * that sums the per-CTA partials (one kernel does both); spif_shard_allreduce is the stand-alone form.  Buffers are owned by
+ * the caller: data[r] is rank r's buffer as mapped into THIS process (CUDA IPC / VMM / torch symmetric memory),
+ * zero-initialised before first use; seq is local.  Calls on the same buffers must be stream-ordered.                  */
+#define SPIF_COMM_MAX_WORLD  8
+#define SPIF_COMM_MAX_BLOCKS 1024
+typedef struct spif_shard_comm {
+    int32_t rank, world;     /* world <= SPIF_COMM_MAX_WORLD */
+    int32_t cap_floats;      /* capacity of one slot in floats (>= n_tok * n_embd, multiple of 4) */
+    int32_t reserved;
+    void *  data[SPIF_COMM_MAX_WORLD];  /* 8-byte words [2][world][cap_floats]  (spif_shard_comm_data_bytes), 16-byte aligned */
+    void *  seq;                        /* local uint32_t [SPIF_COMM_MAX_BLOCKS], zero-initialised                            */
+} spif_shard_comm;
+size_t spif_shard_comm_data_bytes(int world, int cap_floats);
+/* y[0..n) = sum over ranks of y, in place; n % 4 == 0, n <= cap_floats */
+int spif_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, spif_stream_t stream);
+/* spif_sparse_ffn on this rank's rows + the exchange: args->y receives the FULL layer output on every rank */
+int spif_sparse_ffn_sharded(const spif_ffn_args * args, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
+                            spif_stream_t stream);
+
 /* ---- balancer helpers (build_dfr, src/llama-graph.cpp:910-930; binbcast.cu:26-42; sumcols.cu; argsort.cu) ---------
  * One fused kernel: per group of `g` consecutive neurons, delta = #(active, token) pairs, then
  *   ema != 0 : dfr = lambda*dfr + (1-lambda)*delta/(n_tok*g)        (SPIF_DFR_EMA variant, binbcast.cu:28-34)

@@ -21,6 +21,12 @@ class FfnArgs(ctypes.Structure):
     ]
 
 
+class ShardCommStruct(ctypes.Structure):
+    """struct spif_shard_comm (include/spif_b200.h)"""
+    _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("cap_floats", ctypes.c_int32),
+                ("reserved", ctypes.c_int32), ("data", c_vp * 8), ("seq", c_vp)]
+
+
 # name -> (restype, argtypes); every symbol include/spif_b200.h declares
 SYMBOLS = {
     "spif_abi_version": (c_i, []),
@@ -37,6 +43,9 @@ SYMBOLS = {
     "spif_predictor": (c_i, [c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i, c_vp, c_sz, c_vp]),
     "spif_sparse_ffn": (c_i, [ctypes.POINTER(FfnArgs), c_vp, c_sz, c_vp]),
     "spif_dfr_update": (c_i, [c_vp, c_i, c_i, c_i, c_f, c_f, c_i, c_vp, c_vp]),
+    "spif_shard_comm_data_bytes": (c_sz, [c_i, c_i]),
+    "spif_shard_allreduce": (c_i, [c_vp, c_i64, ctypes.POINTER(ShardCommStruct), c_vp]),
+    "spif_sparse_ffn_sharded": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
 }
 
 _lib = None

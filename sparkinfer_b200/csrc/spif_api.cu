@@ -9,6 +9,7 @@ int spif_launch_ffn_q(const spif_ffn_args & a, int mode, const float * hid_in, f
                       size_t ws_bytes, const spif_launch_ctx & ctx);
 int    spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx);
 size_t spif_batch_workspace_bytes(int n_embd, int n_ff, int n_tok);
+int    spif_launch_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, cudaStream_t stream);
 
 static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
     int dev = 0;
@@ -30,6 +31,7 @@ static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
     ctx.sm_count       = cached_sm[slot];
     ctx.max_smem_optin = cached_smem[slot];
     ctx.stream         = (cudaStream_t) stream;
+    ctx.comm           = nullptr;
     return 0;
 }
 
@@ -250,7 +252,8 @@ int spif_predictor(int ptype, const void * wpu, const float * bpu, const void * 
                                  ws, ws_bytes, ctx);
 }
 
-int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif_stream_t stream) {
+static int sparse_ffn_impl(const spif_ffn_args * args, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
+                           spif_stream_t stream) {
     SPIF_REQUIRE(args != nullptr, SPIF_E_NULL);
     const spif_ffn_args & a = *args;
     int rc = check_common(a.type, a.w_up, a.sparse_idx, a.n_embd, a.n_ff, a.m, a.n_tok, a.neuron_idx);
@@ -270,12 +273,40 @@ int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif
     if (a.n_tok >= 2 && !(a.flags & SPIF_FLAG_PER_TOKEN)) {
         // batched / prefill: union of the per-token masks -> gathered GEMM on tensor cores, each row read once
         rc = spif_launch_ffn_batch(a, ws, ws_bytes, ctx);
+        if (rc == 0 && comm) {
+            rc = spif_launch_shard_allreduce(a.y, (int64_t) a.n_embd * a.n_tok, comm, ctx.stream);
+        }
         if (rc != SPIF_E_UNSUPPORTED) {
             return rc;
         }
     }
+    ctx.comm = comm;  // the kernel that sums the per-CTA partials also sums over the shards
     return is_float_type(a.type) ? spif_launch_ffn(a, SPIF_MODE_FUSED, nullptr, nullptr, ws, ws_bytes, ctx) :
                                    spif_launch_ffn_q(a, SPIF_MODE_FUSED, nullptr, nullptr, ws, ws_bytes, ctx);
+}
+
+int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif_stream_t stream) {
+    return sparse_ffn_impl(args, nullptr, ws, ws_bytes, stream);
+}
+
+int spif_sparse_ffn_sharded(const spif_ffn_args * args, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
+                            spif_stream_t stream) {
+    SPIF_REQUIRE(comm != nullptr, SPIF_E_NULL);
+    return sparse_ffn_impl(args, comm, ws, ws_bytes, stream);
+}
+
+size_t spif_shard_comm_data_bytes(int world, int cap_floats) {
+    return (world < 1 || cap_floats < 1) ? 0 : 8 * 2 * (size_t) world * (size_t) cap_floats;
+}
+
+int spif_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, spif_stream_t stream) {
+    SPIF_REQUIRE(comm != nullptr, SPIF_E_NULL);
+    spif_launch_ctx ctx;
+    int             rc = make_ctx(ctx, stream);
+    if (rc) {
+        return rc;
+    }
+    return spif_launch_shard_allreduce(y, n, comm, ctx.stream);
 }
 
 int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,

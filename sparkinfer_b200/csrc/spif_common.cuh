@@ -193,6 +193,7 @@ struct spif_launch_ctx {
     int          sm_count;
     int          max_smem_optin;
     cudaStream_t stream;
+    const spif_shard_comm * comm;  // non-NULL: the fused layer's partial-sum kernel also sums over the GPU shards
 };
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel instantiation, device): `done` is a per-instantiation

@@ -21,6 +21,7 @@
 //     partials in a fixed order -> run-to-run bit-stable, unlike axpy-sparse.cu:84.
 #include "spif_ffn_kernel.cuh"
 #include "spif_ffn_direct.cuh"
+#include "spif_comm.cuh"
 
 unsigned long long * g_spif_trace = nullptr;  // debug only; see tools/trace_ffn.py
 extern "C" void spif_debug_set_trace(void * dev_ptr) {
@@ -34,9 +35,12 @@ extern "C" void spif_debug_set_trace(void * dev_ptr) {
 #define SPIF_RED_COLS  8
 #define SPIF_RED_LANES 32
 #define SPIF_RED_PER   10 /* ceil(P / 32) for P <= 320 CTAs */
+// COMM: the block's 32 finished columns are not written to y but pushed into every shard's exchange buffer; the same block
+// then waits for the peers' flags and writes the sum over shards (spif_comm.cuh) -- partial sum + allreduce in ONE kernel.
+template <bool COMM>
 __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_partials_kernel(
     const float * __restrict__ partials, const float * __restrict__ b_down, float * __restrict__ y,
-    const int32_t * __restrict__ cta_stats, int32_t * __restrict__ stats_out, int n_embd, int P) {
+    const int32_t * __restrict__ cta_stats, int32_t * __restrict__ stats_out, int n_embd, int P, const spif_comm_dev comm) {
     __shared__ float4 sm[SPIF_RED_LANES][SPIF_RED_COLS];
     __shared__ float4 sm2[4][SPIF_RED_COLS];
     const int         tok  = blockIdx.y;
@@ -72,8 +76,10 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
         sm2[py][cx] = t;
     }
     __syncthreads();
-    if (py == 0 && col4 < n4) {
-        float4 t = sm2[0][cx];
+    float4     t   = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool own = (py == 0 && col4 < n4);
+    if (own) {
+        t = sm2[0][cx];
 #pragma unroll
         for (int k = 1; k < 4; ++k) {
             const float4 v = sm2[k][cx];
@@ -83,6 +89,11 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
             const float4 bb = reinterpret_cast<const float4 *>(b_down)[col4];
             t.x += bb.x, t.y += bb.y, t.z += bb.z, t.w += bb.w;
         }
+    }
+    if (COMM) {
+        t = spif_peer_allreduce_f4(comm, t, tok * n4 + col4, own, blockIdx.x + gridDim.x * blockIdx.y);
+    }
+    if (own) {
         reinterpret_cast<float4 *>(y + (size_t) tok * n_embd)[col4] = t;
     }
     if (stats_out && blockIdx.x == 0 && threadIdx.x < 32) {
@@ -142,7 +153,7 @@ static int launch_float(int type, int mode, int vpt, const FfnKParams & kp, dim3
 }
 
 static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y, int32_t * stats_out, int n_embd, int n_tok,
-                         int P, cudaStream_t stream) {
+                         int P, cudaStream_t stream, const spif_shard_comm * comm = nullptr) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = dim3((n_embd / 4 + SPIF_RED_COLS - 1) / SPIF_RED_COLS, n_tok);
     cfg.blockDim           = dim3(SPIF_RED_COLS * SPIF_RED_LANES);
@@ -152,8 +163,20 @@ static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y,
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs                                        = at;
     cfg.numAttrs                                     = 1;
-    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel, (const float *) kp.partials, b_down, y,
-                                     (const int32_t *) kp.cta_stats, stats_out, n_embd, P));
+    spif_comm_dev cd = {};
+    if (comm) {
+        int rc = spif_comm_to_dev(comm, cd);
+        if (rc) {
+            return rc;
+        }
+        SPIF_REQUIRE((int64_t) n_embd * n_tok <= comm->cap_floats, SPIF_E_WORKSPACE);
+        SPIF_REQUIRE(cfg.gridDim.x * cfg.gridDim.y <= SPIF_COMM_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
+        SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel<true>, (const float *) kp.partials, b_down, y,
+                                         (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd));
+        return 0;
+    }
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel<false>, (const float *) kp.partials, b_down, y,
+                                     (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd));
     return 0;
 }
 
@@ -266,7 +289,8 @@ int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_
     }
     if (mode != SPIF_MODE_GEMV) {
         return launch_reduce(kp, (mode == SPIF_MODE_FUSED) ? a.b_down : (const float *) nullptr,
-                             (mode == SPIF_MODE_AXPY) ? dst_dense : a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream);
+                             (mode == SPIF_MODE_AXPY) ? dst_dense : a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream,
+                             (mode == SPIF_MODE_FUSED) ? ctx.comm : nullptr);
     }
     return 0;
 }
@@ -344,7 +368,7 @@ static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_
     if (rc) {
         return rc;
     }
-    return launch_reduce(kp, a.b_down, a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream);
+    return launch_reduce(kp, a.b_down, a.y, a.stats_out, a.n_embd, a.n_tok, P, ctx.stream, ctx.comm);
 }
 
 // F16 / BF16 entry: thread shape = VPT 16-byte vectors per consumer thread

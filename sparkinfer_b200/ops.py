@@ -18,7 +18,7 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import FfnArgs, check
+from ._lib import FfnArgs, ShardCommStruct, check
 
 GGML_TYPE_F32, GGML_TYPE_F16, GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_BF16 = 0, 1, 2, 8, 30
 ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
@@ -49,6 +49,48 @@ class Workspace:
         self.buf = torch.empty(self.nbytes + 256, dtype=torch.uint8, device=device)
         off = (-self.buf.data_ptr()) % 256
         self.ptr = ctypes.c_void_p(self.buf.data_ptr() + off)
+
+
+class ShardComm:
+    """Exchange buffers of the per-layer sum over GPU shards (struct spif_shard_comm).  The buffers are symmetric memory:
+    every rank allocates the same layout and maps all peers' copies (torch.distributed._symmetric_memory is plumbing for
+    the CUDA VMM / IPC handle exchange; the exchange itself is done by our kernels over NVLink peer stores).  world == 1
+    works without torch.distributed (self-exchange; used by the single-GPU tests)."""
+
+    MAX_BLOCKS = 1024
+
+    def __init__(self, cap_floats, group=None, device="cuda"):
+        L = _lib.load()
+        cap = (int(cap_floats) + 3) // 4 * 4
+        world = 1 if group is None else torch.distributed.get_world_size(group)
+        rank = 0 if group is None else torch.distributed.get_rank(group)
+        data_b = (L.spif_shard_comm_data_bytes(world, cap) + 255) // 256 * 256
+        if group is None:
+            self.buf = torch.zeros(data_b, dtype=torch.uint8, device=device)
+            ptrs = [self.buf.data_ptr()]
+            self.handle = None
+        else:
+            import torch.distributed._symmetric_memory as symm
+            self.buf = symm.empty(data_b, dtype=torch.uint8, device=device)
+            self.buf.zero_()
+            self.handle = symm.rendezvous(self.buf, group)
+            ptrs = [int(p) for p in self.handle.buffer_ptrs]
+            torch.cuda.synchronize()
+            torch.distributed.barrier(group)  # everybody's buffers are zero before anyone stores into them
+        self.seq = torch.zeros(self.MAX_BLOCKS, dtype=torch.int32, device=device)
+        c = ShardCommStruct()
+        c.rank, c.world, c.cap_floats, c.reserved = rank, world, cap, 0
+        for r in range(world):
+            c.data[r] = ptrs[r]
+        c.seq = self.seq.data_ptr()
+        self.c = c
+        self.rank, self.world, self.cap = rank, world, cap
+
+
+def shard_allreduce(y, comm):
+    """y = sum over shards of y, in place (spif_shard_allreduce: one-shot exchange over peer memory, rank-order sum)"""
+    check(_lib.load().spif_shard_allreduce(_p(y), y.numel(), ctypes.byref(comm.c), _stream()), "spif_shard_allreduce")
+    return y
 
 
 def _ws(ws, n_embd, n_ff, n_tok, device):
@@ -135,7 +177,7 @@ def predictor(pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, n_ff, 
 
 def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx=None, up_b=None, gate_b=None,
                down_b=None, thr=SPARSE_THRESHOLD, flags=0, want_hidden=False, want_stats=False, ws=None, out=None,
-               stats=None):
+               stats=None, comm=None):
     """build_sparse_ffn for the rows resident on this device.  -> y {n_embd, n_tok} [, hidden {n_ff, n_tok}][, stats]"""
     L = _lib.load()
     n_tok, n_embd = cur.shape
@@ -149,7 +191,11 @@ def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx
                 w_up=_p(up), w_gate=_p(gate), w_down_t=_p(down_t), b_up=_p(up_b), b_gate=_p(gate_b), b_down=_p(down_b),
                 x=_p(cur), sparse_idx=_p(sparse_idx), neuron_idx=_p(neuron_idx), y=_p(y), hidden_out=_p(hid),
                 stats_out=_p(stats))
-    check(L.spif_sparse_ffn(ctypes.byref(a), ws.ptr, ws.nbytes, _stream()), "spif_sparse_ffn")
+    if comm is not None:  # sharded layer: y is the sum over all shards on return (spif_sparse_ffn_sharded)
+        check(L.spif_sparse_ffn_sharded(ctypes.byref(a), ctypes.byref(comm.c), ws.ptr, ws.nbytes, _stream()),
+              "spif_sparse_ffn_sharded")
+    else:
+        check(L.spif_sparse_ffn(ctypes.byref(a), ws.ptr, ws.nbytes, _stream()), "spif_sparse_ffn")
     res = [y]
     if want_hidden:
         res.append(hid)

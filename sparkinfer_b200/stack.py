@@ -30,12 +30,25 @@ class FfnStack:
     """n_layer sparse FFNs + predictors for one decode step (n_tok tokens)"""
 
     def __init__(self, arch, w_type, p_type, n_embd, n_ff_local, r, layers, n_tok=1, group=None, device="cuda",
-                 flags=0):
+                 flags=0, exchange="nccl"):
         self.arch, self.w_type, self.p_type = arch, w_type, p_type
         self.n_embd, self.m, self.r, self.n_tok = n_embd, n_ff_local, r, n_tok
         self.layers = layers
         self.L = len(layers)
         self.group = group  # torch.distributed process group (None: single GPU)
+        # per-layer sum over the shards: "peer" = fused into the layer's partial-sum kernel over NVLink peer memory
+        # (spif_sparse_ffn_sharded), "nccl" = one ncclAllReduce per layer
+        self.comm = None
+        if group is not None and exchange == "peer":
+            try:
+                comm = ops.ShardComm(n_tok * n_embd, group, device)
+            except Exception as e:  # symmetric memory not available here: every rank must take the same decision
+                comm = None
+                print(f"[sparkinfer_b200] peer exchange unavailable ({type(e).__name__}: {e}); using ncclAllReduce", flush=True)
+            ok = torch.tensor([1 if comm is not None else 0], device=device)
+            torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN, group=group)
+            self.comm = comm if int(ok.item()) == 1 else None
+        self.exchange = "peer" if self.comm is not None else ("nccl" if group is not None else "none")
         self.flags = flags
         self.ws = ops.Workspace(n_embd, n_ff_local, n_tok, device)
         self.x = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)
@@ -56,15 +69,16 @@ class FfnStack:
                       flags=self.flags, ws=self.ws_pred, out=self.p[l])
         return 2  # kernels: predictor up GEMV, predictor down GEMV+sigmoid
 
-    def ffn(self, l, want_stats=False, mask_stable=False):
+    def ffn(self, l, want_stats=False, mask_stable=False, exchange=False):
         w = self.layers[l]
         fl = self.flags | (ops.FLAG_MASK_STABLE if mask_stable else 0)
         ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=fl,
-                       ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None)
-        return 2  # kernels: fused gate/up/act/down, partial reduction
+                       ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None,
+                       comm=self.comm if exchange else None)
+        return 2  # kernels: fused gate/up/act/down, partial reduction (+ shard exchange)
 
     def allreduce(self, l):
-        if self.group is not None:
+        if self.group is not None and self.comm is None:
             torch.distributed.all_reduce(self.y[l], group=self.group)
 
     # -- one decode step ----------------------------------------------------------------------------------------
@@ -74,7 +88,7 @@ class FfnStack:
             if l + 1 < self.L:
                 n += self.predict(l + 1, l)  # look-ahead, llama-graph.cpp:939-946
             # the mask of layer l was written >= 2 launches ago (the look-ahead predictor of l+1 sits in between)
-            n += self.ffn(l, want_stats, mask_stable=(l + 1 < self.L) and self.early_mask)
+            n += self.ffn(l, want_stats, mask_stable=(l + 1 < self.L) and self.early_mask, exchange=True)
             self.allreduce(l)
         self.launches_per_step = n
         return n
@@ -100,7 +114,7 @@ class FfnStack:
                 evs.append(e)
         for l in range(self.L):
             main.wait_event(evs[l])
-            n += self.ffn(l, False, mask_stable=self.early_mask)  # full edge from predictor l: the mask is complete
+            n += self.ffn(l, False, mask_stable=self.early_mask, exchange=True)  # full edge from predictor l
             self.allreduce(l)
         main.wait_stream(side)
         self.launches_per_step = n

@@ -118,3 +118,25 @@ def test_batched_quant_sparse_ffn(oracle, arch, wtype, n_embd, n_ff, n_tok, rho)
     assert np.all(stats[:, 2] == int(act.any(axis=0).sum()))
     y2 = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, ws=ws)
     assert np.array_equal(y, y2.cpu().numpy())
+
+
+def test_shard_exchange_single_rank_self_exchange(oracle):
+    """world = 1 exercises the whole peer protocol against this GPU's own buffers (slots, flags, sequence numbers, parity
+    reuse over many calls): the fused partial-sum + exchange kernel and the stand-alone form must reproduce the plain
+    layer bit for bit.  The 2-GPU run is tools/test_peer_exchange.py under torchrun."""
+    import sparkinfer_b200 as sp
+    n_embd, n_ff = 1024, 2048
+    seed = synth.SEED0 + 5
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (dev(oracle.quantize(F16, w)) for w in (Wu, Wg, Wd))
+    comm = sp.ShardComm(8 * n_embd)
+    for n_tok in (1, 8):
+        x = dev(synth.activations(n_embd, n_tok, seed + 1))
+        p = dev(synth.direct_mask(n_ff, n_tok, 0.15, seed + 2))
+        ws = sp.Workspace(n_embd, n_ff, n_tok)
+        y0 = sp.sparse_ffn(ARCH_PROSPARSE, F16, qu, qg, qd, x, p, n_ff, ws=ws)
+        for _ in range(5):  # odd and even sequence numbers
+            y1 = sp.sparse_ffn(ARCH_PROSPARSE, F16, qu, qg, qd, x, p, n_ff, ws=ws, comm=comm)
+            assert torch.equal(y0, y1)
+        y2 = sp.shard_allreduce(y0.clone(), comm)
+        assert torch.equal(y0, y2)

@@ -338,56 +338,72 @@ def run_ours(a):
 
 
 def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
-    """decode at batch T > 1 (BASELINE.json configs[2] shape, on this run's weights): per-token masks from the synthetic
-    predictor, then one spif_sparse_ffn call per layer -- the union-of-masks gathered GEMM on tcgen05 tensor cores (every
-    union row read once) next to the reference's per-(row, token) schedule (mm-sparse.cu:107-210, T x the row traffic).
-    Bytes = (2 A_u + Z_u) * row_bytes with A_u / Z_u the union rows / union rows with a non-zero hidden value."""
+    """decode at batch T > 1 (BASELINE.json configs[2]: Q4_0 at batch 1/8/32; the F16 weights of this run as well):
+    per-token masks from the synthetic predictor, then one spif_sparse_ffn call per layer -- the union-of-masks gathered GEMM
+    on tcgen05 tensor cores (every union row read once) next to the reference's per-(row, token) schedule
+    (mm-sparse.cu:107-210, T x the row traffic).  Bytes = (2 A_u + Z_u) * row_bytes with A_u / Z_u the union rows / union
+    rows with a non-zero hidden value.  Q4_0 weights are random valid block_q4_0 bytes (random-init, like the F16 ones)."""
     import torch
     import sparkinfer_b200 as sp
     E, F = wl["n_embd"], st.m
     nl = min(n_layers, st.L)
     res = []
     gen = torch.Generator(device=device).manual_seed(a.seed + 77)
-    for T in batches:
-        x = torch.randn((T, E), device=device, generator=gen)
-        ws = sp.Workspace(E, F, T)
-        y = torch.empty((T, E), device=device)
-        masks = [sp.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, x, st.p_type, st.r, F, ws=ws).clone()
-                 for w in st.layers[:nl]]
-        stats = [torch.zeros((T, 4), dtype=torch.int32, device=device) for _ in range(nl)]
-        leg = {"n_tok": T, "layers_timed": nl}
-        for name, flags in (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN)):
-            def run():
-                for l, w in enumerate(st.layers[:nl]):
-                    sp.sparse_ffn(st.arch, st.w_type, w.up, w.gate, w.down_t, x, masks[l], F, flags=flags, ws=ws, out=y,
-                                  stats=stats[l], want_stats=True)
-            run()
-            torch.cuda.synchronize()
-            sn = torch.stack(stats).cpu().numpy()
-            g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream(device=device)
-            with torch.cuda.stream(side):
+
+    def q4_rows():
+        nb = E // 32
+        blk = torch.randint(0, 256, (F, nb, 18), dtype=torch.uint8, device=device, generator=gen)
+        d = torch.full((F, nb, 1), 0.02 / 6, dtype=torch.float16, device=device)
+        blk[:, :, :2] = d.view(torch.uint8).reshape(F, nb, 2)
+        return blk.reshape(F, nb * 18).contiguous()
+
+    f16 = [(w.up, w.gate, w.down_t) for w in st.layers[:nl]]
+    q4 = [(q4_rows(), q4_rows(), q4_rows()) for _ in range(nl)] if E % 512 == 0 else None
+    for wname, wtype, rb, weights, Ts in (("f16", st.w_type, 2 * E, f16, batches),
+                                          ("q4_0", sp.GGML_TYPE_Q4_0, E // 32 * 18, q4, (1,) + tuple(batches))):
+        if weights is None:
+            continue
+        for T in Ts:
+            x = torch.randn((T, E), device=device, generator=gen)
+            ws = sp.Workspace(E, F, T)
+            y = torch.empty((T, E), device=device)
+            masks = [sp.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, x, st.p_type, st.r, F, ws=ws).clone()
+                     for w in st.layers[:nl]]
+            stats = [torch.zeros((T, 4), dtype=torch.int32, device=device) for _ in range(nl)]
+            leg = {"weights": wname, "n_tok": T, "layers_timed": nl}
+            for name, flags in ((("per_token", sp.FLAG_PER_TOKEN),) if T == 1 else
+                                (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN))):
+                def run():
+                    for l in range(nl):
+                        u, g_, d_ = weights[l]
+                        sp.sparse_ffn(st.arch, wtype, u, g_, d_, x, masks[l], F, flags=flags, ws=ws, out=y, stats=stats[l],
+                                      want_stats=True)
                 run()
-                side.synchronize()
-                with torch.cuda.graph(g, stream=side):
+                torch.cuda.synchronize()
+                sn = torch.stack(stats).cpu().numpy()
+                g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream(device=device)
+                with torch.cuda.stream(side):
                     run()
-            torch.cuda.synchronize()
-            for _ in range(3):
-                g.replay()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(reps):
-                g.replay()
-            e1.record()
-            torch.cuda.synchronize()
-            us = e0.elapsed_time(e1) * 1e3 / reps / nl
-            if name == "union_gemm":
-                rows = float((2 * sn[:, 0, 2] + sn[:, 0, 3]).mean())
-                leg["union_rows"] = float(sn[:, 0, 2].mean())
-            else:
-                rows = float((2 * sn[:, :, 0] + sn[:, :, 1]).sum(axis=1).mean())
-            leg[name] = {"us_per_layer": us, "ffn_tok_s": T / (us * st.L) * 1e6,
-                         "algorithmic_GBps": rows * 2 * E / us / 1e3}
-        res.append(leg)
+                    side.synchronize()
+                    with torch.cuda.graph(g, stream=side):
+                        run()
+                torch.cuda.synchronize()
+                for _ in range(3):
+                    g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(reps):
+                    g.replay()
+                e1.record()
+                torch.cuda.synchronize()
+                us = e0.elapsed_time(e1) * 1e3 / reps / nl
+                if name == "union_gemm":
+                    rows = float((2 * sn[:, 0, 2] + sn[:, 0, 3]).mean())
+                    leg["union_rows"] = float(sn[:, 0, 2].mean())
+                else:
+                    rows = float((2 * sn[:, :, 0] + sn[:, :, 1]).sum(axis=1).mean())
+                leg[name] = {"us_per_layer": us, "ffn_tok_s": T / (us * st.L) * 1e6, "algorithmic_GBps": rows * rb / us / 1e3}
+            res.append(leg)
     return res
 
 

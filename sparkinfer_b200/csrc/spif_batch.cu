@@ -795,6 +795,9 @@ static int launch_batch_t(const BatchParams & bp, int P, const spif_launch_ctx &
 int spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
     const bool quant = a.type == SPIF_TYPE_Q8_0 || a.type == SPIF_TYPE_Q4_0;
     SPIF_REQUIRE(a.type == SPIF_TYPE_F16 || a.type == SPIF_TYPE_BF16 || quant, SPIF_E_UNSUPPORTED);
+    // Q8_0/Q4_0 with SPIF_FLAG_CPU_ROUNDING asks for the reference CPU arithmetic (x quantised to 8-bit blocks, integer
+    // dots): only the per-token kernel reproduces that; the union GEMM multiplies dequantised weights by F16 activations
+    SPIF_REQUIRE(!(quant && (a.flags & SPIF_FLAG_CPU_ROUNDING)), SPIF_E_UNSUPPORTED);
     SPIF_REQUIRE(a.n_tok >= 2 && a.n_tok <= 32, SPIF_E_UNSUPPORTED);
     const int P = ctx.sm_count;
     SPIF_REQUIRE(a.n_embd % 512 == 0 && (a.n_embd >> 9) <= P && a.m <= SPIF_B_ROWS_MAX * P, SPIF_E_UNSUPPORTED);

@@ -343,6 +343,7 @@ static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_
     kp.arch       = a.arch;
     kp.flags      = a.flags;
     kp.dense_out  = a.hidden_out;
+    kp.trace      = g_spif_trace;
     kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;
     kp.list_cap   = (a.m + P - 1) / P + 1;
     const size_t part_bytes = sizeof(float) * (size_t) a.n_tok * P * a.n_embd;

@@ -34,9 +34,11 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
 
     const bool gated = (p.arch != SPIF_ARCH_RELU_UP);
     const bool early = (p.flags & SPIF_FLAG_MASK_STABLE) != 0;
+    SPIF_STAMP(0);
     if (!early) {
         pdl_wait_prior_grid();
     }
+    SPIF_STAMP(1);
     const float * mask  = p.mask + (size_t) tok * p.mask_len;
     const float * xg    = p.x + (size_t) tok * p.n_embd;
     float *       dense = p.dense_out ? p.dense_out + (size_t) tok * p.n_ff : nullptr;
@@ -44,6 +46,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
                                                         s_counts);
     const int n  = s_counts[0];
     const int nb = (n + NB - 1) / NB;
+    SPIF_STAMP(2);
     const int V  = p.n_embd >> 3;
 
     // this thread's vectors: v = tid + k * NT
@@ -206,10 +209,14 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
 
     for (int b = 0; b < nb; b += 2) {
         iteration(b, GU[0], DN[0], alpha[0], red);
+        if (b == 0) {
+            SPIF_STAMP(3);
+        }
         if (b + 1 < nb) {
             iteration(b + 1, GU[1], DN[1], alpha[1], red + NB * 2 * 32);
         }
     }
+    SPIF_STAMP(4);
     axpy_prev(DN[0], alpha[0]);
     axpy_prev(DN[1], alpha[1]);
 
@@ -227,5 +234,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
         int32_t * st = p.cta_stats + ((size_t) tok * P + c) * 2;
         st[0]        = s_counts[1];
         st[1]        = n_nonzero;
+    }
+    SPIF_STAMP(5);
+    if (p.trace && tid == 0 && blockIdx.y == 0) {
+        p.trace[(size_t) blockIdx.x * 8 + 6] = (unsigned long long) n;
     }
 }

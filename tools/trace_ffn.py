@@ -53,7 +53,7 @@ def main():
             run(l)
         torch.cuda.synchronize()
     setter(None)
-    names = ["entry->pdlwait", "pdlwait->list", "list->first_full", "first_full->gu_done", "gu_done->end"]
+    names = ["entry->pdlwait", "pdlwait->list", "list->first_batch", "first_batch->loop_done", "loop_done->end"]
     for l in range(L):
         t = traces[l].cpu().numpy()
         t0 = t[:, 0].min()

@@ -36,6 +36,9 @@ WORKLOADS = {
     "prosparse-13b": dict(n_embd=5120, n_ff=13824, n_layer=40, arch=0, label="ProSparse-Llama-2-13B FP16 bs=1 decode"),
     "prosparse-7b": dict(n_embd=4096, n_ff=11008, n_layer=32, arch=0, label="ProSparse-Llama-2-7B FP16 bs=1 decode"),
     "relullama-70b": dict(n_embd=8192, n_ff=28672, n_layer=80, arch=0, label="ReluLLaMA-70B FP16 bs=1 decode"),
+    # configs[3]: SiLU gate, mask = top-k of the predictor logits (k = rho * n_ff); no reference code path for it
+    "llama3-8b-topk": dict(n_embd=4096, n_ff=14336, n_layer=32, arch=3, topk=True,
+                           label="Llama-3-8B SiLU top-k FP16 bs=1 decode"),
 }
 GROUP = 16  # neurons per placement group
 
@@ -168,7 +171,7 @@ def build_stack(a, wl, rank, world, device):
                                    pred_down=half(m, R, R ** -0.5), pred_down_b=bpd, m=m))
     group = torch.distributed.group.WORLD if world > 1 else None
     st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device,
-                  exchange=a.exchange)
+                  exchange=a.exchange, topk=int(a.rho * m) if wl.get("topk") else 0)
     return st, expect
 
 
@@ -435,9 +438,9 @@ def cpu_stack_tok_s(a, wl, iters, warmup):
     wl_L = wl["n_layer"]
     nl = min(a.cpu_layers, wl_L)
     cores = os.cpu_count() or 1
-    if oracle_lib.Ref.available():
+    if oracle_lib.Ref.available() and wl["arch"] != 3:
         lib, kind = oracle_lib.Ref(), "reference"
-    else:
+    else:  # (the reference has no SiLU / top-k path: the port times threshold masks with the SiLU recipe there)
         lib, kind = oracle_lib.Oracle(), "port"
     up, gate, down, wpu, wpd, bpd, x = host_layers(a, wl, nl)
     us, _ = oracle_lib.stack_time(lib, wl["arch"], F16, F16, up, gate, down, wpu, wpd, bpd, x, wl["n_embd"], wl["n_ff"],

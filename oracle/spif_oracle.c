@@ -660,6 +660,9 @@ void spifo_activation(int arch, const float * up, const float * gate, const floa
                 case SPIFO_ARCH_RELU_GATED:
                     hid[k] = ((g > 0.f) ? g : 0.f) * ((u > 0.f) ? u : 0.f);
                     break;
+                case SPIFO_ARCH_SILU_GATED: /* no reference code (llama-graph.cpp:1092-1093 aborts): parity unpinned */
+                    hid[k] = (g / (1.0f + expf(-g))) * u;
+                    break;
                 default:
                     hid[k] = (u > 0.f) ? u : 0.f;
                     break;
@@ -753,6 +756,9 @@ int spifo_sparse_ffn_f64(int arch, int type, const void * w_up, const void * w_g
                 case SPIFO_ARCH_RELU_GATED:
                     h = (g > 0 ? g : 0) * (u > 0 ? u : 0);
                     break;
+                case SPIFO_ARCH_SILU_GATED:
+                    h = (g / (1.0 + exp(-g))) * u;
+                    break;
                 default:
                     h = u > 0 ? u : 0;
                     break;
@@ -812,6 +818,7 @@ static void layer_mt(int arch, int type, const void * wu, const void * wg, const
             }
             h = arch == SPIFO_ARCH_PROSPARSE ? ((g > 0.01f) ? g : 0.f) * u :
                 arch == SPIFO_ARCH_RELU_GATED ? ((g > 0.f) ? g : 0.f) * ((u > 0.f) ? u : 0.f) :
+                arch == SPIFO_ARCH_SILU_GATED ? (g / (1.0f + expf(-g))) * u :
                                                 ((u > 0.f) ? u : 0.f);
             hid[n] = h;
             float alpha = type == SPIFO_F16 ? h2f(f2h(h)) : type == SPIFO_BF16 ? bf2f(f2bf(h)) : h;

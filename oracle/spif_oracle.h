@@ -11,7 +11,8 @@ extern "C" {
 /* ggml type ids (ggml/include/ggml.h:385-415) */
 enum { SPIFO_F32 = 0, SPIFO_F16 = 1, SPIFO_Q4_0 = 2, SPIFO_Q8_0 = 8, SPIFO_BF16 = 30 };
 /* arch activation recipes (src/llama-graph.cpp:1063-1094) */
-enum { SPIFO_ARCH_PROSPARSE = 0, SPIFO_ARCH_RELU_GATED = 1, SPIFO_ARCH_RELU_UP = 2 };
+enum { SPIFO_ARCH_PROSPARSE = 0, SPIFO_ARCH_RELU_GATED = 1, SPIFO_ARCH_RELU_UP = 2,
+       SPIFO_ARCH_SILU_GATED = 3 /* Llama-3 / top-k config: no reference code path, parity unpinned */ };
 
 const char * spifo_describe(void);
 size_t       spifo_row_size(int type, int64_t n);

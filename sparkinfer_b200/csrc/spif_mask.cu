@@ -126,24 +126,56 @@ __global__ void __launch_bounds__(1024) spif_topk_mask_kernel(const float * __re
         __syncthreads();
         const uint32_t pre = s_prefix, pmask = s_prefix_mask;
         const int      sh  = pass * 8;
-        for (int i = tid; i < n_ff; i += blockDim.x) {
-            const uint32_t key = float_key(sc[i]);
-            if ((key & pmask) == pre) {
-                atomicAdd(&hist[(key >> sh) & 255], 1);
+        // histogram of the current digit among the keys that still match the prefix.  The top digit (sign + exponent) has
+        // a handful of distinct values, so lanes with the same digit are merged first (match_any) and ONE lane adds the
+        // group's size: without it this pass serialises ~n_ff shared-memory atomics on 3-4 addresses.
+        for (int base = 0; base < n_ff; base += blockDim.x) {
+            const int      i   = base + tid;
+            const uint32_t key = (i < n_ff) ? float_key(sc[i]) : 0u;
+            const bool     in  = (i < n_ff) && ((key & pmask) == pre);
+            const unsigned dig = in ? ((key >> sh) & 255u) : (0x1000u + lane);
+            if (pass == 3) {
+                const unsigned grp = __match_any_sync(0xffffffffu, dig);
+                if (in && (__ffs(grp) - 1) == lane) {
+                    atomicAdd(&hist[dig], __popc(grp));
+                }
+            } else if (in) {  // lower digits are well spread and few keys still match the prefix
+                atomicAdd(&hist[dig], 1);
             }
         }
         __syncthreads();
-        if (tid == 0) {
-            int need = s_k, b = 255;
-            for (; b > 0; --b) {
-                if (hist[b] >= need) {
-                    break;
-                }
-                need -= hist[b];
+        if (warp == 0) {
+            // lane l owns digits 8l .. 8l+7; suffix sums over the lanes above, then the lane holding the k-th key scans its 8
+            int own[8], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                own[j] = hist[lane * 8 + j];
+                sum += own[j];
             }
-            s_k           = need;  // how many to take among keys with this prefix digit
-            s_prefix      = pre | ((uint32_t) b << sh);
-            s_prefix_mask = pmask | (255u << sh);
+            int above = sum;  // inclusive suffix sum over lanes >= lane
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_down_sync(0xffffffffu, above, o);
+                above += (lane + o < 32) ? t : 0;
+            }
+            above -= sum;  // keys in strictly higher lanes
+            const int need = s_k;
+            __syncwarp();  // every lane has read s_k before the owning lane replaces it
+            if (above < need && need <= above + sum) {
+                int rem = need - above, bdig = lane * 8 + 7;
+#pragma unroll
+                for (int j = 7; j >= 0; --j) {
+                    if (rem > 0 && own[j] >= rem) {
+                        bdig = lane * 8 + j;
+                        s_k  = rem;  // how many to take among keys with this prefix digit
+                        rem  = -1;
+                    } else if (rem > 0) {
+                        rem -= own[j];
+                    }
+                }
+                s_prefix      = pre | ((uint32_t) bdig << sh);
+                s_prefix_mask = pmask | (255u << sh);
+            }
         }
         __syncthreads();
     }
@@ -182,8 +214,134 @@ __global__ void __launch_bounds__(1024) spif_topk_mask_kernel(const float * __re
     }
 }
 
+// Register-resident variant for n_ff <= KPT * 1024: every thread loads its KPT keys ONCE (warp w owns the contiguous index
+// chunk [w * chunk, (w+1) * chunk), key j of a lane is index chunk_base + 32 j + lane -> coalesced, and already in the order
+// the tie-break needs), the four radix passes and the ordered output pass then run on registers only.
+template <int KPT>
+__global__ void __launch_bounds__(1024) spif_topk_mask_reg_kernel(const float * __restrict__ score, int n_ff, int k,
+                                                                   float * __restrict__ out) {
+    __shared__ int      hist[256];
+    __shared__ uint32_t s_prefix, s_prefix_mask;
+    __shared__ int      s_k;
+    __shared__ int      warp_cnt[32];
+    const float *       sc = score + (size_t) blockIdx.x * n_ff;
+    float *             o  = out + (size_t) blockIdx.x * n_ff;
+    const int           tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int           chunk = ((n_ff + 1023) / 1024) * 32;
+    const int           r0 = warp * chunk, r1 = min(r0 + chunk, n_ff);
+    if (k <= 0 || k >= n_ff) {
+        for (int i = tid; i < n_ff; i += blockDim.x) {
+            o[i] = (k <= 0) ? 0.f : 1.f;
+        }
+        return;
+    }
+    uint32_t key[KPT];
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        const int i = r0 + j * 32 + lane;
+        key[j]      = (i < r1) ? float_key(sc[i]) : 0u;
+    }
+    if (tid == 0) {
+        s_prefix      = 0;
+        s_prefix_mask = 0;
+        s_k           = k;
+    }
+    for (int pass = 3; pass >= 0; --pass) {
+        for (int i = tid; i < 256; i += blockDim.x) {
+            hist[i] = 0;
+        }
+        __syncthreads();
+        const uint32_t pre = s_prefix, pmask = s_prefix_mask;
+        const int      sh  = pass * 8;
+#pragma unroll
+        for (int j = 0; j < KPT; ++j) {
+            if (r0 + j * 32 >= r1) {
+                continue;  // warp-uniform: nothing of this warp's chunk in this slot
+            }
+            const bool     in  = (r0 + j * 32 + lane < r1) && ((key[j] & pmask) == pre);
+            const unsigned dig = in ? ((key[j] >> sh) & 255u) : 0x1000u;
+            if (pass == 3) {  // sign + exponent: a handful of distinct values -> merge equal lanes, one atomic per group
+                const unsigned grp = __match_any_sync(0xffffffffu, dig);
+                if (in && (__ffs(grp) - 1) == lane) {
+                    atomicAdd(&hist[dig], __popc(grp));
+                }
+            } else if (in) {
+                atomicAdd(&hist[dig], 1);
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {
+            int own[8], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                own[j] = hist[lane * 8 + j];
+                sum += own[j];
+            }
+            int above = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_down_sync(0xffffffffu, above, d);
+                above += (lane + d < 32) ? t : 0;
+            }
+            above -= sum;
+            const int need = s_k;
+            __syncwarp();
+            if (above < need && need <= above + sum) {
+                int rem = need - above, bdig = lane * 8 + 7;
+#pragma unroll
+                for (int j = 7; j >= 0; --j) {
+                    if (rem > 0 && own[j] >= rem) {
+                        bdig = lane * 8 + j;
+                        s_k  = rem;
+                        rem  = -1;
+                    } else if (rem > 0) {
+                        rem -= own[j];
+                    }
+                }
+                s_prefix      = pre | ((uint32_t) bdig << sh);
+                s_prefix_mask = pmask | (255u << sh);
+            }
+        }
+        __syncthreads();
+    }
+    const uint32_t kth     = s_prefix;
+    const int      need_eq = s_k;
+    int            cnt = 0;
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        cnt += __popc(__ballot_sync(0xffffffffu, (r0 + j * 32 + lane < r1) && key[j] == kth));
+    }
+    if (lane == 0) {
+        warp_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    int run = 0;
+    for (int w = 0; w < warp; ++w) {
+        run += warp_cnt[w];
+    }
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        const int      i  = r0 + j * 32 + lane;
+        const unsigned bj = __ballot_sync(0xffffffffu, (i < r1) && key[j] == kth);
+        if (i < r1) {
+            bool sel = key[j] > kth;
+            if (key[j] == kth) {
+                sel = (run + __popc(bj & ((1u << lane) - 1u))) < need_eq;
+            }
+            o[i] = sel ? 1.0f : 0.0f;
+        }
+        run += __popc(bj);
+    }
+}
+
 int spif_launch_topk_mask(const float * score, int n_ff, int n_tok, int k, float * out, cudaStream_t stream) {
-    spif_topk_mask_kernel<<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
+    if (n_ff <= 16 * 1024) {
+        spif_topk_mask_reg_kernel<16><<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
+    } else if (n_ff <= 32 * 1024) {
+        spif_topk_mask_reg_kernel<32><<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
+    } else {
+        spif_topk_mask_kernel<<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
+    }
     SPIF_CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -112,10 +112,11 @@ def mask_compact(sparse_idx, neuron_idx=None, thr=SPARSE_THRESHOLD, flags=0, wan
     return (idx, cnt, uidx, ucnt) if want_union else (idx, cnt)
 
 
-def topk_mask(score, k):
+def topk_mask(score, k, out=None):
+    """sparse_idx[t][i] = 1.0 for the k largest score[t][i] (ties -> lower index), else 0.0 (Llama-3 / SiLU config)"""
     L = _lib.load()
     n_tok, n_ff = score.shape
-    out = torch.empty_like(score)
+    out = out if out is not None else torch.empty_like(score)
     check(L.spif_topk_mask(_p(score), n_ff, n_tok, k, _p(out), None, 0, _stream()), "spif_topk_mask")
     return out
 
@@ -163,16 +164,17 @@ def shifted_step(a, threshold):
 
 
 def predictor(pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, n_ff, flags=0, want_logits=False, ws=None,
-              out=None):
+              out=None, logits_out=None):
     """build_predictor(cur, pred_up, pred_up_b, pred_down, pred_down_b): -> sparse_idx {n_ff, n_tok} (and logits)"""
     L = _lib.load()
     n_tok, n_embd = cur.shape
     out = out if out is not None else torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device)
-    logits = torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device) if want_logits else None
+    logits = logits_out if logits_out is not None else (
+        torch.empty((n_tok, n_ff), dtype=torch.float32, device=cur.device) if want_logits else None)
     ws = _ws(ws, n_embd, n_ff, n_tok, cur.device)
     check(L.spif_predictor(p_type, _p(pred_up), _p(pred_up_b), _p(pred_down), _p(pred_down_b), _p(cur), _p(out), _p(logits),
                            n_embd, r, n_ff, n_tok, flags, ws.ptr, ws.nbytes, _stream()), "spif_predictor")
-    return (out, logits) if want_logits else out
+    return (out, logits) if (want_logits or logits_out is not None) else out
 
 
 def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx=None, up_b=None, gate_b=None,

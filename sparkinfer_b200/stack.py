@@ -30,7 +30,7 @@ class FfnStack:
     """n_layer sparse FFNs + predictors for one decode step (n_tok tokens)"""
 
     def __init__(self, arch, w_type, p_type, n_embd, n_ff_local, r, layers, n_tok=1, group=None, device="cuda",
-                 flags=0, exchange="nccl"):
+                 flags=0, exchange="nccl", topk=0):
         self.arch, self.w_type, self.p_type = arch, w_type, p_type
         self.n_embd, self.m, self.r, self.n_tok = n_embd, n_ff_local, r, n_tok
         self.layers = layers
@@ -55,6 +55,9 @@ class FfnStack:
         self.y = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)
         self.p = torch.zeros((self.L, n_tok, n_ff_local), dtype=torch.float32, device=device)
         self.stats = torch.zeros((self.L, n_tok, 4), dtype=torch.int32, device=device)
+        # top-k masking (Llama-3 / SiLU config): mask = the k largest predictor logits of this shard instead of p >= 0.5
+        self.topk = int(topk)
+        self.logits = torch.zeros((n_tok, n_ff_local), dtype=torch.float32, device=device) if self.topk > 0 else None
         self.graph = None
         self.launches_per_step = 0
         self.early_mask = True
@@ -65,6 +68,11 @@ class FfnStack:
     # -- single pieces ------------------------------------------------------------------------------------------
     def predict(self, l, x_from):
         w = self.layers[l]
+        if self.topk > 0:
+            ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
+                          flags=self.flags, ws=self.ws_pred, out=self.p[l], logits_out=self.logits)
+            ops.topk_mask(self.logits, self.topk, out=self.p[l])
+            return 3
         ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
                       flags=self.flags, ws=self.ws_pred, out=self.p[l])
         return 2  # kernels: predictor up GEMV, predictor down GEMV+sigmoid

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 F32, F16, Q4_0, Q8_0, BF16 = 0, 1, 2, 8, 30
-ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP = 0, 1, 2
+ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
 TYPE_NAMES = {F16: "f16", BF16: "bf16", Q8_0: "q8_0", Q4_0: "q4_0", F32: "f32"}
 
 c_vp, c_i, c_i64, c_f, c_sz, c_d = (ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_float,

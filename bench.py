@@ -57,6 +57,12 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="per-layer sum over GPU shards: fused peer-memory exchange (default) or ncclAllReduce")
+    ap.add_argument("--placement", default="snake", choices=["snake", "contiguous"],
+                    help="N > 1: initial neuron-group placement (snake = placement.initial_placement; contiguous = none)")
+    ap.add_argument("--balance-rounds", type=int, default=0,
+                    help="N > 1: rounds of the online shard balancer (observe masks, plan, swap groups) before the timed region")
+    ap.add_argument("--balance-tokens", type=int, default=32, help="decode steps observed per balancer round")
+    ap.add_argument("--balance-swaps", type=int, default=64, help="max group swaps per layer per balancer round")
     ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
     ap.add_argument("--schedule", default="two-streams", choices=["serial", "two-streams"],
@@ -156,10 +162,17 @@ def build_stack(a, wl, rank, world, device):
     def half(rows, cols, std):
         return u8(torch.empty((rows, cols), dtype=torch.float16, device=device).normal_(0.0, std, generator=gen))
 
-    layers, expect = [], []
+    layers, expect, shard_maps = [], [], []
     for l in range(L):
         p_g = synth_hotness(F, a.rho, a.seed + l)                   # identical on every rank
-        shard_of = placement.initial_placement(p_g, world)
+        if a.placement == "contiguous" and world > 1:
+            # no placement: the offline hotness reorder leaves the groups sorted, dealt in contiguous blocks the hottest
+            # all land on shard 0 (what the online balancer then has to repair)
+            shard_of = np.empty(n_g, dtype=np.int32)
+            shard_of[np.argsort(-p_g, kind="stable")] = np.arange(n_g) // (n_g // world)
+        else:
+            shard_of = placement.initial_placement(p_g, world)
+        shard_maps.append(shard_of)
         mine = np.nonzero(shard_of == rank)[0]
         p_n = np.repeat(p_g[mine], GROUP)                           # this shard's neurons, ascending
         expect.append(float(p_n.sum()))
@@ -172,6 +185,7 @@ def build_stack(a, wl, rank, world, device):
     group = torch.distributed.group.WORLD if world > 1 else None
     st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device,
                   exchange=a.exchange, topk=int(a.rho * m) if wl.get("topk") else 0)
+    st.shard_maps = shard_maps
     return st, expect
 
 
@@ -258,6 +272,62 @@ def run_ours(a):
         torch.cuda.current_stream().synchronize()   # a decode step's result is needed on the host before the next
 
     log('all graphs captured')
+
+    def shard_activity():
+        """active rows per layer of every shard, averaged over the x pool: [world, L]; imbalance = max_s / mean_s"""
+        mine = torch.tensor(np.mean(np.stack(A_pool), axis=0), dtype=torch.float64, device=device)
+        if world == 1:
+            return mine.cpu().numpy()[None]
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        return torch.stack(parts).cpu().numpy()
+
+    def measure_activity():
+        A_pool.clear(), Z_pool.clear()
+        for i in range(a.pool):
+            st.x.copy_(x_pool[i])
+            st.step_eager(want_stats=True)
+            torch.cuda.synchronize()
+            s = st.stats.cpu().numpy()[:, 0, :]
+            A_pool.append(s[:, 0].astype(np.int64))
+            Z_pool.append(s[:, 1].astype(np.int64))
+
+    act = shard_activity()
+    balance = {"placement": a.placement if world > 1 else "single shard",
+               "active_rows_imbalance": float((act.max(axis=0) / np.maximum(act.mean(axis=0), 1e-9)).mean())}
+    if world > 1 and a.balance_rounds > 0:
+        # the online balancer (SURVEY.md 8e): decayed firing rates from the masks of real steps, greedy swap plan, the
+        # rows of the swapped groups exchanged between the two ranks.  Weights move in place, the graphs stay valid.
+        from sparkinfer_b200.balancer import ShardBalancer
+        bal = ShardBalancer(st.layers, st.shard_maps, rank, world, group=dist.group.WORLD, g=GROUP, lam=0.9)
+        n_before = max(50, a.steps // 10)
+        ms_before = timed(step_resident, n_before, 5) / n_before
+        log('balancer: before-leg timed')
+        rounds, t_obs, t_move, tok = [], 0.0, 0.0, 0
+        for rd in range(a.balance_rounds):
+            t0 = time.perf_counter()
+            for _ in range(a.balance_tokens):
+                step_resident(tok)
+                bal.observe(st.p)
+                tok += 1
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            log(f'balancer round {rd}: observed')
+            r = bal.rebalance(max_swaps=a.balance_swaps)
+            log(f'balancer round {rd}: moved {r["swaps"]} swaps')
+            barrier()
+            t2 = time.perf_counter()
+            t_obs, t_move = t_obs + (t1 - t0), t_move + (t2 - t1)
+            rounds.append({"swaps": r["swaps"], "dfr_imbalance_before": r["imbalance_before"],
+                           "dfr_imbalance_planned": r["imbalance_after"]})
+        measure_activity()
+        act2 = shard_activity()
+        balance.update({"active_rows_imbalance_before": balance["active_rows_imbalance"],
+                        "active_rows_imbalance": float((act2.max(axis=0) / np.maximum(act2.mean(axis=0), 1e-9)).mean()),
+                        "tok_s_before": 1e3 / ms_before, "rounds": rounds, "tokens_observed": tok,
+                        "swaps_total": bal.swaps_done, "bytes_sent_rank0": bal.bytes_moved,
+                        "observe_s": t_obs, "plan_and_move_s": t_move, "dfr_launches_per_token": L})
+        log('balancer done')
     sampler = ClockSampler(physical_gpu_index(local))
     sampler.start()
     ms_value = timed(step_resident, a.steps, max(a.warmup, 3))
@@ -323,6 +393,7 @@ def run_ours(a):
                 "d2h_bytes_per_step": 4 * L * E},
         "gpu_launches": launches_per_step * a.steps,
         "clocks": clocks,
+        "shard_balance": balance,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,
                      "kernel": "spif_ffn_kernel<f16,FUSED> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call",

@@ -57,12 +57,21 @@ def rebalance_plan(dfr, shard_of_group, n_shards, max_swaps=8, min_gain=0.0):
             break
         gh = np.nonzero(shard == hot)[0]
         gc = np.nonzero(shard == cold)[0]
-        # moving delta = d[a] - d[b] from hot to cold: new pair max = max(hot - delta, cold + delta); best delta = gap / 2
-        delta = d[gh][:, None] - d[gc][None, :]
-        cost = np.maximum(ld[hot] - delta, ld[cold] + delta)
-        cost[delta <= 0] = np.inf
-        i, j = np.unravel_index(np.argmin(cost), cost.shape)
-        if not np.isfinite(cost[i, j]) or ld[hot] - cost[i, j] <= min_gain:
+        # moving delta = d[a] - d[b] from hot to cold: new pair max = max(hot - delta, cold + delta) = mid + |delta - gap/2|,
+        # so the best pair has delta > 0 closest to gap / 2.  For every a the two candidates are the neighbours of
+        # d[a] - gap/2 in the sorted scores of the cold shard: O(n log n) per swap instead of the n x n table.
+        oc = np.argsort(d[gc], kind="stable")
+        dc = d[gc][oc]
+        pos = np.searchsorted(dc, d[gh] - gap / 2)
+        best = (np.inf, -1, -1)
+        for cand in (np.clip(pos - 1, 0, gc.size - 1), np.clip(pos, 0, gc.size - 1)):
+            delta = d[gh] - dc[cand]
+            cost = np.where(delta > 0, ld[cold] + gap / 2 + np.abs(delta - gap / 2), np.inf)
+            i = int(np.argmin(cost))
+            if cost[i] < best[0]:
+                best = (float(cost[i]), i, int(oc[cand[i]]))
+        c_best, i, j = best
+        if not np.isfinite(c_best) or ld[hot] - c_best <= min_gain:
             break
         a, b = int(gh[i]), int(gc[j])
         shard[a], shard[b] = cold, hot

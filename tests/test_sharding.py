@@ -101,3 +101,80 @@ def test_sharded_path_world2_gloo(wtype):
     err, exact_u = q.get(timeout=5)
     assert exact_u, "per-shard gate/up results are disjoint: their sum must equal the unsharded result bit for bit"
     assert err < 2e-6, err                                   # only the summation order of y differs
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# balancer execution: swap plan -> rows exchanged between the two shards, slot tables stay in step on both ranks
+def _balancer_worker(rank, world, port, q):
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+    import torch
+    import torch.distributed as dist
+    from sparkinfer_b200 import placement
+    from sparkinfer_b200.balancer import ShardBalancer
+    from sparkinfer_b200.stack import LayerWeights
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g, n_g, E, R, L = 16, 32, 64, 8, 3
+        m = n_g // world * g
+        rng = np.random.default_rng(5)
+        hots = [synth.hotness(n_g * g, g, 0.2, rng)[::g] for _ in range(L)]
+        layers, sogs = [], []
+        for l in range(L):
+            order = np.argsort(-hots[l], kind="stable")
+            sog = np.empty(n_g, dtype=np.int32)
+            sog[order] = np.arange(n_g) // (n_g // world)     # worst case: the hottest groups all on shard 0
+            sogs.append(sog)
+            mine = np.nonzero(sog == rank)[0]
+
+            def rows(tag, width, dtype):
+                # every element of a group's rows encodes (layer, matrix, group): the content identifies the group
+                v = (np.repeat(mine, g)[:, None] * 8 + tag + 1000 * l) * np.ones((1, width))
+                return torch.from_numpy(v.astype(dtype))
+            layers.append(LayerWeights(up=rows(0, E, np.float16).view(torch.uint8).reshape(-1),
+                                       gate=rows(1, E, np.float16).view(torch.uint8).reshape(-1),
+                                       down_t=rows(2, E, np.float16).view(torch.uint8).reshape(-1),
+                                       pred_up=None, pred_down=rows(3, R, np.float16).view(torch.uint8).reshape(-1),
+                                       pred_down_b=rows(4, 1, np.float32).reshape(-1), m=m))
+        bal = ShardBalancer(layers, sogs, rank, world, group=None, g=g)
+        for l in range(L):                                    # scores as the DFR kernel would leave them
+            bal.dfr[l] = torch.from_numpy(hots[l][bal.local_groups(l)].astype(np.float32))
+        res = bal.rebalance(max_swaps=6)
+        ok = True
+        for l in range(L):
+            mine = bal.local_groups(l)
+            w = layers[l]
+            for tag, t, dt, width in ((0, w.up, torch.float16, E), (1, w.gate, torch.float16, E),
+                                      (2, w.down_t, torch.float16, E), (3, w.pred_down, torch.float16, R)):
+                got = t.view(dt).reshape(m, width).double().numpy()
+                want = (np.repeat(mine, g)[:, None] * 8 + tag + 1000 * l) * np.ones((1, width))
+                ok &= bool(np.array_equal(got, want.astype(np.float16).astype(np.float64)))
+            ok &= bool(np.array_equal(w.pred_down_b.numpy(), (np.repeat(mine, g) * 8 + 4 + 1000 * l).astype(np.float32)))
+            ok &= bool(np.array_equal(bal.dfr[l].numpy(), hots[l][mine].astype(np.float32)))   # scores moved with the rows
+            ok &= sorted(np.concatenate(list(bal.slots[l])).tolist()) == list(range(n_g))        # still a partition
+        again = bal.rebalance(max_swaps=6)                   # scores() after the move must reproduce the planned state
+        q.put((rank, ok, res, again["imbalance_before"], [s.tolist() for s in bal.slots]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_balancer_swaps_rows_world2_gloo():
+    pytest.importorskip("torch")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_balancer_worker, args=(r, 2, port, q)) for r in range(2)]
+    for pr in procs:
+        pr.start()
+    got = [q.get(timeout=180) for _ in range(2)]
+    for pr in procs:
+        pr.join(timeout=60)
+        assert pr.exitcode == 0
+    got.sort(key=lambda t: t[0])
+    for _, ok, res, again_before, _ in got:
+        assert ok, "rows / bias / scores in a slot do not belong to the group the slot table names"
+        assert res["swaps"] > 0 and res["bytes_sent_this_rank"] > 0
+        assert res["imbalance_after"] < res["imbalance_before"] and res["imbalance_after"] < 1.1
+        assert abs(again_before - res["imbalance_after"]) < 1e-6
+    assert got[0][4] == got[1][4], "slot tables diverged between the ranks"

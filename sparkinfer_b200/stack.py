@@ -5,7 +5,7 @@ its own mask from x_0, and while layer l runs, the mask of layer l+1 is predicte
 The attention blocks between the FFNs are out of scope, so the x_l are inputs.
 
 Sharding: with world_size G each rank holds the rows of n_ff / G neurons of every matrix (whole groups of
-`g` consecutive neurons, dealt by the placement in balancer.py), predicts / masks / computes only those, and the partial
+`g` consecutive neurons, dealt by placement.py, moved online by balancer.py), predicts / masks / computes only those, and the partial
 y_l is summed over ranks with ONE allreduce per layer.
 
 torch is plumbing only (device memory, streams, NCCL through torch.distributed); every compute step is a call into

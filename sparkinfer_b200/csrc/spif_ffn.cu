@@ -317,8 +317,12 @@ static int launch_direct_t(const FfnKParams & kp, dim3 grid, int threads, size_t
 static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
     const int V = a.n_embd / 8;
     SPIF_REQUIRE(V <= 1024, SPIF_E_UNSUPPORTED);
-    const int vpt     = V <= 640 ? 1 : 2;
-    const int threads = ((V + vpt - 1) / vpt + 31) / 32 * 32;
+    // half-size CTAs (<= 320 threads x 2 vectors, 41 K registers) leave room for a co-resident predictor CTA of the next
+    // layer (spif_launch_predictor caps its CTAs to match); SPIF_DIRECT_SMALL=0 restores the 640-thread shape
+    static const int k_small = [] { const char * e = getenv("SPIF_DIRECT_SMALL"); return e ? atoi(e) : 1; }();
+    const bool small   = k_small && V <= 640 && V > 320;
+    const int  vpt     = (V <= 640 && !small) ? 1 : 2;
+    const int  threads = ((V + vpt - 1) / vpt + 31) / 32 * 32;
     SPIF_REQUIRE(a.m <= 4096 * (threads / 32), SPIF_E_UNSUPPORTED);  // activity bits kept in registers by build_my_list
     const int P = ctx.sm_count;
     SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_LANES * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
@@ -362,6 +366,9 @@ static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_
     if (vpt == 1) {
         rc = f16 ? launch_direct_t<spif_f16, 1, 2, 640>(kp, grid, threads, smem, ctx.stream) :
                    launch_direct_t<spif_bf16, 1, 2, 640>(kp, grid, threads, smem, ctx.stream);
+    } else if (small) {
+        rc = f16 ? launch_direct_t<spif_f16, 2, 1, 320>(kp, grid, threads, smem, ctx.stream) :
+                   launch_direct_t<spif_bf16, 2, 1, 320>(kp, grid, threads, smem, ctx.stream);
     } else {
         rc = f16 ? launch_direct_t<spif_f16, 2, 1, 512>(kp, grid, threads, smem, ctx.stream) :
                    launch_direct_t<spif_bf16, 2, 1, 512>(kp, grid, threads, smem, ctx.stream);

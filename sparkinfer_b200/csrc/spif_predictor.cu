@@ -182,7 +182,7 @@ static int launch_dg_v(int vl, const DenseGemvParams & p, dim3 grid, int threads
 
 // out[t][row] = epi(W[row] . x[t] + bias[row])
 static int dense_gemv(int type, int epi, const void * w, const float * bias, const float * x, float * out, float * logits,
-                      int rows, int K, int n_tok, int flags, const spif_launch_ctx & ctx) {
+                      int rows, int K, int n_tok, int flags, int warp_cap, const spif_launch_ctx & ctx) {
     DenseGemvParams p = {};
     p.w      = (const unsigned char *) w;
     p.bias   = bias;
@@ -194,10 +194,19 @@ static int dense_gemv(int type, int epi, const void * w, const float * bias, con
     p.V      = K / 8;
     p.flags  = flags;
     // slice width: VL*32 vectors of 8 elements per warp pass
-    const int vl = (p.V >= 128) ? 4 : (p.V >= 64 ? 2 : 1);
+    static const int k_vl = [] { const char * e = getenv("SPIF_DG_VL"); return e ? atoi(e) : 4; }();
+    int              vl   = (p.V >= 128) ? 4 : (p.V >= 64 ? 2 : 1);
+    vl                    = vl > k_vl ? k_vl : vl;
     p.ns = (p.V + vl * 32 - 1) / (vl * 32);
     SPIF_REQUIRE(p.ns <= DG_MAX_WARPS, SPIF_E_SHAPE);  // K <= 12 * 1024 elements
     p.nrw             = DG_MAX_WARPS / p.ns;
+    // warp_cap: smaller CTAs that fit next to a resident FFN CTA (see spif_predictor); SPIF_DG_WARPS overrides, 0 = no cap
+    static const int k_warps = [] { const char * e = getenv("SPIF_DG_WARPS"); return e ? atoi(e) : -1; }();
+    const int        wcap    = k_warps >= 0 ? k_warps : warp_cap;
+    if (wcap > 0) {
+        const int cap = wcap / p.ns < 1 ? 1 : wcap / p.ns;
+        p.nrw         = p.nrw > cap ? cap : p.nrw;
+    }
     const int threads = p.ns * p.nrw * 32;
     const int per_sm  = (2 * DG_MAX_WARPS * 32) / threads;  // CTAs that fit the 2 x 384-thread register budget
     const int G       = ctx.sm_count * (per_sm < 1 ? 1 : per_sm);
@@ -230,9 +239,14 @@ int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const 
     SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= h1_off + h1_bytes, SPIF_E_WORKSPACE);
     float * h1 = (float *) ((char *) ws + h1_off);
     const int fl = flags & SPIF_FLAG_CPU_ROUNDING;
-    int       rc = dense_gemv(ptype, DG_EPI_RELU, wpu, bpu, x, h1, nullptr, r, n_embd, n_tok, fl, ctx);
+    // The predictor of layer l+1 runs next to the FFN of layer l (look-ahead).  For 320 < n_embd/8 <= 640 the FFN kernel runs
+    // 320-thread CTAs that leave 24 K registers per SM (spif_launch_ffn_direct): 6-warp predictor CTAs fit beside one, 12-warp
+    // ones would wait for the FFN to leave.  profiles/r1d_coresidency.txt: 13B decode 1034 -> 1110 tok/s.
+    const int V8   = n_embd / 8;
+    const int wcap = (n_tok == 1 && V8 > 320 && V8 <= 640) ? 6 : 0;
+    int       rc = dense_gemv(ptype, DG_EPI_RELU, wpu, bpu, x, h1, nullptr, r, n_embd, n_tok, fl, wcap, ctx);
     if (rc) {
         return rc;
     }
-    return dense_gemv(ptype, DG_EPI_SIGMOID, wpd, bpd, h1, sparse_idx_out, logits_out, n_ff, r, n_tok, fl, ctx);
+    return dense_gemv(ptype, DG_EPI_SIGMOID, wpd, bpd, h1, sparse_idx_out, logits_out, n_ff, r, n_tok, fl, wcap, ctx);
 }

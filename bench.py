@@ -396,7 +396,7 @@ def run_ours(a):
         "shard_balance": balance,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "spif_ffn_kernel<f16,FUSED> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call",
+                     "kernel": "spif_ffn_direct_kernel<f16> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call",
                      "bytes_per_launch": ffn_bytes / L, "us_per_launch": ms_ffn * 1e3 / L,
                      "predictor": {"achieved": pred_bytes / (ms_pred * 1e-3) / 1e9, "us_per_layer": ms_pred * 1e3 / L,
                                    "bytes_per_layer": pred_bytes / L},

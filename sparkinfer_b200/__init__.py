@@ -12,4 +12,6 @@ from .ops import (  # noqa: F401
     ShardComm, dfr_update, fatrelu, mask_compact, mul_mat_sparse, predictor, row_size, shard_allreduce, shifted_step, sparse_ffn,
     topk_mask)
 
+from .balancer import ShardBalancer  # noqa: F401,E402
+
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -40,7 +40,8 @@ extern "C" void spif_debug_set_trace(void * dev_ptr) {
 template <bool COMM>
 __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_partials_kernel(
     const float * __restrict__ partials, const float * __restrict__ b_down, float * __restrict__ y,
-    const int32_t * __restrict__ cta_stats, int32_t * __restrict__ stats_out, int n_embd, int P, const spif_comm_dev comm) {
+    const int32_t * __restrict__ cta_stats, int32_t * __restrict__ stats_out, int n_embd, int P, const spif_comm_dev comm,
+    const int launch_first) {
     __shared__ float4 sm[SPIF_RED_LANES][SPIF_RED_COLS];
     __shared__ float4 sm2[4][SPIF_RED_COLS];
     const int         tok  = blockIdx.y;
@@ -48,8 +49,15 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
     const int         py   = threadIdx.x / SPIF_RED_COLS;
     const int         col4 = blockIdx.x * SPIF_RED_COLS + cx;
     const int         n4   = n_embd >> 2;
+    if (launch_first) {
+        // the next layer's kernel may start (mask scan, first weight rows) while this grid still waits for the partials;
+        // it touches x / y / the workspace only after ITS griddepcontrol.wait, i.e. after this grid has completed
+        pdl_launch_dependents();
+    }
     pdl_wait_prior_grid();
-    pdl_launch_dependents();
+    if (!launch_first) {
+        pdl_launch_dependents();
+    }
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (col4 < n4) {
         const float4 * base = reinterpret_cast<const float4 *>(partials + (size_t) tok * P * n_embd) + col4;
@@ -163,6 +171,7 @@ static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y,
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs                                        = at;
     cfg.numAttrs                                     = 1;
+    static const int k_red_first = [] { const char * e = getenv("SPIF_RED_FIRST"); return e ? atoi(e) : 1; }();
     spif_comm_dev cd = {};
     if (comm) {
         int rc = spif_comm_to_dev(comm, cd);
@@ -172,11 +181,11 @@ static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y,
         SPIF_REQUIRE((int64_t) n_embd * n_tok <= comm->cap_floats, SPIF_E_WORKSPACE);
         SPIF_REQUIRE(cfg.gridDim.x * cfg.gridDim.y <= SPIF_COMM_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
         SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel<true>, (const float *) kp.partials, b_down, y,
-                                         (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd));
+                                         (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd, k_red_first));
         return 0;
     }
     SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel<false>, (const float *) kp.partials, b_down, y,
-                                     (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd));
+                                     (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd, k_red_first));
     return 0;
 }
 
@@ -345,7 +354,8 @@ static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_
     kp.row_bytes  = a.n_embd * 2;
     kp.thr        = a.thr;
     kp.arch       = a.arch;
-    kp.flags      = a.flags;
+    static const int k_pdl_late = [] { const char * e = getenv("SPIF_PDL_LATE"); return e ? atoi(e) : 0; }();
+    kp.flags      = a.flags | (k_pdl_late ? SPIF_KFLAG_PDL_LATE : 0);
     kp.dense_out  = a.hidden_out;
     kp.trace      = g_spif_trace;
     kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;

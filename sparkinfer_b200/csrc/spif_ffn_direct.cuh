@@ -78,7 +78,10 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
     if (early) {
         pdl_wait_prior_grid();  // x, y and the partials workspace belong to the previous kernels until here
     }
-    pdl_launch_dependents();
+    const bool pdl_late = (p.flags & SPIF_KFLAG_PDL_LATE) != 0;
+    if (!pdl_late) {
+        pdl_launch_dependents();
+    }
 
     float xr[VPT * 8], acc[VPT * 8];
 #pragma unroll
@@ -217,6 +220,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_direct_kernel(const FfnKPara
         }
     }
     SPIF_STAMP(4);
+    if (pdl_late) {
+        pdl_launch_dependents();  // the partial-sum CTAs take their registers only now (room for the predictor until here)
+    }
     axpy_prev(DN[0], alpha[0]);
     axpy_prev(DN[1], alpha[1]);
 

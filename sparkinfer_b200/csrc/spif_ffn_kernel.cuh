@@ -8,6 +8,8 @@
 #define SPIF_NB        2   /* neurons per reduction batch */
 #define SPIF_MAX_WARPS 17  /* 16 consumer warps + 1 producer */
 
+#define SPIF_KFLAG_PDL_LATE (1 << 30) /* kernel-internal: launch the dependent grid after the row loop */
+
 struct FfnKParams {
     const unsigned char * w_up;
     const unsigned char * w_gate;

@@ -17,6 +17,23 @@
 
 #define DG_MAX_WARPS 12
 #define DG_U         2 /* rows in flight per warp */
+#define DG_DEPTH     4 /* ASYNC variant: batches of DG_U rows in flight per warp */
+
+// ASYNC variant (spif_dense_gemv_kernel<..., true>): the same walk, but the rows travel through a thread-PRIVATE shared-memory
+// ring filled by 16-byte cp.async (LDGSTS): DG_DEPTH batches are in flight per lane and hold no registers while they fly.
+// Every lane reads back only the bytes it requested itself, so cp.async.wait_group is the only synchronisation.  Purpose:
+// next to a resident sparse-FFN CTA only ONE small predictor CTA fits by registers (profiles/r1d_coresidency.txt); with
+// register-held loads that CTA keeps 24 KB in flight, with the ring 4x as much -- shared memory is what the FFN kernel
+// leaves free.
+__device__ __forceinline__ void dg_cp_async16(uint32_t dst, const void * src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void dg_cp_async_commit() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void dg_cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 
 enum { DG_EPI_RELU = 0, DG_EPI_SIGMOID = 1 };
 
@@ -32,9 +49,9 @@ struct DenseGemvParams {
     int                   flags;
 };
 
-template <typename WT, int VL, int EPI>
+template <typename WT, int VL, int EPI, bool ASYNC>
 __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(const DenseGemvParams p) {
-    extern __shared__ float part[];  // [rpc][ns] partial dots (only when ns > 1)
+    extern __shared__ __align__(16) float part[];  // [rpc][ns] partial dots (only when ns > 1), then the ASYNC ring
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tok  = blockIdx.y;
     const int sl   = warp % p.ns;  // my K-slice
@@ -46,7 +63,11 @@ __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(c
 
     // vector k of lane: v0 + lane + 32 k   (coalesced 512 B per warp instruction)
     uint4 wv[DG_U][VL];
-    auto  load_rows = [&](int rbase) {
+    // ASYNC ring: slot d, row u, vector k of thread t at uint4 index ((d * DG_U + u) * VL + k) * blockDim.x + t
+    const int      NT       = blockDim.x;
+    uint4 *        ring     = reinterpret_cast<uint4 *>(part + ((p.ns > 1 ? p.rpc * p.ns : 0) + 3) / 4 * 4);
+    const uint32_t ring_s   = (uint32_t) __cvta_generic_to_shared(ring);
+    auto           load_rows = [&](int rbase, int slot) {
 #pragma unroll
         for (int u = 0; u < DG_U; ++u) {
             const int row = min(rbase + u * p.nrw, r1 - 1);
@@ -54,14 +75,39 @@ __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(c
 #pragma unroll
             for (int k = 0; k < VL; ++k) {
                 const int v = min(v0 + lane + 32 * k, p.V - 1);
-                wv[u][k]    = ldg_stream_v4(rp + (size_t) v * 16);
+                if (ASYNC) {
+                    dg_cp_async16(ring_s + (uint32_t) ((((slot * DG_U + u) * VL + k) * NT + (int) threadIdx.x) * 16),
+                                  rp + (size_t) v * 16);
+                } else {
+                    wv[u][k] = ldg_stream_v4(rp + (size_t) v * 16);
+                }
+            }
+        }
+    };
+    auto take_rows = [&](int slot) {  // ASYNC: my own bytes of the oldest batch -> registers
+#pragma unroll
+        for (int u = 0; u < DG_U; ++u) {
+#pragma unroll
+            for (int k = 0; k < VL; ++k) {
+                wv[u][k] = ring[((slot * DG_U + u) * VL + k) * NT + threadIdx.x];
             }
         }
     };
 
     const bool have_work = (rl < p.nrw) && (r0 + rl < r1);
+    const int  step      = DG_U * p.nrw;
     if (have_work) {
-        load_rows(r0 + rl);  // in flight across the PDL wait
+        if (ASYNC) {
+#pragma unroll
+            for (int d = 0; d < DG_DEPTH; ++d) {  // one commit group per batch, empty ones included: uniform counting
+                if (r0 + rl + d * step < r1) {
+                    load_rows(r0 + rl + d * step, d);
+                }
+                dg_cp_async_commit();
+            }
+        } else {
+            load_rows(r0 + rl, 0);  // in flight across the PDL wait
+        }
     }
     pdl_wait_prior_grid();  // x (h1) comes from the previous kernel
     pdl_launch_dependents();
@@ -107,8 +153,12 @@ __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(c
     };
 
     if (have_work) {
-        const int step = DG_U * p.nrw;
+        int slot = 0;
         for (int rb = r0 + rl; rb < r1; rb += step) {
+            if (ASYNC) {
+                dg_cp_async_wait<DG_DEPTH - 1>();
+                take_rows(slot);
+            }
             float acc[DG_U][2];
 #pragma unroll
             for (int u = 0; u < DG_U; ++u) {
@@ -123,8 +173,14 @@ __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(c
                     }
                 }
             }
-            if (rb + step < r1) {
-                load_rows(rb + step);  // next batch in flight while this one is reduced
+            if (ASYNC) {
+                if (rb + DG_DEPTH * step < r1) {
+                    load_rows(rb + DG_DEPTH * step, slot);  // the slot just read is free again
+                }
+                dg_cp_async_commit();
+                slot = (slot + 1 == DG_DEPTH) ? 0 : slot + 1;
+            } else if (rb + step < r1) {
+                load_rows(rb + step, 0);  // next batch in flight while this one is reduced
             }
 #pragma unroll
             for (int u = 0; u < DG_U; ++u) {
@@ -152,8 +208,16 @@ __global__ void __launch_bounds__(DG_MAX_WARPS * 32, 2) spif_dense_gemv_kernel(c
     }
 }
 
-template <typename WT, int VL, int EPI>
+template <typename WT, int VL, int EPI, bool ASYNC>
 static int launch_dg(const DenseGemvParams & p, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+    if (smem > 48 * 1024) {
+        static bool done = false;  // per instantiation
+        if (!done) {
+            SPIF_CUDA_TRY(cudaFuncSetAttribute(spif_dense_gemv_kernel<WT, VL, EPI, ASYNC>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            done = true;
+        }
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = grid;
     cfg.blockDim           = dim3(threads);
@@ -164,19 +228,29 @@ static int launch_dg(const DenseGemvParams & p, dim3 grid, int threads, size_t s
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs                                        = at;
     cfg.numAttrs                                     = 1;
-    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_dense_gemv_kernel<WT, VL, EPI>, p));
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_dense_gemv_kernel<WT, VL, EPI, ASYNC>, p));
     return 0;
 }
 
 template <typename WT, int EPI>
-static int launch_dg_v(int vl, const DenseGemvParams & p, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+static int launch_dg_v(int vl, bool async, const DenseGemvParams & p, dim3 grid, int threads, size_t smem, cudaStream_t stream) {
+    if (async) {
+        switch (vl) {
+            case 1:
+                return launch_dg<WT, 1, EPI, true>(p, grid, threads, smem, stream);
+            case 2:
+                return launch_dg<WT, 2, EPI, true>(p, grid, threads, smem, stream);
+            default:
+                return launch_dg<WT, 4, EPI, true>(p, grid, threads, smem, stream);
+        }
+    }
     switch (vl) {
         case 1:
-            return launch_dg<WT, 1, EPI>(p, grid, threads, smem, stream);
+            return launch_dg<WT, 1, EPI, false>(p, grid, threads, smem, stream);
         case 2:
-            return launch_dg<WT, 2, EPI>(p, grid, threads, smem, stream);
+            return launch_dg<WT, 2, EPI, false>(p, grid, threads, smem, stream);
         default:
-            return launch_dg<WT, 4, EPI>(p, grid, threads, smem, stream);
+            return launch_dg<WT, 4, EPI, false>(p, grid, threads, smem, stream);
     }
 }
 
@@ -208,23 +282,33 @@ static int dense_gemv(int type, int epi, const void * w, const float * bias, con
         p.nrw         = p.nrw > cap ? cap : p.nrw;
     }
     const int threads = p.ns * p.nrw * 32;
-    const int per_sm  = (2 * DG_MAX_WARPS * 32) / threads;  // CTAs that fit the 2 x 384-thread register budget
+    int       per_sm  = (2 * DG_MAX_WARPS * 32) / threads;  // CTAs that fit the 2 x 384-thread register budget
+    // cp.async ring variant (see the top of the file): SPIF_DG_ASYNC=1
+    static const int k_async = [] { const char * e = getenv("SPIF_DG_ASYNC"); return e ? atoi(e) : 0; }();
+    const bool   async      = k_async != 0;
+    const size_t ring_bytes = async ? (size_t) DG_DEPTH * DG_U * vl * 16 * threads : 0;
+    if (async) {
+        const int by_smem = (int) ((200 * 1024) / (ring_bytes + 2048));
+        per_sm            = per_sm > by_smem ? by_smem : per_sm;
+    }
     const int G       = ctx.sm_count * (per_sm < 1 ? 1 : per_sm);
     p.rpc             = (rows + G - 1) / G;
     // keep every row lane busy: at least nrw rows per CTA when there are enough rows
     if (p.rpc < p.nrw) {
         p.rpc = p.nrw;
     }
-    const int    grid_x = (rows + p.rpc - 1) / p.rpc;
-    const size_t smem   = (p.ns > 1) ? sizeof(float) * (size_t) p.rpc * p.ns : 0;
-    SPIF_REQUIRE(smem <= 48 * 1024, SPIF_E_SHAPE);
+    const int    grid_x    = (rows + p.rpc - 1) / p.rpc;
+    const size_t part_b    = (p.ns > 1) ? sizeof(float) * (size_t) ((p.rpc * p.ns + 3) / 4 * 4) : 0;
+    SPIF_REQUIRE(part_b <= 48 * 1024, SPIF_E_SHAPE);
+    const size_t smem = part_b + ring_bytes;
+    SPIF_REQUIRE(smem <= 200 * 1024, SPIF_E_SHAPE);
     const dim3 grid(grid_x, n_tok);
     if (type == SPIF_TYPE_F16) {
-        return epi == DG_EPI_RELU ? launch_dg_v<spif_f16, DG_EPI_RELU>(vl, p, grid, threads, smem, ctx.stream) :
-                                    launch_dg_v<spif_f16, DG_EPI_SIGMOID>(vl, p, grid, threads, smem, ctx.stream);
+        return epi == DG_EPI_RELU ? launch_dg_v<spif_f16, DG_EPI_RELU>(vl, async, p, grid, threads, smem, ctx.stream) :
+                                    launch_dg_v<spif_f16, DG_EPI_SIGMOID>(vl, async, p, grid, threads, smem, ctx.stream);
     }
-    return epi == DG_EPI_RELU ? launch_dg_v<spif_bf16, DG_EPI_RELU>(vl, p, grid, threads, smem, ctx.stream) :
-                                launch_dg_v<spif_bf16, DG_EPI_SIGMOID>(vl, p, grid, threads, smem, ctx.stream);
+    return epi == DG_EPI_RELU ? launch_dg_v<spif_bf16, DG_EPI_RELU>(vl, async, p, grid, threads, smem, ctx.stream) :
+                                launch_dg_v<spif_bf16, DG_EPI_SIGMOID>(vl, async, p, grid, threads, smem, ctx.stream);
 }
 
 int spif_launch_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,

@@ -15,11 +15,10 @@ except Exception as e:
     print(n, 'FAILED', e)
 PY
 }
-run small_w6 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=6
-run small_w7 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=7
-run small_w9 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=9
-run small_w5 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=5
-run small_w6_vl2 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=6 SPIF_DG_VL=2
-run small_w8_vl2 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=8 SPIF_DG_VL=2
-run small_w12_vl2 SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=12 SPIF_DG_VL=2
-run small_w6_serial SPIF_DIRECT_SMALL=1 SPIF_DG_WARPS=6 SPIF_X=1
+run base X=0
+run async_w6 SPIF_DG_ASYNC=1
+run async_w7 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=7
+run async_w4 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=4
+run async_w12 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=12
+run async_w6_redfirst SPIF_DG_ASYNC=1 SPIF_RED_FIRST=1
+run async_w3 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=3

@@ -178,3 +178,35 @@ def test_balancer_swaps_rows_world2_gloo():
         assert res["imbalance_after"] < res["imbalance_before"] and res["imbalance_after"] < 1.1
         assert abs(again_before - res["imbalance_after"]) < 1e-6
     assert got[0][4] == got[1][4], "slot tables diverged between the ranks"
+
+
+def test_rebalance_plan_matches_exhaustive_pair_search():
+    """the sorted-search pair selection picks a pair with the same cost as the n x n table it replaced"""
+    from sparkinfer_b200 import placement as P
+
+    def exhaustive(d, shard, G, max_swaps):
+        shard = shard.copy()
+        for _ in range(max_swaps):
+            ld = P.shard_loads(d, shard, G)
+            hot, cold = int(ld.argmax()), int(ld.argmin())
+            if ld[hot] - ld[cold] <= 0:
+                break
+            gh, gc = np.nonzero(shard == hot)[0], np.nonzero(shard == cold)[0]
+            delta = d[gh][:, None] - d[gc][None, :]
+            cost = np.maximum(ld[hot] - delta, ld[cold] + delta)
+            cost[delta <= 0] = np.inf
+            i, j = np.unravel_index(np.argmin(cost), cost.shape)
+            if not np.isfinite(cost[i, j]) or ld[hot] - cost[i, j] <= 0:
+                break
+            shard[gh[i]], shard[gc[j]] = cold, hot
+        return P.imbalance(d, shard, G)
+
+    rng = np.random.default_rng(3)
+    for G in (2, 4, 8):
+        n = G * 48
+        d = rng.random(n) ** 3
+        shard = np.repeat(np.arange(G), n // G).astype(np.int32)[np.argsort(np.argsort(-d))]   # hottest block on shard 0
+        plan, new = P.rebalance_plan(d, shard, G, max_swaps=24)
+        assert np.all(np.bincount(new, minlength=G) == n // G)
+        assert abs(P.imbalance(d, new, G) - exhaustive(d, shard, G, 24)) < 1e-9
+        assert P.imbalance(d, new, G) < P.imbalance(d, shard, G)

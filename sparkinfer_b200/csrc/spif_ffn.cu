@@ -333,7 +333,9 @@ static int spif_launch_ffn_direct(const spif_ffn_args & a, void * ws, size_t ws_
     const int  vpt     = (V <= 640 && !small) ? 1 : 2;
     const int  threads = ((V + vpt - 1) / vpt + 31) / 32 * 32;
     SPIF_REQUIRE(a.m <= 4096 * (threads / 32), SPIF_E_UNSUPPORTED);  // activity bits kept in registers by build_my_list
-    const int P = ctx.sm_count;
+    // SPIF_FFN_CTAS < SM count leaves whole SMs to the look-ahead predictor grid (experiment knob; 0 = one CTA per SM)
+    static const int k_ffn_ctas = [] { const char * e = getenv("SPIF_FFN_CTAS"); return e ? atoi(e) : 0; }();
+    const int        P          = (k_ffn_ctas > 0 && k_ffn_ctas < ctx.sm_count) ? k_ffn_ctas : ctx.sm_count;
     SPIF_REQUIRE(P >= 1 && P <= SPIF_RED_LANES * SPIF_RED_PER, SPIF_E_UNSUPPORTED);
     SPIF_REQUIRE(a.neuron_idx != nullptr || a.m == a.n_ff, SPIF_E_SHAPE);
     SPIF_REQUIRE(a.sparse_idx != nullptr, SPIF_E_NULL);

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 run() {
     name=$1; shift
-    env "$@" timeout 120 python bench.py --steps 1000 --warmup 10 --no-batched --no-cpu-baseline > gpurun_out/v3_$name.json 2> gpurun_out/v3_$name.err
+    env "$@" timeout 120 python bench.py --steps 600 --warmup 10 --no-batched --no-cpu-baseline > gpurun_out/v3_$name.json 2> gpurun_out/v3_$name.err
     python - "$name" <<'PY'
 import json, sys
 n = sys.argv[1]
@@ -15,10 +15,7 @@ except Exception as e:
     print(n, 'FAILED', e)
 PY
 }
-run base X=0
-run async_w6 SPIF_DG_ASYNC=1
-run async_w7 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=7
-run async_w4 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=4
-run async_w12 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=12
-run async_w6_redfirst SPIF_DG_ASYNC=1 SPIF_RED_FIRST=1
-run async_w3 SPIF_DG_ASYNC=1 SPIF_DG_WARPS=3
+run p132 SPIF_FFN_CTAS=132
+run p120 SPIF_FFN_CTAS=120
+run p104 SPIF_FFN_CTAS=104
+run p120_w12 SPIF_FFN_CTAS=120 SPIF_DG_WARPS=12

@@ -294,7 +294,8 @@ def run_ours(a):
 
     act = shard_activity()
     balance = {"placement": a.placement if world > 1 else "single shard",
-               "active_rows_imbalance": float((act.max(axis=0) / np.maximum(act.mean(axis=0), 1e-9)).mean())}
+               "active_rows_imbalance": float((act.max(axis=0) / np.maximum(act.mean(axis=0), 1e-9)).mean()),
+               "active_rows_per_shard": [float(v) for v in act.mean(axis=1)]}
     if world > 1 and a.balance_rounds > 0:
         # the online balancer: decayed firing rates from the masks of real steps, greedy swap plan, the
         # rows of the swapped groups exchanged between the two ranks.  Weights move in place, the graphs stay valid.
@@ -318,12 +319,14 @@ def run_ours(a):
             barrier()
             t2 = time.perf_counter()
             t_obs, t_move = t_obs + (t1 - t0), t_move + (t2 - t1)
-            rounds.append({"swaps": r["swaps"], "dfr_imbalance_before": r["imbalance_before"],
+            rounds.append({"swaps": r["swaps"], "lambda": r["lambda"], "dfr_imbalance_before": r["imbalance_before"],
                            "dfr_imbalance_planned": r["imbalance_after"]})
         measure_activity()
         act2 = shard_activity()
         balance.update({"active_rows_imbalance_before": balance["active_rows_imbalance"],
                         "active_rows_imbalance": float((act2.max(axis=0) / np.maximum(act2.mean(axis=0), 1e-9)).mean()),
+                        "active_rows_per_shard_before": balance["active_rows_per_shard"],
+                        "active_rows_per_shard": [float(v) for v in act2.mean(axis=1)],
                         "tok_s_before": 1e3 / ms_before, "rounds": rounds, "tokens_observed": tok,
                         "swaps_total": bal.swaps_done, "bytes_sent_rank0": bal.bytes_moved,
                         "observe_s": t_obs, "plan_and_move_s": t_move, "dfr_launches_per_token": L})

@@ -32,11 +32,16 @@ class ShardBalancer:
 
     LAYER_CHUNK = 16
 
-    def __init__(self, layers, shard_of_group, rank, world, group=None, g=16, lam=0.9):
+    def __init__(self, layers, shard_of_group, rank, world, group=None, g=16, lam=0.9, lam_step=0.05, drift_tol=0.02):
         """layers: this rank's LayerWeights (m rows each); shard_of_group: per layer int array [n_g] (same on all ranks).
         Slot s of shard r initially holds the s-th smallest group id placed on r (placement.shard_rows order)."""
         self.layers, self.rank, self.world, self.group = layers, rank, world, group
         self.g, self.lam = g, lam
+        # adaptive decay (ggml-sparkinfer.hpp:169-173: lambda *= 1 +- SPIF_DX_DFR_DECAY/1000, clamped to [0.05, 0.95], raised
+        # when the compute had to wait for reloads, lowered otherwise).  Re-targeted: raised when the balance the last plan
+        # promised did not hold until this round (the scores were too jumpy and the swaps were wasted), lowered otherwise.
+        self.lam_step, self.drift_tol = lam_step, drift_tol
+        self._promised = None
         self.L = len(layers)
         self.n_slot = layers[0].m // g
         self.slots = []  # per layer: int32 [world, n_slot] = group id held by each slot of each shard
@@ -158,11 +163,16 @@ class ShardBalancer:
         """gather scores, plan per layer, execute.  -> dict(imbalance_before, imbalance_after (planned), swaps, bytes)"""
         sc = self.scores()
         before = self.imbalance(sc)
+        if self.lam_step > 0.0 and self._promised is not None:
+            drifted = float(np.mean(before)) > self._promised * (1.0 + self.drift_tol)
+            self.lam = float(np.clip(self.lam * (1.0 + (self.lam_step if drifted else -self.lam_step)), 0.05, 0.95))
         plans = []
         for l in range(self.L):
             plan, _ = placement.rebalance_plan(sc[l], self.shard_of_group(l), self.world, max_swaps, min_gain)
             plans.append(plan)
         moved = self.apply(plans) if self.world > 1 else 0
         after = [placement.imbalance(sc[l], self.shard_of_group(l), self.world) for l in range(self.L)]
-        return {"imbalance_before": float(np.mean(before)), "imbalance_after": float(np.mean(after)),
+        self._promised = float(np.mean(after))
+        return {"lambda": self.lam,
+                "imbalance_before": float(np.mean(before)), "imbalance_after": float(np.mean(after)),
                 "swaps": int(sum(len(p) for p in plans)), "bytes_sent_this_rank": int(moved)}

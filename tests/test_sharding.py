@@ -153,7 +153,11 @@ def _balancer_worker(rank, world, port, q):
             ok &= bool(np.array_equal(bal.dfr[l].numpy(), hots[l][mine].astype(np.float32)))   # scores moved with the rows
             ok &= sorted(np.concatenate(list(bal.slots[l])).tolist()) == list(range(n_g))        # still a partition
         again = bal.rebalance(max_swaps=6)                   # scores() after the move must reproduce the planned state
-        q.put((rank, ok, res, again["imbalance_before"], [s.tolist() for s in bal.slots]))
+        lam_calm = bal.lam                                    # the promised balance held -> decay lowered (more reactive)
+        for l in range(L):                                    # hotness changes completely: the promise cannot hold
+            bal.dfr[l] = torch.from_numpy(np.sort(hots[(l + 1) % L])[::-1][rank::world].copy().astype(np.float32))
+        bal.rebalance(max_swaps=6)
+        q.put((rank, ok, res, again["imbalance_before"], [s.tolist() for s in bal.slots], lam_calm, bal.lam))
     finally:
         dist.destroy_process_group()
 
@@ -172,7 +176,9 @@ def test_balancer_swaps_rows_world2_gloo():
         pr.join(timeout=60)
         assert pr.exitcode == 0
     got.sort(key=lambda t: t[0])
-    for _, ok, res, again_before, _ in got:
+    for _, ok, res, again_before, _, lam_calm, lam_drift in got:
+        # adaptive decay (ggml-sparkinfer.hpp:169-173): 0.9 * 0.95 after a round whose promise held, * 1.05 after one that did not
+        assert abs(lam_calm - 0.9 * 0.95) < 1e-6 and abs(lam_drift - 0.9 * 0.95 * 1.05) < 1e-6
         assert ok, "rows / bias / scores in a slot do not belong to the group the slot table names"
         assert res["swaps"] > 0 and res["bytes_sent_this_rank"] > 0
         assert res["imbalance_after"] < res["imbalance_before"] and res["imbalance_after"] < 1.1

@@ -195,6 +195,21 @@ int spif_sparse_ffn_sharded(const spif_ffn_args * args, const spif_shard_comm * 
 int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,
                     float * dfr_scores, spif_stream_t stream);
 
+/* ---- shard placement and swap planning (host code, no device work) ------------------------------------------------
+ * Replaces the planning half of the reference's cache manager (sparkinfer_reload_plan, src/llama-sparkinfer.cpp:45-91:
+ * scores -> copy_pair list, ggml-sparkinfer.hpp:16-24), re-targeted from "which groups live on the GPU" to "which GPU
+ * shard holds which group" (SURVEY.md 8e).  Every group is on exactly one of n_shards shards, equal group count per shard.
+ *
+ * spif_initial_placement: groups sorted by hotness (descending, ties by index), dealt to the shards in snake order ->
+ *   shard_of_group[n_g].  n_g % n_shards == 0.
+ * spif_rebalance_plan: up to max_swaps times, take the most- and the least-loaded shard (load = sum of dfr over its groups)
+ *   and swap the pair of groups (one from each) that lowers the larger of the two loads most; stop when the gain is
+ *   <= min_gain.  shard_of_group is updated in place; plan[4*i .. 4*i+3] = {group leaving the hot shard, group leaving the
+ *   cold shard, hot shard, cold shard}; *n_swaps = number of swaps planned.  The executor moves the rows. */
+int spif_initial_placement(const float * group_hotness, int n_g, int n_shards, int32_t * shard_of_group);
+int spif_rebalance_plan(const float * dfr, int32_t * shard_of_group, int n_g, int n_shards, int max_swaps, float min_gain,
+                        int32_t * plan, int * n_swaps);
+
 #ifdef __cplusplus
 }
 #endif

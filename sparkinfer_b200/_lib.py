@@ -46,6 +46,8 @@ SYMBOLS = {
     "spif_shard_comm_data_bytes": (c_sz, [c_i, c_i]),
     "spif_shard_allreduce": (c_i, [c_vp, c_i64, ctypes.POINTER(ShardCommStruct), c_vp]),
     "spif_sparse_ffn_sharded": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
+    "spif_initial_placement": (c_i, [c_vp, c_i, c_i, c_vp]),
+    "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
 }
 
 _lib = None

@@ -11,7 +11,7 @@ addresses never change, captured CUDA graphs stay valid.
 Division of labour:
   observe()    one spif_dfr_update launch per layer on this rank's masks  (CUDA, C-ABI)
   scores()     all_gather of the per-slot scores -> global score per group (torch.distributed)
-  rebalance()  placement.rebalance_plan per layer (host, identical on every rank) + the row exchange
+  rebalance()  spif_rebalance_plan per layer (host code in the library, identical on every rank) + the row exchange
 The plan only depends on gathered data, so every rank derives the same one without a coordinator.
 """
 import numpy as np
@@ -166,9 +166,10 @@ class ShardBalancer:
         if self.lam_step > 0.0 and self._promised is not None:
             drifted = float(np.mean(before)) > self._promised * (1.0 + self.drift_tol)
             self.lam = float(np.clip(self.lam * (1.0 + (self.lam_step if drifted else -self.lam_step)), 0.05, 0.95))
+        from . import ops
         plans = []
-        for l in range(self.L):
-            plan, _ = placement.rebalance_plan(sc[l], self.shard_of_group(l), self.world, max_swaps, min_gain)
+        for l in range(self.L):  # planner = host code inside the library (spif_rebalance_plan); placement.py mirrors it
+            plan, _ = ops.rebalance_plan(sc[l], self.shard_of_group(l), self.world, max_swaps, min_gain)
             plans.append(plan)
         moved = self.apply(plans) if self.world > 1 else 0
         after = [placement.imbalance(sc[l], self.shard_of_group(l), self.world) for l in range(self.L)]

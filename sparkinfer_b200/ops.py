@@ -213,3 +213,28 @@ def dfr_update(sparse_idx, dfr_scores, g, lam, ema=True, thr=SPARSE_THRESHOLD):
     check(L.spif_dfr_update(_p(sparse_idx), n_ff, n_tok, g, thr, lam, 1 if ema else 0, _p(dfr_scores), _stream()),
           "spif_dfr_update")
     return dfr_scores
+
+
+# -- shard placement / swap planning (host code inside the library, no device work) -------------------------------------
+def initial_placement(group_hotness, n_shards):
+    """spif_initial_placement: snake-deal of the groups sorted by hotness -> int32 shard_of_group[n_g]"""
+    import numpy as np
+    L = _lib.load()
+    h = np.ascontiguousarray(group_hotness, dtype=np.float32)
+    out = np.empty(h.size, dtype=np.int32)
+    check(L.spif_initial_placement(h.ctypes.data, h.size, n_shards, out.ctypes.data), "spif_initial_placement")
+    return out
+
+
+def rebalance_plan(dfr, shard_of_group, n_shards, max_swaps=8, min_gain=0.0):
+    """spif_rebalance_plan (the re-targeted sparkinfer_reload_plan, src/llama-sparkinfer.cpp:45-91)
+    -> (list of (group_from_hot_shard, group_from_cold_shard, hot_shard, cold_shard), new shard_of_group)"""
+    import numpy as np
+    L = _lib.load()
+    d = np.ascontiguousarray(dfr, dtype=np.float32)
+    shard = np.array(shard_of_group, dtype=np.int32, copy=True)
+    plan = np.zeros((max(int(max_swaps), 1), 4), dtype=np.int32)
+    n = ctypes.c_int(0)
+    check(L.spif_rebalance_plan(d.ctypes.data, shard.ctypes.data, d.size, n_shards, int(max_swaps), float(min_gain),
+                                plan.ctypes.data, ctypes.byref(n)), "spif_rebalance_plan")
+    return [tuple(r) for r in plan[:n.value].tolist()], shard

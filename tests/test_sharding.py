@@ -216,3 +216,29 @@ def test_rebalance_plan_matches_exhaustive_pair_search():
         assert np.all(np.bincount(new, minlength=G) == n // G)
         assert abs(P.imbalance(d, new, G) - exhaustive(d, shard, G, 24)) < 1e-9
         assert P.imbalance(d, new, G) < P.imbalance(d, shard, G)
+
+
+def test_c_abi_planner_matches_host_logic():
+    """spif_initial_placement / spif_rebalance_plan (host code in libspif_b200.so, no GPU needed) take the same decisions
+    as placement.py on float32 scores, tie-breaks included"""
+    import ctypes
+    from sparkinfer_b200 import _lib, placement as P
+    L = _lib.load()
+    rng = np.random.default_rng(9)
+    for G, n_g in ((2, 64), (4, 864), (8, 1792)):
+        d = (rng.random(n_g) ** 3).astype(np.float32)
+        d[::7] = d[3]                                           # plenty of exact ties
+        got = np.empty(n_g, dtype=np.int32)
+        assert L.spif_initial_placement(d.ctypes.data, n_g, G, got.ctypes.data) == 0
+        assert np.array_equal(got, P.initial_placement(d, G))
+        shard = np.repeat(np.arange(G), n_g // G).astype(np.int32)[np.argsort(np.argsort(-d, kind="stable"), kind="stable")]
+        want_plan, want_shard = P.rebalance_plan(d, shard, G, max_swaps=32)
+        mine = shard.copy()
+        plan = np.zeros((32, 4), dtype=np.int32)
+        n = ctypes.c_int(0)
+        assert L.spif_rebalance_plan(d.ctypes.data, mine.ctypes.data, n_g, G, 32, 0.0, plan.ctypes.data, ctypes.byref(n)) == 0
+        assert n.value == len(want_plan) and n.value > 0
+        assert [tuple(r) for r in plan[:n.value].tolist()] == [tuple(int(v) for v in r) for r in want_plan]
+        assert np.array_equal(mine, want_shard)
+    bad = np.zeros(6, dtype=np.int32)
+    assert L.spif_initial_placement(np.zeros(6, np.float32).ctypes.data, 6, 4, bad.ctypes.data) != 0   # 6 % 4 != 0

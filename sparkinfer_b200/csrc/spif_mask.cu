@@ -4,6 +4,8 @@
 // Reference: the mask is the float tensor `sparse_idx`; no index list is ever built (mm-sparse.cu:22, axpy-sparse.cu:53).
 // fatrelu / shifted_step: ggml/src/ggml-cuda/unary.cu:564-652.  build_dfr: src/llama-graph.cpp:910-930 with
 // op_scale_add(_ema) ggml/src/ggml-cuda/binbcast.cu:26-42.
+#include <cooperative_groups.h>
+
 #include "spif_common.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -334,7 +336,181 @@ __global__ void __launch_bounds__(1024) spif_topk_mask_reg_kernel(const float * 
     }
 }
 
+// Cluster variant (EXPERIMENTAL, off unless SPIF_TOPK_CLUSTER=1 -- not yet validated on hardware): one cluster of
+// TK_CL CTAs per token.  Every CTA keeps 1/TK_CL of the keys in registers and a private histogram; after one cluster
+// barrier per pass each CTA sums the TK_CL histograms through distributed shared memory and takes the SAME decision, so
+// no result has to be broadcast.  Index ranges ascend with (cluster rank, warp, slot, lane): the tie-break order is the
+// same as in the single-CTA kernels.  Meant for the Llama-3-8B top-k chain where the 1-CTA kernel (16 us) is the longest
+// link (open items).
+#define TK_CL      8
+#define TK_THREADS 256
+template <int KPT>
+__global__ void __launch_bounds__(TK_THREADS) spif_topk_mask_cluster_kernel(const float * __restrict__ score, int n_ff, int k,
+                                                                            float * __restrict__ out) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group   cluster = cg::this_cluster();
+    __shared__ int      hist[2][256];  // double-buffered: a peer may still read pass p while pass p+1 is being zeroed
+    __shared__ int      ghist[256];
+    __shared__ uint32_t s_prefix, s_prefix_mask;
+    __shared__ int      s_k;
+    __shared__ int      warp_cnt[TK_THREADS / 32];
+    __shared__ int      s_cta_eq;
+    const float *       sc = score + (size_t) blockIdx.y * n_ff;
+    float *             o  = out + (size_t) blockIdx.y * n_ff;
+    const int           tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int           rank   = (int) cluster.block_rank();
+    const int           nwarp  = TK_THREADS / 32;
+    const int           wchunk = ((n_ff + TK_CL * nwarp - 1) / (TK_CL * nwarp) + 31) / 32 * 32;  // <= 32 * KPT (launcher)
+    const int           r0 = min((rank * nwarp + warp) * wchunk, n_ff), r1 = min(r0 + wchunk, n_ff);
+    if (k <= 0 || k >= n_ff) {  // uniform over the cluster: nobody reaches a barrier
+        for (int i = r0 + lane; i < r1; i += 32) {
+            o[i] = (k <= 0) ? 0.f : 1.f;
+        }
+        return;
+    }
+    uint32_t key[KPT];
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        const int i = r0 + j * 32 + lane;
+        key[j]      = (i < r1) ? float_key(sc[i]) : 0u;
+    }
+    if (tid == 0) {
+        s_prefix      = 0;
+        s_prefix_mask = 0;
+        s_k           = k;
+    }
+    for (int pass = 3; pass >= 0; --pass) {
+        int * h = hist[pass & 1];
+        for (int i = tid; i < 256; i += TK_THREADS) {
+            h[i] = 0;
+        }
+        __syncthreads();
+        const uint32_t pre = s_prefix, pmask = s_prefix_mask;
+        const int      sh  = pass * 8;
+#pragma unroll
+        for (int j = 0; j < KPT; ++j) {
+            if (r0 + j * 32 >= r1) {
+                continue;  // warp-uniform
+            }
+            const bool     in  = (r0 + j * 32 + lane < r1) && ((key[j] & pmask) == pre);
+            const unsigned dig = in ? ((key[j] >> sh) & 255u) : 0x1000u;
+            if (pass == 3) {
+                const unsigned grp = __match_any_sync(0xffffffffu, dig);
+                if (in && (__ffs(grp) - 1) == lane) {
+                    atomicAdd(&h[dig], __popc(grp));
+                }
+            } else if (in) {
+                atomicAdd(&h[dig], 1);
+            }
+        }
+        cluster.sync();  // every CTA's histogram of this pass is complete (and visible cluster-wide)
+        {
+            int sum = 0;
+#pragma unroll
+            for (int r = 0; r < TK_CL; ++r) {
+                sum += cluster.map_shared_rank(h, r)[tid];  // TK_THREADS == 256 bins
+            }
+            ghist[tid] = sum;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            int own[8], sum = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                own[j] = ghist[lane * 8 + j];
+                sum += own[j];
+            }
+            int above = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_down_sync(0xffffffffu, above, d);
+                above += (lane + d < 32) ? t : 0;
+            }
+            above -= sum;
+            const int need = s_k;
+            __syncwarp();
+            if (above < need && need <= above + sum) {
+                int rem = need - above, bdig = lane * 8 + 7;
+#pragma unroll
+                for (int j = 7; j >= 0; --j) {
+                    if (rem > 0 && own[j] >= rem) {
+                        bdig = lane * 8 + j;
+                        s_k  = rem;
+                        rem  = -1;
+                    } else if (rem > 0) {
+                        rem -= own[j];
+                    }
+                }
+                s_prefix      = pre | ((uint32_t) bdig << sh);
+                s_prefix_mask = pmask | (255u << sh);
+            }
+        }
+        __syncthreads();
+    }
+    const uint32_t kth     = s_prefix;
+    const int      need_eq = s_k;
+    int            cnt = 0;
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        cnt += __popc(__ballot_sync(0xffffffffu, (r0 + j * 32 + lane < r1) && key[j] == kth));
+    }
+    if (lane == 0) {
+        warp_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int t = 0;
+        for (int w = 0; w < nwarp; ++w) {
+            t += warp_cnt[w];
+        }
+        s_cta_eq = t;
+    }
+    cluster.sync();
+    int run = 0;
+    for (int r = 0; r < rank; ++r) {
+        run += *cluster.map_shared_rank(&s_cta_eq, r);
+    }
+    for (int w = 0; w < warp; ++w) {
+        run += warp_cnt[w];
+    }
+#pragma unroll
+    for (int j = 0; j < KPT; ++j) {
+        const int      i  = r0 + j * 32 + lane;
+        const unsigned bj = __ballot_sync(0xffffffffu, (i < r1) && key[j] == kth);
+        if (i < r1) {
+            bool sel = key[j] > kth;
+            if (key[j] == kth) {
+                sel = (run + __popc(bj & ((1u << lane) - 1u))) < need_eq;
+            }
+            o[i] = sel ? 1.0f : 0.0f;
+        }
+        run += __popc(bj);
+    }
+    cluster.sync();  // no CTA may exit while a peer can still read its shared memory
+}
+
+static int launch_topk_cluster(const float * score, int n_ff, int n_tok, int k, float * out, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(TK_CL, n_tok);
+    cfg.blockDim           = dim3(TK_THREADS);
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id               = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = TK_CL;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs              = at;
+    cfg.numAttrs           = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_topk_mask_cluster_kernel<8>, score, n_ff, k, out));
+    return 0;
+}
+
 int spif_launch_topk_mask(const float * score, int n_ff, int n_tok, int k, float * out, cudaStream_t stream) {
+    // experimental cluster kernel: read per call so that a test can switch it on (see above; default off)
+    const char * e_cl = getenv("SPIF_TOPK_CLUSTER");
+    if (e_cl && atoi(e_cl) != 0 && n_ff <= TK_CL * TK_THREADS * 8) {
+        return launch_topk_cluster(score, n_ff, n_tok, k, out, stream);
+    }
     if (n_ff <= 16 * 1024) {
         spif_topk_mask_reg_kernel<16><<<n_tok, 1024, 0, stream>>>(score, n_ff, k, out);
     } else if (n_ff <= 32 * 1024) {

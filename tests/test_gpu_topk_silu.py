@@ -4,6 +4,8 @@ The reference has NO code for this (LLM_ARCH_LLAMA never loads predictor tensors
 build_sparse_ffn aborts for non-ReLU archs, src/llama-graph.cpp:1092-1093): the oracle is our own restatement
 (h = silu(g) * u on the rows of the k largest predictor logits, ties -> lower index) -- PARITY UNPINNED by the reference,
 as stated in DESIGN.md.  -m gpu."""
+import os
+
 import numpy as np
 import pytest
 
@@ -35,6 +37,25 @@ def test_topk_mask_bit_exact(oracle, n_ff, n_tok, k):
         ref = oracle.topk_mask(score[t], k)
         assert np.array_equal(got[t], ref), (t, int((got[t] != ref).sum()))
         assert int(got[t].sum()) == min(max(k, 0), n_ff)
+
+
+@pytest.mark.skipif(os.environ.get("SPIF_EXPERIMENTAL") != "1",
+                    reason="cluster top-k kernel is experimental (off by default): SPIF_EXPERIMENTAL=1 to run")
+@pytest.mark.parametrize("n_ff,n_tok,k", [(14336, 1, 1434), (14336, 4, 2867), (1000, 3, 1), (1000, 2, 999), (4096, 1, 0),
+                                          (4096, 1, 4096), (16384, 2, 5000), (8191, 3, 4000)])
+def test_topk_mask_cluster_variant(oracle, n_ff, n_tok, k):
+    """the 8-CTA cluster radix select (SPIF_TOPK_CLUSTER=1) against the oracle, ties included"""
+    import sparkinfer_b200 as sp
+    rng = np.random.default_rng(synth.SEED0 + 3 * n_ff + k)
+    score = rng.normal(0, 1, (n_tok, n_ff)).astype(np.float32)
+    score[:, ::3] = np.round(score[:, ::3] * 4) / 4
+    os.environ["SPIF_TOPK_CLUSTER"] = "1"
+    try:
+        got = sp.topk_mask(dev(score), k).cpu().numpy()
+    finally:
+        os.environ.pop("SPIF_TOPK_CLUSTER", None)
+    for t in range(n_tok):
+        assert np.array_equal(got[t], oracle.topk_mask(score[t], k)), t
 
 
 @pytest.mark.parametrize("wtype", [F16, BF16])

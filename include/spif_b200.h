@@ -207,6 +207,17 @@ int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float 
  *   <= min_gain.  shard_of_group is updated in place; plan[4*i .. 4*i+3] = {group leaving the hot shard, group leaving the
  *   cold shard, hot shard, cold shard}; *n_swaps = number of swaps planned.  The executor moves the rows. */
 int spif_initial_placement(const float * group_hotness, int n_g, int n_shards, int32_t * shard_of_group);
+/* Load-time half of the cache manager (sparkinfer_cache_manager ctor, src/llama-sparkinfer.cpp:179-202, 283-323):
+ * spif_cache_group_budget: groups per layer that fit `vram_budget` bytes -- budget = vram_budget / (group_bytes * (has_gate ?
+ *   3 : 2)); layer l starts with min((int)(budget * pattern[l]), n_group) (pattern = the model-split file's
+ *   `ffn_normalized_pattern`), the remainder is dealt round-robin, one group per layer per turn, to layers that are not full.
+ *   On a B200 every layer is normally full (m == n_ff, the reference's gpu_only); smaller budgets give the GPU-cache subset
+ *   that spif_mul_mat_sparse / spif_axpy_sparse address through neuron_idx.
+ * spif_reorder_rows: dst row new = src row perm[new] (`blk.N.ffn_reorder_perms`, new_row -> old_row, :283-304); host
+ *   memory, dst != src, row_bytes per row (a 1-D tensor is n rows of its element size).                                   */
+int spif_cache_group_budget(int64_t vram_budget, int64_t group_bytes, int has_gate, const float * pattern, int n_layer,
+                            int n_group, int32_t * groups_per_layer);
+int spif_reorder_rows(const void * src, void * dst, const int32_t * perm, int64_t n_rows, int64_t row_bytes);
 int spif_rebalance_plan(const float * dfr, int32_t * shard_of_group, int n_g, int n_shards, int max_swaps, float min_gain,
                         int32_t * plan, int * n_swaps);
 

@@ -48,6 +48,8 @@ SYMBOLS = {
     "spif_sparse_ffn_sharded": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
     "spif_initial_placement": (c_i, [c_vp, c_i, c_i, c_vp]),
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
+    "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),
+    "spif_reorder_rows": (c_i, [c_vp, c_vp, c_vp, c_i64, c_i64]),
 }
 
 _lib = None

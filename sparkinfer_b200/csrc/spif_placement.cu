@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <limits>
 #include <numeric>
 #include <vector>
@@ -104,5 +105,57 @@ extern "C" int spif_rebalance_plan(const float * dfr, int32_t * shard_of_group, 
         plan[4 * n + 0] = a, plan[4 * n + 1] = b, plan[4 * n + 2] = hot, plan[4 * n + 3] = cold;
     }
     *n_swaps = n;
+    return 0;
+}
+
+// sparkinfer_cache_manager ctor, src/llama-sparkinfer.cpp:183-202: per-layer share of the VRAM budget, then round-robin
+extern "C" int spif_cache_group_budget(int64_t vram_budget, int64_t group_bytes, int has_gate, const float * pattern,
+                                       int n_layer, int n_group, int32_t * groups_per_layer) {
+    if (!pattern || !groups_per_layer) {
+        return SPIF_E_NULL;
+    }
+    if (vram_budget < 0 || group_bytes <= 0 || n_layer <= 0 || n_group <= 0) {
+        return SPIF_E_SHAPE;
+    }
+    const int budget = (int) std::min<int64_t>(vram_budget / (group_bytes * (has_gate ? 3 : 2)), (int64_t) n_layer * n_group);
+    int       used   = 0;
+    for (int il = 0; il < n_layer; ++il) {
+        const int init       = std::min<int>((int) ((float) budget * pattern[il]), n_group);  // int * float, truncated (:185)
+        groups_per_layer[il] = init < 0 ? 0 : init;
+        used += groups_per_layer[il];
+    }
+    for (int left = budget - used; left > 0;) {
+        const int before = left;
+        for (int il = 0; il < n_layer && left > 0; ++il) {
+            if (groups_per_layer[il] < n_group) {
+                ++groups_per_layer[il];
+                --left;
+            }
+        }
+        if (left == before) {
+            break;  // every layer is full
+        }
+    }
+    return 0;
+}
+
+// reorder_tensor_2d / _1d, src/llama-sparkinfer.cpp:285-311
+extern "C" int spif_reorder_rows(const void * src, void * dst, const int32_t * perm, int64_t n_rows, int64_t row_bytes) {
+    if (!src || !dst || !perm) {
+        return SPIF_E_NULL;
+    }
+    if (n_rows < 0 || row_bytes <= 0 || src == dst) {
+        return SPIF_E_SHAPE;
+    }
+    for (int64_t i = 0; i < n_rows; ++i) {
+        if (perm[i] < 0 || perm[i] >= n_rows) {
+            return SPIF_E_SHAPE;
+        }
+    }
+    const unsigned char * s = (const unsigned char *) src;
+    unsigned char *       d = (unsigned char *) dst;
+    for (int64_t i = 0; i < n_rows; ++i) {
+        std::memcpy(d + i * row_bytes, s + (int64_t) perm[i] * row_bytes, (size_t) row_bytes);
+    }
     return 0;
 }

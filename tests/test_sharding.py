@@ -242,3 +242,51 @@ def test_c_abi_planner_matches_host_logic():
         assert np.array_equal(mine, want_shard)
     bad = np.zeros(6, dtype=np.int32)
     assert L.spif_initial_placement(np.zeros(6, np.float32).ctypes.data, 6, 4, bad.ctypes.data) != 0   # 6 % 4 != 0
+
+
+def test_c_abi_cache_budget_and_reorder():
+    """load-time half of the cache manager (src/llama-sparkinfer.cpp:179-202, 283-311): groups per layer from the
+    model-split file's normalized pattern, and the new_row -> old_row row reorder; host code, no GPU"""
+    from sparkinfer_b200 import _lib
+    L = _lib.load()
+    rng = np.random.default_rng(21)
+
+    def reference_budget(vram, group_bytes, gate, pattern, n_group):
+        budget = int(vram // (group_bytes * (3 if gate else 2)))
+        out = [min(int(np.float32(budget) * np.float32(p)), n_group) for p in pattern]
+        left = budget - sum(out)
+        while left > 0:
+            before = left
+            for il in range(len(out)):
+                if left > 0 and out[il] < n_group:
+                    out[il] += 1
+                    left -= 1
+            if left == before:
+                break
+        return out
+
+    for n_layer, n_group, gate in ((40, 864, 1), (32, 896, 1), (24, 512, 0)):
+        group_bytes = 16 * 2 * 5120
+        pattern = rng.random(n_layer).astype(np.float32)
+        pattern /= pattern.sum()
+        for frac in (0.0, 0.13, 0.5, 0.97, 1.0, 3.0):
+            vram = int(frac * n_layer * n_group * group_bytes * (3 if gate else 2))
+            got = np.zeros(n_layer, dtype=np.int32)
+            assert L.spif_cache_group_budget(vram, group_bytes, gate, pattern.ctypes.data, n_layer, n_group, got.ctypes.data) == 0
+            want = reference_budget(vram, group_bytes, gate, pattern, n_group)
+            if frac <= 1.0:
+                assert got.tolist() == want, (n_layer, frac)
+            assert got.max() <= n_group and (frac < 1.0 or np.all(got == n_group))       # full budget -> gpu_only everywhere
+
+    n, rb = 1000, 34 * 5
+    src = rng.integers(0, 256, (n, rb), dtype=np.uint8)
+    perm = rng.permutation(n).astype(np.int32)
+    dst = np.zeros_like(src)
+    assert L.spif_reorder_rows(src.ctypes.data, dst.ctypes.data, perm.ctypes.data, n, rb) == 0
+    assert np.array_equal(dst, src[perm])
+    bias = rng.normal(size=n).astype(np.float32)                                          # 1-D tensor: rows of 4 bytes
+    out = np.zeros_like(bias)
+    assert L.spif_reorder_rows(bias.ctypes.data, out.ctypes.data, perm.ctypes.data, n, 4) == 0
+    assert np.array_equal(out, bias[perm])
+    perm[3] = n                                                                            # out of range -> error, no write
+    assert L.spif_reorder_rows(src.ctypes.data, dst.ctypes.data, perm.ctypes.data, n, rb) != 0

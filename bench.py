@@ -65,8 +65,14 @@ def parse_args():
     ap.add_argument("--balance-swaps", type=int, default=64, help="max group swaps per layer per balancer round")
     ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
-    ap.add_argument("--schedule", default="two-streams", choices=["serial", "two-streams"],
-                    help="serial: the reference's node order on one stream; two-streams: predictor chain || FFN chain")
+    ap.add_argument("--schedule", default="fused", choices=["fused", "serial", "two-streams"],
+                    help="fused (default): ONE launch per layer, FFN(l) + look-ahead predictor(l+1) (spif_sparse_ffn_lookahead), "
+                         "true data edges of the reference graph; serial: the reference's node order, 4 launches per layer on one "
+                         "stream; two-streams: round-1 schedule, free-running predictor chain next to the FFN chain (looser than "
+                         "a real decode: kept for comparison only)")
+    ap.add_argument("--parity-layers", type=int, default=4, help="layers of the timed stack checked against the CPU oracle")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-scale-70b", action="store_true", help="N > 1: skip the relullama-70b scaling leg")
     ap.add_argument("--no-early-mask", action="store_true", help="do not use SPIF_FLAG_MASK_STABLE")
     return ap.parse_args()
 
@@ -227,11 +233,14 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    fused = a.schedule == "fused" and st.fused_supported()
+    schedule = a.schedule if (fused or a.schedule != "fused") else "two-streams"
+    step_stats = st.step_fused if fused else st.step_eager
     # eager warm-up (sets kernel attributes) + per-pool-entry activity statistics for the byte accounting
     A_pool, Z_pool = [], []
     for i in range(a.pool):
         st.x.copy_(x_pool[i])
-        st.step_eager(want_stats=True)
+        step_stats(want_stats=True)
         torch.cuda.synchronize()
         s = st.stats.cpu().numpy()[:, 0, :]
         A_pool.append(s[:, 0].astype(np.int64))
@@ -239,10 +248,12 @@ def run_ours(a):
     launches_per_step = st.launches_per_step
     log('eager warm-up done')
     st.early_mask = not a.no_early_mask
-    g_step = st.capture(st.step_two_streams if a.schedule == "two-streams" else st.step_eager)
+    step_fn = st.step_fused if fused else (st.step_two_streams if schedule == "two-streams" else st.step_eager)
+    g_step = st.capture(step_fn)
+    launches_per_step = st.launches_per_step
     log('step graph captured')
-    g_ffn = st.capture(st.ffn_only_eager)
-    g_pred = st.capture(st.predict_only_eager)
+    g_ffn = st.capture(st.ffn_only_fused if fused else st.ffn_only_eager)
+    g_pred = st.capture(st.predict_only_fused if fused else st.predict_only_eager)
 
     def timed(fn, steps, warmup):
         for i in range(warmup):
@@ -286,7 +297,7 @@ def run_ours(a):
         A_pool.clear(), Z_pool.clear()
         for i in range(a.pool):
             st.x.copy_(x_pool[i])
-            st.step_eager(want_stats=True)
+            step_stats(want_stats=True)
             torch.cuda.synchronize()
             s = st.stats.cpu().numpy()[:, 0, :]
             A_pool.append(s[:, 0].astype(np.int64))
@@ -339,16 +350,23 @@ def run_ours(a):
     ms_e2e = timed(step_e2e, a.steps, max(a.warmup, 3))
     log('e2e leg done')
 
-    # ---- roofline leg: the sparse FFNs alone (fused kernel + fixed-order partial reduction per layer), masks of pool[0]
+    # ---- parity leg: layers 0..k of the stack against the CPU oracle on the host (unsharded problem), every N
+    parity = None
+    if not a.no_parity and a.parity_layers > 0:
+        parity = parity_check(a, st, wl, x_pool[0], g_step, step_stats, rank, world, device)
+    log('parity leg done')
+
+    # ---- roofline legs: (i) the dominant kernel of the step, (ii) the sparse FFNs alone, (iii) the predictors alone
     st.x.copy_(x_pool[0])
     g_step.replay()
     torch.cuda.synchronize()
     reps = max(10, min(200, a.steps // 10))
     ms_ffn = timed(lambda i: g_ffn.replay(), reps, 3) / reps
     ms_pred = timed(lambda i: g_pred.replay(), reps, 3) / reps
+    ms_step0 = timed(lambda i: g_step.replay(), reps, 3) / reps      # the step on the masks of pool[0] (no x refresh)
     A0, Z0 = A_pool[0], Z_pool[0]
     ffn_bytes = float(((2 * A0 + Z0) * row_bytes).sum())          # this rank's shard, all layers of one step
-    pred_bytes = float(L * (E * R + R * st.m) * 2)
+    pred_bytes = float(L * (E * R // (world if fused else 1) + R * st.m) * 2)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -356,12 +374,14 @@ def run_ours(a):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6650"
-    achieved = ffn_bytes / (ms_ffn * 1e-3) / 1e9
     traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_top_kernel.json"))).get("dram_bytes_per_launch")
-    except Exception:
-        pass
+    if world == 1:  # the ncu capture is of the single-GPU launch; at N > 1 the per-launch bytes differ, so no constant is quoted
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_top_kernel.json")))
+            if (tj.get("kernel", "").startswith("spif_layer_kernel")) == fused:
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
 
     def leave():
         # NCCL communicators that were captured into CUDA graphs can hang in destroy_process_group / interpreter
@@ -373,12 +393,36 @@ def run_ours(a):
             sys.stderr.flush()
             os._exit(0)
 
-    if rank != 0:
+    scale_70b = None
+    if world > 1 and not a.no_scale_70b and a.workload == "prosparse-13b":
+        # the north-star's scaling target (BASELINE.json configs[4]): ReluLLaMA-70B neuron-sharded over the same ranks
+        g_step = g_ffn = g_pred = None   # the 13B graphs and weights make room for the 70B shard
+        st.layers = None
+        torch.cuda.empty_cache()
+        scale_70b = quick_leg(a, "relullama-70b", rank, world, device, barrier)
+        log('70b leg done')
+        if rank != 0:
+            barrier()
+            sys.stdout.flush()
+            os._exit(0)
+    elif rank != 0:
         leave()
         return
     ms_step = ms_value / a.steps
     A_mean = float(np.mean([x.mean() for x in A_pool]))
     Z_mean = float(np.mean([x.mean() for x in Z_pool]))
+    if fused:
+        # ONE launch per layer does FFN(l) + predictor(l+1): algorithmic bytes of a launch = (2A+Z)*row_bytes + the predictor's
+        # two matrices (this shard's part); duration = the captured step / launches (L + 1: the extra one is predictor(0))
+        n_launch = L + 1
+        bytes_launch = (ffn_bytes + pred_bytes) / n_launch
+        us_launch = ms_step0 * 1e3 / n_launch
+        kname = "spif_layer_kernel<f16> (sparse FFN of layer l + predictor of layer l+1 + list + sum over CTAs%s): one spif_sparse_ffn_lookahead call" % (
+            " + shard exchange" if world > 1 else "")
+    else:
+        bytes_launch, us_launch = ffn_bytes / L, ms_ffn * 1e3 / L
+        kname = "spif_ffn_direct_kernel<f16> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call"
+    achieved = bytes_launch / (us_launch * 1e-6) / 1e9
     out = {
         "metric": "decode tok/s ProSparse-13B bs1; sparse-FFN effective HBM GB/s vs B200 peak",
         "value": 1e3 / ms_step, "unit": "tok/s (sparse-FFN path of all layers: predictor + mask + gate/up + down)",
@@ -390,28 +434,163 @@ def run_ours(a):
                    "nonzero_hidden_per_layer": Z_mean * world if world > 1 else Z_mean,
                    "sharding": f"neuron groups of {GROUP} over {world} GPU(s), one sum of y over shards per layer ({st.exchange})"
                    if world > 1 else "all neurons resident on 1 GPU",
-                   "schedule": a.schedule, "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
+                   "schedule": schedule + (": one launch per layer, FFN(l) + predictor(l+1); predictor(l+1) reads x_l, launch l+1 "
+                                           "follows launch l on one stream (the reference graph's data edges)" if fused else ""),
+                   "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
                          ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool},
         "e2e": {"value": 1e3 / (ms_e2e / a.steps), "unit": "tok/s", "h2d_bytes_per_step": 4 * L * E,
                 "d2h_bytes_per_step": 4 * L * E},
         "gpu_launches": launches_per_step * a.steps,
         "clocks": clocks,
+        "parity": parity,
         "shard_balance": balance,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "spif_ffn_direct_kernel<f16> (+ spif_reduce_partials_kernel): one spif_sparse_ffn call",
-                     "bytes_per_launch": ffn_bytes / L, "us_per_launch": ms_ffn * 1e3 / L,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": kname,
+                     "bytes_per_launch": bytes_launch, "us_per_launch": us_launch,
+                     "ffn": {"achieved": ffn_bytes / (ms_ffn * 1e-3) / 1e9, "frac": ffn_bytes / (ms_ffn * 1e-3) / 1e9 / peak,
+                             "us_per_layer": ms_ffn * 1e3 / L, "bytes_per_layer": ffn_bytes / L,
+                             "what": ("the layer kernel with pred == NULL + spif_mask_to_list (2 launches)" if fused else
+                                      "spif_ffn_direct_kernel + spif_reduce_partials_kernel") +
+                                     (", shard exchange included" if (fused and world > 1) else
+                                      (", shard exchange NOT included" if world > 1 else ""))},
                      "predictor": {"achieved": pred_bytes / (ms_pred * 1e-3) / 1e9, "us_per_layer": ms_pred * 1e3 / L,
                                    "bytes_per_layer": pred_bytes / L},
                      "layer": {"achieved": (ffn_bytes + pred_bytes + 4 * L * (2 * E + st.m)) / (ms_step * 1e-3) / 1e9,
                                "us_per_layer": ms_step * 1e3 / L}},
     }
+    if scale_70b is not None:
+        out["scale_70b"] = scale_70b
     if world == 1 and not a.no_batched:
         out["batched"] = batched_legs(a, st, wl, device)
     if world == 1 and not a.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(a, wl, iters=8, warmup=2)
     print(json.dumps(out), flush=True)
     leave()
+
+
+def quick_leg(a, workload, rank, world, device, barrier):
+    """a second workload in the same process (N > 1: the 70B scaling leg): tok/s with x resident, same timing rules"""
+    import copy
+
+    import torch
+    import torch.distributed as dist
+    a2 = copy.copy(a)
+    a2.workload = workload
+    wl = WORKLOADS[workload]
+    E, L = wl["n_embd"], wl["n_layer"]
+    st, _ = build_stack(a2, wl, rank, world, device)
+    rng = np.random.default_rng(a.seed + 1)
+    pool = min(a.pool, 4)
+    x_pool = torch.from_numpy(rng.normal(0.0, 1.0, (pool, L, 1, E)).astype(np.float32)).to(device)
+    fused = a.schedule == "fused" and st.fused_supported()
+    step_stats = st.step_fused if fused else st.step_eager
+    A_all, Z_all = [], []
+    for i in range(pool):
+        st.x.copy_(x_pool[i])
+        step_stats(want_stats=True)
+        torch.cuda.synchronize()
+        sn = st.stats.cpu().numpy()[:, 0, :]
+        A_all.append(sn[:, 0].astype(np.int64)), Z_all.append(sn[:, 1].astype(np.int64))
+    g = st.capture(st.step_fused if fused else st.step_two_streams)
+    steps = max(20, min(a.steps, 200))
+
+    def run(i):
+        st.x.copy_(x_pool[i % pool])
+        g.replay()
+    for i in range(5):
+        run(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        run(i)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    parity = parity_check(a2, st, wl, x_pool[0], g, step_stats, rank, world, device, n_layers=2) if not a.no_parity else None
+    ffn_bytes = float(((2 * A_all[0] + Z_all[0]) * 2 * E).sum())
+    pred_bytes = float(L * (E * a.rank // (world if fused else 1) + a.rank * st.m) * 2)
+    res = {"workload": wl["label"], "n_gpus": world, "value": 1e3 / ms, "unit": "tok/s", "ms_per_step": ms, "steps": steps,
+           "us_per_layer": ms * 1e3 / L, "schedule": "fused" if fused else "two-streams", "exchange": st.exchange,
+           "active_rows_per_layer": float(np.mean([x.mean() for x in A_all])) * world,
+           "per_gpu_algorithmic_GBps": (ffn_bytes + pred_bytes) / (ms * 1e-3) / 1e9, "parity": parity}
+    del g
+    return res
+
+
+def parity_check(a, st, wl, x0, g_step, step_stats, rank, world, device, n_layers=None):
+    """Runs one step on x0 and checks layers 0..k-1 against the CPU oracle on the host, on the UNSHARDED problem (the rows
+    of all shards concatenated in rank order; a sum over neurons does not care about their order):
+      index_flips   predictor: neurons whose active / inactive decision differs from the oracle's, with the CPU-rounding flag
+                    (x and h1 rounded to F16 like the reference CPU backend); flips_outside_band counts those with
+                    |oracle logit| >= 1e-4 -- must be 0 (BASELINE.json north_star)
+      max_rel_err   sparse FFN: max |y - y_oracle| / max |y_oracle| over the checked layers, the oracle run on the GPU's own
+                    masks; the captured graph's default mode (F32 activations, tolerance 1e-3)
+      ranks_bit_identical   N > 1: y of every layer is bit-identical on all ranks"""
+    import oracle_lib  # test infrastructure: the checker, never the product path
+    import torch
+    import torch.distributed as dist
+    E, F, L, R = wl["n_embd"], wl["n_ff"], wl["n_layer"], a.rank
+    k = min(n_layers if n_layers is not None else a.parity_layers, L)
+    st.x.copy_(x0)
+    g_step.replay()
+    torch.cuda.synchronize()
+    y_gpu = st.y[:k, 0].clone()
+    p_gpu = st.p[:k, 0].clone()
+    # CPU-rounding pass (eager): predictor flips within the 1e-4 band
+    old_flags = st.flags
+    st.flags = old_flags | 1
+    step_stats(want_stats=False)
+    torch.cuda.synchronize()
+    p_cr = st.p[:k, 0].clone()
+    st.flags = old_flags
+    g_step.replay()          # leave the default-mode masks / lists in place
+    torch.cuda.synchronize()
+
+    def gather(t):
+        """concatenate a per-shard tensor over ranks (rank order) -> host numpy on rank 0"""
+        if world == 1:
+            return t.cpu().numpy()
+        parts = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(parts, t.contiguous())
+        return torch.cat(parts, dim=0).cpu().numpy() if rank == 0 else None
+
+    same = None
+    if world > 1:
+        ys = [torch.empty_like(st.y) for _ in range(world)]
+        dist.all_gather(ys, st.y)
+        same = all(torch.equal(ys[0], v) for v in ys[1:])
+    res = {"layers_checked": k, "max_rel_err": 0.0, "index_flips": 0, "flips_outside_band": 0, "tolerance": 1e-3,
+           "oracle": None, "ranks_bit_identical": same}
+    o = oracle_lib.Oracle() if rank == 0 else None
+    if rank == 0:
+        res["oracle"] = "oracle/libspif_oracle.so (C restatement pinned bit-exact to the reference CPU ops)"
+    for l in range(k):
+        w = st.layers[l]
+        rows = lambda t, n: gather(t.view(st.m, -1))
+        up, gate, down = rows(w.up, E), rows(w.gate, E), rows(w.down_t, E)
+        wpd, bpd = rows(w.pred_down, R), gather(w.pred_down_b)
+        pl, pcr = gather(p_gpu[l]), gather(p_cr[l])
+        if rank != 0:
+            continue
+        x_l = x0[l].cpu().numpy()
+        y_ref = o.sparse_ffn(wl["arch"], F16, up.reshape(-1), gate.reshape(-1), down.reshape(-1), x_l, pl[None], E, F)[0]
+        yg = y_gpu[l].cpu().numpy()
+        res["max_rel_err"] = max(res["max_rel_err"], float(np.abs(yg - y_ref[0]).max() / max(np.abs(y_ref).max(), 1e-30)))
+        if not wl.get("topk"):
+            x_p = x0[max(l - 1, 0)].cpu().numpy()   # look-ahead: the mask of layer l comes from x_{l-1} (layer 0: its own x)
+            p_ref, z_ref = o.predictor(F16, w.pred_up.cpu().numpy(), None, wpd.reshape(-1), bpd, x_p, E, R, F)
+            flips = (pcr < 0.5) != (p_ref[0] < 0.5)
+            res["index_flips"] += int(flips.sum())
+            res["flips_outside_band"] += int((np.abs(z_ref[0][flips]) >= 1e-4).sum())
+    if world > 1:
+        t = torch.tensor([res["max_rel_err"], res["index_flips"], res["flips_outside_band"]], dtype=torch.float64, device=device)
+        dist.broadcast(t, src=0)
+        res["max_rel_err"], res["index_flips"], res["flips_outside_band"] = float(t[0]), int(t[1]), int(t[2])
+    res["ok"] = bool(res["max_rel_err"] < 1e-3 and res["flips_outside_band"] == 0 and (same is None or same))
+    return res
 
 
 def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define SPIF_B200_ABI_VERSION 1
+#define SPIF_B200_ABI_VERSION 2
 
 typedef struct CUstream_st * spif_stream_t; /* == cudaStream_t */
 
@@ -55,9 +55,8 @@ enum spif_flags {
     SPIF_FLAG_CPU_ROUNDING = 1 << 0,
     /* sparse_idx is indexed by weight row (shard-local mask of length m) instead of by neuron id */
     SPIF_FLAG_MASK_BY_ROW  = 1 << 1,
-    /* accumulate the down projection with float atomics (fast, run-to-run unstable, like axpy-sparse.cu:84).
-     * Default is the deterministic two-level reduction. */
-    SPIF_FLAG_ATOMIC_DOWN  = 1 << 2,
+    /* (bit 2 is reserved: round 1 declared a float-atomics down projection here that no kernel implemented; every
+     * down projection is the deterministic fixed-order sum, unlike axpy-sparse.cu:84) */
     /* Caller's promise (spif_sparse_ffn only): sparse_idx was produced at least TWO kernel launches before this call on
      * `stream` (or is otherwise known to be complete), as in the reference's look-ahead order where the mask of layer l
      * is predicted one whole layer earlier (src/llama-graph.cpp:939-946).  The kernel then scans the mask and starts
@@ -100,8 +99,7 @@ int spif_mask_compact(const float * sparse_idx, const int32_t * neuron_idx, int 
 
 /* ---- top-k mask (Llama-3 / SiLU config; no reference code) ----------------------------------------
  * sparse_idx_out[t][i] = 1.0f for the k largest score[t][i] (ties -> lower index), else 0.0f.                    */
-int spif_topk_mask(const float * score, int n_ff, int n_tok, int k, float * sparse_idx_out, void * ws, size_t ws_bytes,
-                   spif_stream_t stream);
+int spif_topk_mask(const float * score, int n_ff, int n_tok, int k, float * sparse_idx_out, spif_stream_t stream);
 
 /* ---- GGML_OP_MUL_MAT_SPARSE (ggml.c:3310-3331; CUDA mm-sparse.cu:366-431, mmq-sparse.cu:293-394) ------------------
  * dst[t][neu] = dot(W[row], x[t]) for active rows, 0 elsewhere (dst {n_ff, n_tok} is zero-filled by the callee).
@@ -112,7 +110,7 @@ int spif_mul_mat_sparse(int type, const void * w, const float * x, const float *
 
 /* ---- GGML_OP_AXPY_SPARSE (ggml.c:3333-3356; CUDA axpy-sparse.cu:139-204, axpyq-sparse.cu:135-185) -----------------
  * dst[t][:] = sum over active rows with hid[t][neu] != 0 of hid[t][neu] * Wt[row][:]   (dst {n_embd, n_tok}).
- * Deterministic (fixed summation order) unless SPIF_FLAG_ATOMIC_DOWN.                                              */
+ * Deterministic (fixed summation order), unlike the reference's float atomics (axpy-sparse.cu:84).               */
 int spif_axpy_sparse(int type, const void * wt, const float * hid, const float * sparse_idx,
                      const int32_t * neuron_idx, float * dst, int n_embd, int n_ff, int m, int n_tok, float thr,
                      int flags, void * ws, size_t ws_bytes, spif_stream_t stream);
@@ -167,18 +165,23 @@ int spif_sparse_ffn(const spif_ffn_args * args, void * ws, size_t ws_bytes, spif
  * Each GPU holds the rows of a subset of neurons and produces a partial y; the sum over GPUs is a one-shot exchange over
  * NVLink peer memory: every rank stores its chunk, as 8-byte {value, sequence number} words, into its slot of every peer's
  * exchange buffer; the receiver polls the words themselves (no flag, no fence, one NVLink hop) and adds the slots in RANK
- * ORDER (bit-identical on all ranks, run-to-run stable).  In spif_sparse_ffn_sharded this is the epilogue of the kernel
- * that sums the per-CTA partials (one kernel does both); spif_shard_allreduce is the stand-alone form.  Buffers are owned by
- * the caller: data[r] is rank r's buffer as mapped into THIS process (CUDA IPC / VMM / torch symmetric memory),
- * zero-initialised before first use; seq is local.  Calls on the same buffers must be stream-ordered.                  */
+ * ORDER (bit-identical on all ranks, run-to-run stable).  In spif_sparse_ffn_sharded / spif_sparse_ffn_lookahead this is the
+ * epilogue of the kernel that sums the per-CTA partials (one kernel does both); spif_shard_allreduce is the stand-alone form.
+ * Buffers are owned by the caller: data[r] is rank r's buffer as mapped into THIS process (CUDA IPC / VMM / torch symmetric
+ * memory), zero-initialised before first use; seq is LOCAL device memory, zero-initialised before first use.
+ * The sequence number is one counter per comm object and per call (seq[0]), advanced by the last block of every call, so
+ * the stand-alone, the partial-sum-fused and the layer-fused forms can be mixed freely on one comm as long as every rank
+ * issues the same sequence of calls, stream-ordered.  A peer that does not answer within the spin bound (several seconds)
+ * makes the affected outputs NaN and sets a sticky error word that spif_shard_comm_status() returns: a wrong sum is never
+ * returned silently.  world == 1 is legal (no peers; the look-ahead layer kernel needs a comm for its own control words).   */
 #define SPIF_COMM_MAX_WORLD  8
-#define SPIF_COMM_MAX_BLOCKS 1024
+#define SPIF_COMM_SEQ_WORDS  1024
 typedef struct spif_shard_comm {
     int32_t rank, world;     /* world <= SPIF_COMM_MAX_WORLD */
-    int32_t cap_floats;      /* capacity of one slot in floats (>= n_tok * n_embd, multiple of 4) */
+    int32_t cap_floats;      /* capacity of one slot in floats: >= n_tok * n_embd (+ pred rank r for the look-ahead layer), multiple of 4 */
     int32_t reserved;
     void *  data[SPIF_COMM_MAX_WORLD];  /* 8-byte words [2][world][cap_floats]  (spif_shard_comm_data_bytes), 16-byte aligned */
-    void *  seq;                        /* local uint32_t [SPIF_COMM_MAX_BLOCKS], zero-initialised                            */
+    void *  seq;                        /* local uint32_t [SPIF_COMM_SEQ_WORDS], zero-initialised: [0] calls completed, [2] error */
 } spif_shard_comm;
 size_t spif_shard_comm_data_bytes(int world, int cap_floats);
 /* y[0..n) = sum over ranks of y, in place; n % 4 == 0, n <= cap_floats */
@@ -186,6 +189,44 @@ int spif_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, spi
 /* spif_sparse_ffn on this rank's rows + the exchange: args->y receives the FULL layer output on every rank */
 int spif_sparse_ffn_sharded(const spif_ffn_args * args, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
                             spif_stream_t stream);
+/* synchronises `stream`, then *error_out = the comm's sticky error word (0 = every exchange completed; 1 = a peer timed out) */
+int spif_shard_comm_status(const spif_shard_comm * comm, int * error_out, spif_stream_t stream);
+
+/* ---- look-ahead layer: sparse FFN of layer l + predictor of layer l+1 in ONE launch ------------------------------------
+ * The reference builds the predictor of layer l+1 from layer l's FFN input while layer l runs (src/llama-graph.cpp:932-946):
+ * both read the same x.  spif_sparse_ffn_lookahead runs, in one persistent kernel, build_sparse_ffn of layer l on the rows
+ * this device holds (`ffn`, n_tok == 1, F16/BF16) and build_predictor of layer l+1 (`pred`), and hands the next launch the
+ * ACTIVE-ROW LIST of layer l+1 (`list_out`, warp-ballot compaction per block of rows) so that no kernel ever scans the float
+ * mask again.  ffn == NULL: predictor only (layer 0's own mask).  pred == NULL: FFN only (last layer).
+ *   - `list_in` / `list_out`: opaque device buffers of spif_active_list_bytes(m) bytes, 16-byte aligned; produced by this
+ *     call, or from a float mask by spif_mask_to_list (mask indexed by ROW, like SPIF_FLAG_MASK_BY_ROW);
+ *   - ffn->sparse_idx is ignored (the list replaces it); ffn->flags: SPIF_FLAG_CPU_ROUNDING;
+ *   - pred->sparse_idx_out / logits_out (nullable) receive sigmoid / logit per Wpd row held here; list_out is nullable
+ *     (top-k configs build the mask from the logits with spif_topk_mask + spif_mask_to_list);
+ *   - `comm` is REQUIRED (world 1 on a single GPU): its buffers carry the predictor's hidden vector (every shard computes
+ *     r / world rows of it) and the sum of y over shards, its seq words the call counter; cap_floats >= n_embd + r;
+ *   - ws as for spif_sparse_ffn.  y is the full layer output on every rank (b_down added once per rank that passes it).
+ * Limits: n_embd <= 8192, r % 256 == 0, r <= n_embd, r % world == 0, pred->ptype == ffn->type; otherwise
+ * SPIF_E_UNSUPPORTED and the caller uses spif_predictor + spif_sparse_ffn.                                              */
+typedef struct spif_pred_args {
+    int32_t ptype;   /* SPIF_TYPE_F16 / SPIF_TYPE_BF16 */
+    int32_t n_embd;
+    int32_t r;       /* pred_lora */
+    int32_t m;       /* rows of Wpd held here == rows of the next layer's FFN matrices on this device */
+    int32_t flags;   /* SPIF_FLAG_CPU_ROUNDING */
+    float   thr;     /* threshold of the list: active <=> !(sigmoid < thr) */
+    const void *  wpu;  /* {n_embd, r}, replicated on every shard */
+    const float * bpu;  /* nullable {r} */
+    const void *  wpd;  /* {r, m} */
+    const float * bpd;  /* nullable {m} */
+    const float * x;    /* {n_embd}; must equal ffn->x when both are given */
+    float * sparse_idx_out; /* nullable {m} */
+    float * logits_out;     /* nullable {m} */
+} spif_pred_args;
+size_t spif_active_list_bytes(int m);
+int spif_mask_to_list(const float * sparse_idx, int m, float thr, void * list_out, spif_stream_t stream);
+int spif_sparse_ffn_lookahead(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+                              const spif_shard_comm * comm, void * ws, size_t ws_bytes, spif_stream_t stream);
 
 /* ---- balancer helpers (build_dfr, src/llama-graph.cpp:910-930; binbcast.cu:26-42; sumcols.cu; argsort.cu) ---------
  * One fused kernel: per group of `g` consecutive neurons, delta = #(active, token) pairs, then

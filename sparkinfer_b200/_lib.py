@@ -21,6 +21,15 @@ class FfnArgs(ctypes.Structure):
     ]
 
 
+class PredArgs(ctypes.Structure):
+    """struct spif_pred_args (include/spif_b200.h)"""
+    _fields_ = [
+        ("ptype", ctypes.c_int32), ("n_embd", ctypes.c_int32), ("r", ctypes.c_int32), ("m", ctypes.c_int32),
+        ("flags", ctypes.c_int32), ("thr", ctypes.c_float),
+        ("wpu", c_vp), ("bpu", c_vp), ("wpd", c_vp), ("bpd", c_vp), ("x", c_vp), ("sparse_idx_out", c_vp), ("logits_out", c_vp),
+    ]
+
+
 class ShardCommStruct(ctypes.Structure):
     """struct spif_shard_comm (include/spif_b200.h)"""
     _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("cap_floats", ctypes.c_int32),
@@ -35,7 +44,7 @@ SYMBOLS = {
     "spif_row_size": (c_sz, [c_i, c_i64]),
     "spif_workspace_size": (c_sz, [c_i, c_i, c_i]),
     "spif_mask_compact": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_i, c_vp, c_vp, c_vp, c_vp, c_vp]),
-    "spif_topk_mask": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_vp, c_sz, c_vp]),
+    "spif_topk_mask": (c_i, [c_vp, c_i, c_i, c_i, c_vp, c_vp]),
     "spif_mul_mat_sparse": (c_i, [c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_f, c_i, c_vp, c_sz, c_vp]),
     "spif_axpy_sparse": (c_i, [c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_f, c_i, c_vp, c_sz, c_vp]),
     "spif_fatrelu": (c_i, [c_vp, c_vp, c_i64, c_f, c_vp]),
@@ -46,6 +55,11 @@ SYMBOLS = {
     "spif_shard_comm_data_bytes": (c_sz, [c_i, c_i]),
     "spif_shard_allreduce": (c_i, [c_vp, c_i64, ctypes.POINTER(ShardCommStruct), c_vp]),
     "spif_sparse_ffn_sharded": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
+    "spif_shard_comm_status": (c_i, [ctypes.POINTER(ShardCommStruct), ctypes.POINTER(c_i), c_vp]),
+    "spif_active_list_bytes": (c_sz, [c_i]),
+    "spif_mask_to_list": (c_i, [c_vp, c_i, c_f, c_vp, c_vp]),
+    "spif_sparse_ffn_lookahead": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(PredArgs), c_vp, c_vp,
+                                        ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
     "spif_initial_placement": (c_i, [c_vp, c_i, c_i, c_vp]),
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
     "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),

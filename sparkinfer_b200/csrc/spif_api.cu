@@ -10,6 +10,10 @@ int spif_launch_ffn_q(const spif_ffn_args & a, int mode, const float * hid_in, f
 int    spif_launch_ffn_batch(const spif_ffn_args & a, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx);
 size_t spif_batch_workspace_bytes(int n_embd, int n_ff, int n_tok);
 int    spif_launch_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, cudaStream_t stream);
+size_t spif_active_list_bytes_impl(int m);
+int    spif_launch_mask_to_list(const float * mask, int m, float thr, void * list, const spif_launch_ctx & ctx);
+int    spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+                         const spif_shard_comm * comm, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx);
 
 static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
     int dev = 0;
@@ -130,10 +134,7 @@ int spif_mask_compact(const float * sparse_idx, const int32_t * neuron_idx, int 
                                     union_count, ctx.stream);
 }
 
-int spif_topk_mask(const float * score, int n_ff, int n_tok, int k, float * sparse_idx_out, void * ws, size_t ws_bytes,
-                   spif_stream_t stream) {
-    (void) ws;
-    (void) ws_bytes;
+int spif_topk_mask(const float * score, int n_ff, int n_tok, int k, float * sparse_idx_out, spif_stream_t stream) {
     SPIF_REQUIRE(score && sparse_idx_out, SPIF_E_NULL);
     SPIF_REQUIRE(n_ff > 0 && n_tok > 0, SPIF_E_SHAPE);
     spif_launch_ctx ctx;
@@ -209,7 +210,7 @@ int spif_axpy_sparse(int type, const void * wt, const float * hid, const float *
     a.n_ff          = n_ff;
     a.m             = m;
     a.n_tok         = n_tok;
-    a.flags         = flags & (SPIF_FLAG_CPU_ROUNDING | SPIF_FLAG_MASK_BY_ROW | SPIF_FLAG_ATOMIC_DOWN);
+    a.flags         = flags & (SPIF_FLAG_CPU_ROUNDING | SPIF_FLAG_MASK_BY_ROW);
     a.thr           = thr;
     a.w_down_t      = wt;
     a.sparse_idx    = sparse_idx;
@@ -307,6 +308,38 @@ int spif_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, spi
         return rc;
     }
     return spif_launch_shard_allreduce(y, n, comm, ctx.stream);
+}
+
+int spif_shard_comm_status(const spif_shard_comm * comm, int * error_out, spif_stream_t stream) {
+    SPIF_REQUIRE(comm != nullptr && comm->seq != nullptr && error_out != nullptr, SPIF_E_NULL);
+    SPIF_CUDA_TRY(cudaStreamSynchronize((cudaStream_t) stream));
+    uint32_t w = 0;
+    SPIF_CUDA_TRY(cudaMemcpy(&w, (const uint32_t *) comm->seq + 2, sizeof(w), cudaMemcpyDeviceToHost));
+    *error_out = (int) w;
+    return 0;
+}
+
+size_t spif_active_list_bytes(int m) {
+    return spif_active_list_bytes_impl(m);
+}
+
+int spif_mask_to_list(const float * sparse_idx, int m, float thr, void * list_out, spif_stream_t stream) {
+    spif_launch_ctx ctx;
+    int             rc = make_ctx(ctx, stream);
+    if (rc) {
+        return rc;
+    }
+    return spif_launch_mask_to_list(sparse_idx, m, thr, list_out, ctx);
+}
+
+int spif_sparse_ffn_lookahead(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+                              const spif_shard_comm * comm, void * ws, size_t ws_bytes, spif_stream_t stream) {
+    spif_launch_ctx ctx;
+    int             rc = make_ctx(ctx, stream);
+    if (rc) {
+        return rc;
+    }
+    return spif_launch_layer(ffn, pred, list_in, list_out, comm, ws, ws_bytes, ctx);
 }
 
 int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,

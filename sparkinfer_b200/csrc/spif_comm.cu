@@ -5,12 +5,17 @@
 __global__ void __launch_bounds__(256) spif_shard_allreduce_kernel(float * __restrict__ y, int n4, const spif_comm_dev comm) {
     pdl_wait_prior_grid();
     pdl_launch_dependents();
-    const int  i   = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool own = i < n4;
-    float4     v   = own ? reinterpret_cast<const float4 *>(y)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-    v              = spif_peer_allreduce_f4(comm, v, i, own, blockIdx.x);
+    const uint32_t seq = spif_comm_call_seq(comm);
+    const int      i   = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool     own = i < n4;
+    float4         v   = own ? reinterpret_cast<const float4 *>(y)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    v                  = spif_peer_allreduce_f4(comm, seq, v, i, own);
     if (own) {
         reinterpret_cast<float4 *>(y)[i] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        spif_comm_block_done(comm, seq, gridDim.x);
     }
 }
 
@@ -25,7 +30,6 @@ int spif_launch_shard_allreduce(float * y, int64_t n, const spif_shard_comm * co
     const int n4     = (int) (n / 4);
     // few, fat blocks keep the flag traffic low; at least 64 threads per block so that a block's stores fill NVLink packets
     int       blocks = (n4 + 255) / 256;
-    SPIF_REQUIRE(blocks <= SPIF_COMM_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = dim3(blocks);
     cfg.blockDim           = dim3(256);

@@ -2,19 +2,31 @@
 //
 // Low-latency protocol (the idea of NCCL's LL): every 4-byte value travels in an 8-byte word {value, sequence number} written
 // with ONE naturally aligned 8-byte store, which is single-copy atomic -- the receiver polls the word itself, so there is no
-// separate flag, no fence and no extra NVLink round trip.  Per block and call:
-//   seq = local counter + 1 (never 0, the buffers start zeroed), parity = seq & 1
-//   1. a thread holding a float4 stores 4 words into slot [parity][my rank] of every PEER's buffer (NVLink peer stores)
-//   2. it polls the 4 words of every peer's slot in its OWN buffer until they carry seq (bounded spin), and adds the values
-//      in rank order, its own contribution at its rank's position -> bit-identical on all ranks
-// Slot reuse is safe with two parities: a rank can only be two calls ahead of a peer after that peer has sent the words of the
-// call in between, which it does after it finished reading the older slot (calls are stream-ordered on every rank).
+// separate flag, no fence and no extra NVLink round trip.
+//
+// Sequence numbers are PER COMM OBJECT AND PER CALL, never per block: comm.seq[0] holds the number of calls completed on this
+// rank ("epoch"); every kernel that uses the buffers reads it after its programmatic-dependent-launch wait (the previous call
+// on the stream has completed then), uses seq = epoch + 1 for every word of the call, and its last block to finish stores
+// seq back.  All ranks issue the same sequence of calls on a comm, so they agree on seq whatever the launch shapes of the
+// individual calls are (fused layer kernel, partial-sum kernel, stand-alone allreduce can be mixed freely on one comm).
+// A stale word can never be mistaken for a fresh one: it carries an older seq.  parity = seq & 1 selects one of two slot
+// sets: a rank can only be two calls ahead of a peer after that peer has sent the words of the call in between, which it
+// does after it finished reading the older slot set (calls are stream-ordered on every rank).
+//
+// Local control words (comm.seq, uint32, zero-initialised by the caller):
+//   [0] epoch   [1] blocks that have finished the current call   [2] sticky error (SPIF_COMM_ERR_*)   [3] layer kernel:
+//   CTAs whose partial y is written   [4..7] reserved
+// A peer that does not answer within the spin bound sets the error word, and the affected outputs are NaN: a wrong sum is
+// never returned silently.  spif_shard_comm_status() reads the error word.
 #pragma once
 #include "spif_common.cuh"
 
+#define SPIF_COMM_ERR_TIMEOUT 1u
+#define SPIF_COMM_SPIN_LIMIT  (1u << 24) /* polls of local memory: several seconds */
+
 struct spif_comm_dev {
     uint2 *    data[SPIF_COMM_MAX_WORLD];  // [2][world][cap] words {float bits, seq}
-    uint32_t * seq;
+    uint32_t * seq;                        // local control words, see above
     int        rank, world, cap;
 };
 
@@ -26,52 +38,105 @@ __device__ __forceinline__ uint2 ld_word_sys(const uint2 * p) {
     asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
     return v;
 }
+// two adjacent words with one 16-byte load whose ELEMENTS are the 8-byte words (each element is single-copy atomic)
+__device__ __forceinline__ void ld_word2_sys(const uint2 * p, uint2 & a, uint2 & b) {
+    unsigned long long x, y;
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(p) : "memory");
+    a = make_uint2((uint32_t) x, (uint32_t) (x >> 32));
+    b = make_uint2((uint32_t) y, (uint32_t) (y >> 32));
+}
+__device__ __forceinline__ uint32_t ld_u32_relaxed_gpu(const uint32_t * p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_u32_acquire_gpu(const uint32_t * p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
-// idx4: float4 index of this thread's value inside y (only read when has_value); block: counter index, unique per block.
-// Must be called by all threads of the block.  Returns the sum over ranks for threads with has_value.
-__device__ __forceinline__ float4 spif_peer_allreduce_f4(const spif_comm_dev & c, float4 v, int idx4, bool has_value, int block) {
-    const int      tid = threadIdx.x + threadIdx.y * blockDim.x;
-    const uint32_t seq = c.seq[block] + 1u;
-    const uint32_t par = seq & 1u;
-    __syncthreads();  // everybody has read the counter before thread 0 advances it
-    float4 s = v;
-    if (has_value) {
-        const float  mine[4] = { v.x, v.y, v.z, v.w };
-        const size_t out_off = ((size_t) par * c.world + c.rank) * c.cap + (size_t) idx4 * 4;
-        for (int r = 0; r < c.world; ++r) {
-            if (r != c.rank) {
+// seq of the call this kernel belongs to.  Must be read after griddepcontrol.wait (or in a normally ordered launch).
+__device__ __forceinline__ uint32_t spif_comm_call_seq(const spif_comm_dev & c) {
+    return ld_u32_relaxed_gpu(c.seq + 0) + 1u;
+}
+
+// Called by ONE thread per block after all threads of the block are done with the comm (i.e. after a __syncthreads()).
+// The last block of the call publishes the new epoch and clears the per-call counters.
+__device__ __forceinline__ void spif_comm_block_done(const spif_comm_dev & c, uint32_t seq, unsigned n_blocks) {
+    __threadfence();
+    const unsigned old = atomicAdd(c.seq + 1, 1u);
+    if (old == n_blocks - 1u) {
+        c.seq[1] = 0u;
+        c.seq[3] = 0u;
+        __threadfence();
+        c.seq[0] = seq;
+    }
+}
+
+// idx4: float4 index of this thread's value inside the slot (only read when has_value).  Returns the sum over ranks, added
+// in RANK ORDER (bit-identical on all ranks) for threads with has_value.  All peer words are requested at once and only the
+// missing ones are polled again (the first version polled 4 x (world-1) words one after the other: 12 us at 8 GPUs).
+__device__ __forceinline__ float4 spif_peer_allreduce_f4(const spif_comm_dev & c, uint32_t seq, float4 v, int idx4,
+                                                         bool has_value) {
+    if (!has_value || c.world == 1) {
+        return v;
+    }
+    const uint32_t par     = seq & 1u;
+    const size_t   out_off = ((size_t) par * c.world + c.rank) * c.cap + (size_t) idx4 * 4;
+    const uint32_t mine[4] = { __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w) };
+#pragma unroll 1
+    for (int r = 1; r < c.world; ++r) {  // start with the next rank: spreads the stores over the links
+        const int dst = (c.rank + r) % c.world;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    st_word_sys(c.data[r] + out_off + e, __float_as_uint(mine[e]), seq);
+        for (int e = 0; e < 4; ++e) {
+            st_word_sys(c.data[dst] + out_off + e, mine[e], seq);
+        }
+    }
+    uint2 w[SPIF_COMM_MAX_WORLD][4];
+    const uint2 * in0 = c.data[c.rank] + (size_t) par * c.world * c.cap + (size_t) idx4 * 4;
+    unsigned      pending = 0;
+#pragma unroll
+    for (int r = 0; r < SPIF_COMM_MAX_WORLD; ++r) {
+        if (r < c.world && r != c.rank) {
+            ld_word2_sys(in0 + (size_t) r * c.cap, w[r][0], w[r][1]);
+            ld_word2_sys(in0 + (size_t) r * c.cap + 2, w[r][2], w[r][3]);
+            pending |= 1u << r;
+        }
+    }
+    unsigned spins = 0;
+    while (pending) {
+#pragma unroll
+        for (int r = 0; r < SPIF_COMM_MAX_WORLD; ++r) {
+            if (pending & (1u << r)) {
+                if (w[r][0].y == seq && w[r][1].y == seq && w[r][2].y == seq && w[r][3].y == seq) {
+                    pending &= ~(1u << r);
+                } else {
+                    ld_word2_sys(in0 + (size_t) r * c.cap, w[r][0], w[r][1]);
+                    ld_word2_sys(in0 + (size_t) r * c.cap + 2, w[r][2], w[r][3]);
                 }
             }
         }
-        float acc[4] = { 0.f, 0.f, 0.f, 0.f };
-        for (int r = 0; r < c.world; ++r) {
-            if (r == c.rank) {
+        if (++spins > SPIF_COMM_SPIN_LIMIT) {
+            break;
+        }
+    }
+    if (pending) {  // a peer never answered: poison the result and raise the sticky error word
+        atomicOr(c.seq + 2, SPIF_COMM_ERR_TIMEOUT);
+        const float qnan = __uint_as_float(0x7fc00000u);
+        return make_float4(qnan, qnan, qnan, qnan);
+    }
+    float acc[4] = { 0.f, 0.f, 0.f, 0.f };
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    acc[e] += mine[e];
-                }
-                continue;
-            }
-            const uint2 * in = c.data[c.rank] + ((size_t) par * c.world + r) * c.cap + (size_t) idx4 * 4;
+    for (int r = 0; r < SPIF_COMM_MAX_WORLD; ++r) {
+        if (r < c.world) {
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                uint2 w = ld_word_sys(in + e);
-                // bounded: a peer that died must not hang this GPU forever (the sum is then wrong, which the tests catch)
-                for (int spin = 0; w.y != seq && spin < (1 << 22); ++spin) {
-                    w = ld_word_sys(in + e);
-                }
-                acc[e] += __uint_as_float(w.x);
+                acc[e] += (r == c.rank) ? __uint_as_float(mine[e]) : __uint_as_float(w[r][e].x);
             }
         }
-        s = make_float4(acc[0], acc[1], acc[2], acc[3]);
     }
-    if (tid == 0) {
-        c.seq[block] = seq;
-    }
-    return s;
+    return make_float4(acc[0], acc[1], acc[2], acc[3]);
 }
 
 static inline int spif_comm_to_dev(const spif_shard_comm * h, spif_comm_dev & d) {

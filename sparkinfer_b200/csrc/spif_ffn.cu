@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
     if (!launch_first) {
         pdl_launch_dependents();
     }
+    const uint32_t seq = COMM ? spif_comm_call_seq(comm) : 0u;  // after the wait: the previous call on this comm is complete
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (col4 < n4) {
         const float4 * base = reinterpret_cast<const float4 *>(partials + (size_t) tok * P * n_embd) + col4;
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
         }
     }
     if (COMM) {
-        t = spif_peer_allreduce_f4(comm, t, tok * n4 + col4, own, blockIdx.x + gridDim.x * blockIdx.y);
+        t = spif_peer_allreduce_f4(comm, seq, t, tok * n4 + col4, own);
     }
     if (own) {
         reinterpret_cast<float4 *>(y + (size_t) tok * n_embd)[col4] = t;
@@ -118,6 +119,12 @@ __global__ void __launch_bounds__(SPIF_RED_COLS * SPIF_RED_LANES) spif_reduce_pa
             stats_out[tok * 4 + 1] = nz;
             stats_out[tok * 4 + 2] = 0;
             stats_out[tok * 4 + 3] = 0;
+        }
+    }
+    if (COMM) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            spif_comm_block_done(comm, seq, gridDim.x * gridDim.y);
         }
     }
 }
@@ -179,7 +186,6 @@ static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y,
             return rc;
         }
         SPIF_REQUIRE((int64_t) n_embd * n_tok <= comm->cap_floats, SPIF_E_WORKSPACE);
-        SPIF_REQUIRE(cfg.gridDim.x * cfg.gridDim.y <= SPIF_COMM_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
         SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, spif_reduce_partials_kernel<true>, (const float *) kp.partials, b_down, y,
                                          (const int32_t *) kp.cta_stats, stats_out, n_embd, P, cd, k_red_first));
         return 0;

@@ -1,0 +1,979 @@
+// spif_layer.cu -- ONE persistent kernel per decode layer: the sparse FFN of layer l and the look-ahead predictor of layer l+1.
+//
+// Reference graph order (src/llama-graph.cpp:932-946, 896-1142): while layer l runs, the mask of layer l+1 is predicted from
+// layer l's FFN input x_l.  The reference issues 6 predictor nodes + 2 MUL_MAT_SPARSE + activation + AXPY_SPARSE (+ memsets)
+// per layer; round 1 of this repo used 4 launches on two streams (predictor up, predictor down, fused FFN, partial sum).
+// Here everything that shares x_l is one launch, and every grid-wide dependency is hidden behind other streaming work:
+//
+//   per CTA (one per SM, all co-resident), in queue order:
+//     A  its share of the predictor up-projection rows  Wpu[r][n_embd]      -> h1 rows, published as {value, seq} words
+//     B  its share of layer l's ACTIVE neurons: gate/up rows -> hidden value -> W_down^T row (only if hidden != 0)
+//        -> partial y in registers -> written once, counted
+//     C  its contiguous block of predictor down-projection rows Wpd[m][r]   (needs all of h1: long complete by now)
+//        -> sigmoid -> sparse_idx of layer l+1, and the block's ACTIVE-ROW LIST for the next launch (warp ballot + popc)
+//     D  column-sliced fixed-order sum of the partial y of all CTAs (long complete by now) [+ the shard exchange]
+//
+//   * The mask is never scanned again: launch l+1 reads 148 block counts + its own ~9 list entries instead of 55 KB of floats
+//     per CTA (round 1: 2.5 us on every layer's critical path, 148 times the same scan).
+//   * No second kernel for the partial sum (round 1: 3-4 us per layer, 10.7 % of the launch list).
+//   * One register budget: round 1's FFN and predictor grids fought for the SMs and overlapped by 2.7 us of 25.
+//
+// Data movement: ONE elected thread streams everything with 1-D TMA bulk copies (cp.async.bulk -> UBLKCP) into a ring of
+// slots of two rows each (13B: 10 x 20 KB = 200 KB in flight per SM, Little's law needs ~64 KB); completion by mbarrier
+// complete_tx.  Consumer warps own fixed 16-byte column slices of a row (x in registers), multiply whatever item arrives
+// (two rows -> two partial dots, reduced with ONE packed shuffle tree), publish per-warp partials in shared memory and
+// arrive on the slot's `done` barrier; they never wait for each other.  The producer warp doubles as the epilogue: it
+// retires items in order (cross-warp sum in a fixed order, bias, activation, sigmoid, list compaction), pushes the
+// W_down^T rows of neurons whose hidden value is non-zero into the queue, and refills the freed slot.
+//
+// Determinism: every sum has a fixed shape (packed shuffle tree per warp, fixed warp order, W_down^T rows in ascending
+// neuron order per CTA, partials in CTA order) -> run-to-run bit-stable, unlike axpy-sparse.cu:84 (float atomics).
+#include "spif_comm.cuh"
+
+#define SPIF_LIST_MAX_BLOCKS 1024
+#define SPIF_LIST_HDR        4 /* int32: {nblk, m, 0, 0} */
+
+enum { IT_WPU2 = 0, IT_GU = 1, IT_DN2 = 2, IT_WPD2 = 3, IT_FLUSH = 4, IT_END = 5 };
+
+struct LayerParams {
+    // ---- sparse FFN of this layer (has_ffn)
+    const unsigned char * w_up;
+    const unsigned char * w_gate;
+    const unsigned char * w_down;
+    const float *         b_up;
+    const float *         b_gate;
+    const float *         b_down;
+    const float *         x;           // [n_embd] (also the predictor's input: look-ahead)
+    float *               y;           // [n_embd]
+    const int32_t *       neuron_idx;  // nullable [m]
+    float *               hidden_out;  // nullable dense [n_ff]
+    int32_t *             stats_out;   // nullable [4]
+    const int32_t *       lin_cnt;     // active-row list of this layer: counts per block
+    const int32_t *       lin_rows;    //   rows, block b at offset floor(b * m / nblk)
+    float *               partials;    // [P][n_embd]
+    int32_t *             cta_stats;   // [P][2]
+    // ---- predictor of the next layer (has_pred)
+    const unsigned char * wpu;         // [r][n_embd]
+    const unsigned char * wpd;         // [pm][r]
+    const float *         bpu;
+    const float *         bpd;
+    float *               p_out;       // nullable [pm]
+    float *               logits_out;  // nullable [pm]
+    int32_t *             lout_cnt;    // nullable: active-row list of the next layer
+    int32_t *             lout_rows;
+    int32_t *             lout_hdr;
+    int                   has_ffn, has_pred;
+    int                   n_embd, V, row_bytes;
+    int                   m, n_ff, lin_nblk;
+    int                   r, pm, Vr, RP, WR;  // Vr = r/8 vectors per Wpd row, RP = Wpd rows per half slot, WR = warps per Wpd row
+    int                   nw;                 // consumer warps
+    int                   nslots;
+    int                   cap_ffn, cap_pd, cap_pu;
+    float                 thr_next;           // threshold for the list of the next layer
+    int                   arch, flags, pflags;
+    spif_comm_dev         comm;
+    unsigned long long *  trace;
+};
+
+struct LayerSmem {
+    uint32_t ring, full, done, desc, dalpha, part, list_row, list_neu, list_bu, list_bg, pend_row, pend_alpha, bpu_s, bpd_s,
+        lout_s, total;
+};
+
+__host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int slot_bytes, int cap_ffn, int cap_pd, int cap_pu) {
+    LayerSmem L;
+    uint32_t  o = 0;
+    auto      take = [&](uint32_t bytes, uint32_t align) {
+        o               = (o + align - 1) / align * align;
+        const uint32_t r = o;
+        o += bytes;
+        return r;
+    };
+    L.ring       = take((uint32_t) nslots * slot_bytes, 128);
+    L.full       = take(8u * nslots, 8);
+    L.done       = take(8u * nslots, 8);
+    L.desc       = take(16u * nslots, 16);
+    L.dalpha     = take(8u * nslots, 8);
+    L.part       = take(4u * 64 * nslots, 16);
+    L.list_row   = take(4u * cap_ffn, 4);
+    L.list_neu   = take(4u * cap_ffn, 4);
+    L.list_bu    = take(4u * cap_ffn, 4);
+    L.list_bg    = take(4u * cap_ffn, 4);
+    L.pend_row   = take(4u * cap_ffn, 4);
+    L.pend_alpha = take(4u * cap_ffn, 4);
+    L.bpu_s      = take(4u * cap_pu, 4);
+    L.bpd_s      = take(4u * cap_pd, 4);
+    L.lout_s     = take(4u * cap_pd, 4);
+    L.total      = (o + 127) / 128 * 128;
+    return L;
+}
+
+#define LAYER_STAMP(k)                                                   \
+    do {                                                                 \
+        if (p.trace && lane == 0) {                                      \
+            unsigned long long _t;                                       \
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(_t));        \
+            p.trace[(size_t) blockIdx.x * 16 + (k)] = _t;                \
+        }                                                                \
+    } while (0)
+
+// lanes 0..15 return the warp sum of a, lanes 16..31 the warp sum of b: two reductions for the price of one tree
+__device__ __forceinline__ float reduce2(float a, float b, int lane) {
+    const bool hi   = (lane & 16) != 0;
+    float      keep = hi ? b : a;
+    float      send = hi ? a : b;
+    keep += __shfl_xor_sync(0xffffffffu, send, 16);
+    keep += __shfl_xor_sync(0xffffffffu, keep, 8);
+    keep += __shfl_xor_sync(0xffffffffu, keep, 4);
+    keep += __shfl_xor_sync(0xffffffffu, keep, 2);
+    keep += __shfl_xor_sync(0xffffffffu, keep, 1);
+    return keep;
+}
+
+template <typename WT, int VPT, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int NW = p.nw, NC = NW * 32;
+    const int P = gridDim.x, c = blockIdx.x;
+    const int N = p.nslots;
+    const int slot_bytes = 2 * p.row_bytes;
+
+    const LayerSmem L = layer_smem_layout(N, slot_bytes, p.cap_ffn, p.cap_pd, p.cap_pu);
+    unsigned char * ring       = smem + L.ring;
+    uint64_t *      full       = reinterpret_cast<uint64_t *>(smem + L.full);
+    uint64_t *      done       = reinterpret_cast<uint64_t *>(smem + L.done);
+    int4 *          desc       = reinterpret_cast<int4 *>(smem + L.desc);
+    float *         dalpha     = reinterpret_cast<float *>(smem + L.dalpha);  // [N][2]
+    float *         part       = reinterpret_cast<float *>(smem + L.part);    // [N][2][32]
+    int *           list_row   = reinterpret_cast<int *>(smem + L.list_row);
+    int *           list_neu   = reinterpret_cast<int *>(smem + L.list_neu);
+    float *         list_bu    = reinterpret_cast<float *>(smem + L.list_bu);
+    float *         list_bg    = reinterpret_cast<float *>(smem + L.list_bg);
+    int *           pend_row   = reinterpret_cast<int *>(smem + L.pend_row);
+    float *         pend_alpha = reinterpret_cast<float *>(smem + L.pend_alpha);
+    float *         bpu_s      = reinterpret_cast<float *>(smem + L.bpu_s);
+    float *         bpd_s      = reinterpret_cast<float *>(smem + L.bpd_s);
+    int *           lout_s     = reinterpret_cast<int *>(smem + L.lout_s);
+
+    if (tid == 0) {
+        for (int s = 0; s < N; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&done[s], NW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    const bool     gated    = (p.arch != SPIF_ARCH_RELU_UP);
+    const bool     rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
+    const int      world    = p.comm.world;
+    const int      h1_off   = p.n_embd;  // h1 words live behind the y words of a slot
+    uint32_t       seq      = 0;
+
+    // my shares of the dense predictor matrices (weights: independent of the previous kernel)
+    int ra = 0, rb = 0, pa = 0, pb = 0;
+    if (p.has_pred) {
+        const int R0 = (int) ((long long) p.comm.rank * p.r / world), R1 = (int) ((long long) (p.comm.rank + 1) * p.r / world);
+        ra = R0 + (int) ((long long) c * (R1 - R0) / P);
+        rb = R0 + (int) ((long long) (c + 1) * (R1 - R0) / P);
+        pa = (int) ((long long) c * p.pm / P);
+        pb = (int) ((long long) (c + 1) * p.pm / P);
+    }
+
+    if (warp == NW) {
+        // =========================================== producer + epilogue warp ===========================================
+        const uint64_t pol = l2_policy_evict_first();
+        for (int i = lane; i < rb - ra; i += 32) {
+            bpu_s[i] = p.bpu ? __ldg(p.bpu + ra + i) : 0.f;
+        }
+        for (int i = lane; i < pb - pa; i += 32) {
+            bpd_s[i] = p.bpd ? __ldg(p.bpd + pa + i) : 0.f;
+        }
+        __syncwarp();
+
+        int  q_issue = 0, q_done = 0;
+        int  a_next = ra, b_next = 0, b_end = 0, c_next = pa;
+        int  pend_head = 0, pend_tail = 0, gu_inflight = 0;
+        int  n_nonzero = 0, cnt_out = 0, total_active = 0;
+        bool flushed = false, ended = false, list_ready = !p.has_ffn;
+        const int rows_per_wpd = 2 * p.RP;
+
+        // issue one item into slot q % N; returns false if nothing can be issued right now
+        auto issue_next = [&]() -> bool {
+            const int s  = q_issue % N;
+            const int np = pend_tail - pend_head;
+            int       type = -1;
+            if (np >= 2) {
+                type = IT_DN2;
+            } else if (a_next < rb) {
+                type = IT_WPU2;
+            } else if (!list_ready) {
+                return false;
+            } else if (b_next < b_end) {
+                type = IT_GU;
+            } else if (np == 1 && gu_inflight == 0) {
+                type = IT_DN2;
+            } else if (p.has_ffn && !flushed && gu_inflight == 0 && np == 0) {
+                type = IT_FLUSH;
+            } else if (c_next < pb) {
+                type = IT_WPD2;
+            } else if (q_done == q_issue && np == 0 && gu_inflight == 0 && (flushed || !p.has_ffn)) {
+                type = IT_END;
+            } else {
+                return false;
+            }
+            unsigned char * dst = ring + (size_t) s * slot_bytes;
+            switch (type) {
+                case IT_WPU2: {
+                    const int n = min(2, rb - a_next);
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_WPU2, a_next, n, 0);
+                        mbar_arrive_expect_tx(&full[s], (uint32_t) n * p.row_bytes);
+                        for (int j = 0; j < n; ++j) {
+                            tma_load_1d(dst + (size_t) j * p.row_bytes, p.wpu + (size_t) (a_next + j) * p.row_bytes, p.row_bytes,
+                                        &full[s], pol);
+                        }
+                    }
+                    a_next += n;
+                } break;
+                case IT_GU: {
+                    const int n = gated ? 1 : min(2, b_end - b_next);
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_GU, b_next, n, 0);
+                        mbar_arrive_expect_tx(&full[s], (uint32_t) (gated ? 2 : n) * p.row_bytes);
+                        if (gated) {
+                            const size_t off = (size_t) list_row[b_next] * p.row_bytes;
+                            tma_load_1d(dst, p.w_up + off, p.row_bytes, &full[s], pol);
+                            tma_load_1d(dst + p.row_bytes, p.w_gate + off, p.row_bytes, &full[s], pol);
+                        } else {
+                            for (int j = 0; j < n; ++j) {
+                                tma_load_1d(dst + (size_t) j * p.row_bytes, p.w_up + (size_t) list_row[b_next + j] * p.row_bytes,
+                                            p.row_bytes, &full[s], pol);
+                            }
+                        }
+                    }
+                    b_next += n;
+                    ++gu_inflight;
+                } break;
+                case IT_DN2: {
+                    const int n = min(2, np);
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_DN2, n, 0, 0);
+                        mbar_arrive_expect_tx(&full[s], (uint32_t) n * p.row_bytes);
+                        for (int j = 0; j < n; ++j) {
+                            dalpha[s * 2 + j] = pend_alpha[pend_head + j];
+                            tma_load_1d(dst + (size_t) j * p.row_bytes, p.w_down + (size_t) pend_row[pend_head + j] * p.row_bytes,
+                                        p.row_bytes, &full[s], pol);
+                        }
+                    }
+                    pend_head += n;
+                } break;
+                case IT_WPD2: {
+                    const int n  = min(rows_per_wpd, pb - c_next);
+                    const int n0 = min(p.RP, n), n1 = n - n0;
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_WPD2, c_next, n0, n1);
+                        const uint32_t wrow = (uint32_t) p.r * 2;
+                        mbar_arrive_expect_tx(&full[s], (uint32_t) n * wrow);
+                        tma_load_1d(dst, p.wpd + (size_t) c_next * wrow, (uint32_t) n0 * wrow, &full[s], pol);
+                        if (n1 > 0) {
+                            tma_load_1d(dst + p.row_bytes, p.wpd + (size_t) (c_next + n0) * wrow, (uint32_t) n1 * wrow, &full[s], pol);
+                        }
+                    }
+                    c_next += n;
+                } break;
+                case IT_FLUSH:
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_FLUSH, 0, 0, 0);
+                        mbar_arrive(&full[s]);
+                    }
+                    flushed = true;
+                    break;
+                default: /* IT_END */
+                    if (lane == 0) {
+                        desc[s] = make_int4(IT_END, 0, 0, 0);
+                        mbar_arrive(&full[s]);
+                    }
+                    ended = true;
+                    break;
+            }
+            ++q_issue;
+            __syncwarp();  // desc / dalpha written by lane 0 are read by every lane at retire time
+            return true;
+        };
+
+        // ---- before the programmatic-dependent-launch wait: the predictor up-projection rows are already on their way
+        while (q_issue < N && a_next < rb) {
+            issue_next();
+        }
+        LAYER_STAMP(0);
+        pdl_wait_prior_grid();
+        pdl_launch_dependents();
+        LAYER_STAMP(1);
+        seq = spif_comm_call_seq(p.comm);
+        const uint32_t par = seq & 1u;
+
+        // ---- my share of this layer's active rows: ranks [c*A/P, (c+1)*A/P) of the concatenated block lists
+        if (p.has_ffn) {
+            const int nb = p.lin_nblk, kb = (nb + 31) / 32;
+            const int b0 = min(lane * kb, nb), b1 = min(b0 + kb, nb);
+            int       local = 0;
+            for (int b = b0; b < b1; ++b) {
+                local += __ldcg(p.lin_cnt + b);
+            }
+            int incl = local;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                incl += (lane >= o) ? t : 0;
+            }
+            total_active = __shfl_sync(0xffffffffu, incl, 31);
+            const int lo = (int) ((long long) c * total_active / P), hi = (int) ((long long) (c + 1) * total_active / P);
+            b_end        = hi - lo;
+            int pbk      = incl - local;
+            for (int b = b0; b < b1; ++b) {
+                const int cb = __ldcg(p.lin_cnt + b);
+                const int s0 = max(pbk, lo), s1 = min(pbk + cb, hi);
+                if (s0 < s1) {
+                    const int start_b = (int) ((long long) b * p.m / nb);
+                    for (int i = s0; i < s1; ++i) {
+                        list_row[i - lo] = __ldcg(p.lin_rows + start_b + (i - pbk));
+                    }
+                }
+                pbk += cb;
+            }
+            __syncwarp();
+            for (int j = lane; j < b_end; j += 32) {
+                const int row = list_row[j];
+                const int neu = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
+                list_neu[j]   = neu;
+                list_bu[j]    = p.b_up ? __ldg(p.b_up + neu) : 0.f;
+                list_bg[j]    = p.b_gate ? __ldg(p.b_gate + neu) : 0.f;
+            }
+            __syncwarp();
+            list_ready = true;
+        }
+        LAYER_STAMP(2);
+
+        // ---- retire item q (in order): cross-warp sums in a fixed order + the epilogue of its kind
+        auto retire = [&](int q) {
+            const int      s   = q % N;
+            const unsigned ph  = (unsigned) (q / N) & 1u;
+            mbar_wait(&done[s], ph);
+            const int4    d  = desc[s];
+            const float * ps = part + s * 64;
+            if (d.x == IT_WPU2 || d.x == IT_GU) {
+                const float a0 = (lane < NW) ? ps[lane] : 0.f;
+                const float a1 = (lane < NW) ? ps[32 + lane] : 0.f;
+                const float k  = reduce2(a0, a1, lane);
+                const float s0 = __shfl_sync(0xffffffffu, k, 0), s1 = __shfl_sync(0xffffffffu, k, 16);
+                if (d.x == IT_WPU2) {
+                    // h1[row] = relu(Wpu[row] . x + bpu[row])  (llama-graph.cpp:871-880), published to every shard
+                    if (lane < d.z) {
+                        const int   row = d.y + lane;
+                        float       z   = (lane == 0 ? s0 : s1) + bpu_s[row - ra];
+                        z               = (z > 0.f) ? z : 0.f;
+                        const size_t off = ((size_t) par * world + p.comm.rank) * p.comm.cap + h1_off + row;
+                        for (int r = 0; r < world; ++r) {
+                            st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
+                        }
+                    }
+                } else {
+                    --gu_inflight;
+                    const int nn = d.z;
+                    for (int j = 0; j < nn; ++j) {  // gated: one neuron (u, g); ungated: up to two neurons (u0, u1)
+                        const int i   = d.y + j;
+                        float     u   = (gated || j == 0) ? s0 : s1;
+                        float     g   = gated ? s1 : 0.f;
+                        u += list_bu[i];
+                        g += list_bg[i];
+                        float h = spif_activation(p.arch, g, u);
+                        if (lane == 0 && p.hidden_out) {
+                            p.hidden_out[list_neu[i]] = h;
+                        }
+                        if (rounding) {
+                            h = round_through<WT>(h);
+                        }
+                        if (!(h == 0.0f)) {  // axpy-sparse.cu:53: rows with hid == 0 are never read
+                            if (lane == 0) {
+                                pend_row[pend_tail]   = list_row[i];
+                                pend_alpha[pend_tail] = h;
+                            }
+                            ++pend_tail;
+                            ++n_nonzero;
+                        }
+                    }
+                    __syncwarp();
+                }
+            } else if (d.x == IT_WPD2) {
+                const int row0 = d.y, n0 = d.z, n = d.z + d.w;
+                for (int base = 0; base < n; base += 32) {
+                    const int  idx   = base + lane;
+                    const bool valid = idx < n;
+                    float      z     = 0.f;
+                    if (valid) {
+                        const int     half = idx >= n0 ? 1 : 0;
+                        const int     rho  = idx - half * n0;
+                        const float * pp   = ps + half * 32 + rho * p.WR;
+                        for (int j = 0; j < p.WR; ++j) {  // fixed order
+                            z += pp[j];
+                        }
+                        z += bpd_s[row0 - pa + idx];
+                    }
+                    const float pr = 1.f / (1.f + expf(-z));  // unary-ops.cpp:31-33 / unary.cu:48-50
+                    if (valid) {
+                        if (p.p_out) {
+                            p.p_out[row0 + idx] = pr;
+                        }
+                        if (p.logits_out) {
+                            p.logits_out[row0 + idx] = z;
+                        }
+                    }
+                    const bool     act  = valid && spif_is_active(pr, p.thr_next);
+                    const unsigned ball = __ballot_sync(0xffffffffu, act);
+                    if (act) {
+                        lout_s[cnt_out + __popc(ball & ((1u << lane) - 1u))] = row0 + idx;
+                    }
+                    cnt_out += __popc(ball);
+                }
+            } else if (d.x == IT_FLUSH) {
+                // every consumer thread has stored its slice of the partial y and fenced; publish the count
+                if (lane == 0) {
+                    p.cta_stats[c * 2 + 0] = total_active;
+                    p.cta_stats[c * 2 + 1] = n_nonzero;
+                    __threadfence();
+                    atomicAdd(p.comm.seq + 3, 1u);
+                }
+                LAYER_STAMP(4);
+            }
+        };
+
+        bool first_gu = true;
+        while (!ended) {
+            while (q_issue - q_done < N && !ended) {
+                if (!issue_next()) {
+                    break;
+                }
+                if (first_gu && gu_inflight > 0) {
+                    first_gu = false;
+                    LAYER_STAMP(3);
+                }
+            }
+            if (ended) {
+                break;
+            }
+            if (q_done < q_issue) {
+                retire(q_done);
+                ++q_done;
+            }
+        }
+        LAYER_STAMP(5);
+        // ---- the next layer's active-row list: this block's rows in ascending order + its count
+        if (p.has_pred && p.lout_cnt) {
+            __syncwarp();
+            for (int i = lane; i < cnt_out; i += 32) {
+                p.lout_rows[pa + i] = lout_s[i];
+            }
+            if (lane == 0) {
+                p.lout_cnt[c] = cnt_out;
+                if (c == 0) {
+                    p.lout_hdr[0] = P;
+                    p.lout_hdr[1] = p.pm;
+                }
+            }
+        }
+        LAYER_STAMP(6);
+    } else {
+        // ================================================ consumer warps ================================================
+        float xr[VPT * 8], acc[VPT * 8], hr[VPT * 8];
+#pragma unroll
+        for (int e = 0; e < VPT * 8; ++e) {
+            xr[e] = 0.f, acc[e] = 0.f, hr[e] = 0.f;
+        }
+        pdl_wait_prior_grid();
+        pdl_launch_dependents();
+        seq = spif_comm_call_seq(p.comm);
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+            const int v = tid + k * NC;
+            if (v < p.V) {
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v);
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v + 1);
+                xr[k * 8 + 0] = a.x, xr[k * 8 + 1] = a.y, xr[k * 8 + 2] = a.z, xr[k * 8 + 3] = a.w;
+                xr[k * 8 + 4] = b.x, xr[k * 8 + 5] = b.y, xr[k * 8 + 6] = b.z, xr[k * 8 + 7] = b.w;
+                if (rounding) {  // ggml-cpu.c:1832-1856: x is converted to the weight type
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        xr[k * 8 + e] = round_through<WT>(xr[k * 8 + e]);
+                    }
+                }
+            }
+        }
+        bool h1_loaded = false;
+        int  s = 0;
+        unsigned ph = 0;
+        bool first = true;
+        for (;;) {
+            mbar_wait(&full[s], ph);
+            if (first) {
+                first = false;
+                if (warp == 0) {
+                    LAYER_STAMP(8);
+                }
+            }
+            const int4            d    = desc[s];
+            const unsigned char * slot = ring + (size_t) s * slot_bytes;
+            if (d.x == IT_END) {
+                break;
+            }
+            if (d.x == IT_WPU2 || d.x == IT_GU) {
+                float a = 0.f, b = 0.f;
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * NC;
+                    if (v < p.V) {
+                        float w[8];
+                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            a = fmaf(w[e], xr[k * 8 + e], a);
+                        }
+                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            b = fmaf(w[e], xr[k * 8 + e], b);
+                        }
+                    }
+                }
+                const bool two = (d.x == IT_GU) ? (gated || d.z == 2) : (d.z == 2);
+                b              = two ? b : 0.f;  // the second half of the slot was not loaded
+                const float k2 = reduce2(a, b, lane);
+                if ((lane & 15) == 0) {
+                    part[s * 64 + (lane >> 4) * 32 + warp] = k2;
+                }
+            } else if (d.x == IT_DN2) {
+                const float al0 = dalpha[s * 2], al1 = (d.y == 2) ? dalpha[s * 2 + 1] : 0.f;
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * NC;
+                    if (v < p.V) {
+                        float w[8];
+                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            acc[k * 8 + e] = fmaf(w[e], al0, acc[k * 8 + e]);
+                        }
+                        if (d.y == 2) {
+                            unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                acc[k * 8 + e] = fmaf(w[e], al1, acc[k * 8 + e]);
+                            }
+                        }
+                    }
+                }
+            } else if (d.x == IT_WPD2) {
+                if (!h1_loaded) {
+                    // the hidden vector of the predictor: {value, seq} words, complete once every CTA (of every shard) has
+                    // retired its Wpu rows -- they were first in everybody's queue
+                    h1_loaded          = true;
+                    const uint32_t par = seq & 1u;
+#pragma unroll
+                    for (int k = 0; k < VPT; ++k) {
+                        const int v = tid + k * NC;
+                        if (v < p.V) {
+                            const int     col   = v % p.Vr;
+                            const int     owner = (col * 8) / (p.r / world);
+                            const uint2 * src   = p.comm.data[p.comm.rank] + ((size_t) par * world + owner) * p.comm.cap + h1_off + col * 8;
+                            uint2         w8[8];
+                            bool          ok    = false;
+                            unsigned      spins = 0;
+                            while (!ok) {
+#pragma unroll
+                                for (int e = 0; e < 8; e += 2) {
+                                    ld_word2_sys(src + e, w8[e], w8[e + 1]);
+                                }
+                                ok = true;
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    ok = ok && (w8[e].y == seq);
+                                }
+                                if (++spins > SPIF_COMM_SPIN_LIMIT) {
+                                    break;
+                                }
+                            }
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                float hv = ok ? __uint_as_float(w8[e].x) : __uint_as_float(0x7fc00000u);
+                                if (p.pflags & SPIF_FLAG_CPU_ROUNDING) {
+                                    hv = round_through<WT>(hv);
+                                }
+                                hr[k * 8 + e] = hv;
+                            }
+                            if (!ok) {
+                                atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
+                            }
+                        }
+                    }
+                    if (warp == 0) {
+                        LAYER_STAMP(9);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * NC;
+                    float     a = 0.f, b = 0.f;
+                    if (v < p.V) {
+                        float w[8];
+                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            a = fmaf(w[e], hr[k * 8 + e], a);
+                        }
+                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            b = fmaf(w[e], hr[k * 8 + e], b);
+                        }
+                    }
+                    b              = (d.w > 0) ? b : 0.f;
+                    const float k2 = reduce2(a, b, lane);
+                    const int   g  = warp + k * NW;  // 32-vector group of the slot half
+                    if ((lane & 15) == 0 && g < 32) {
+                        part[s * 64 + (lane >> 4) * 32 + g] = k2;
+                    }
+                }
+            } else { /* IT_FLUSH: this CTA's partial y */
+                float * prt = p.partials + (size_t) c * p.n_embd;
+#pragma unroll
+                for (int k = 0; k < VPT; ++k) {
+                    const int v = tid + k * NC;
+                    if (v < p.V) {
+                        float4 * o = reinterpret_cast<float4 *>(prt) + 2 * v;
+                        __stcg(o, make_float4(acc[k * 8 + 0], acc[k * 8 + 1], acc[k * 8 + 2], acc[k * 8 + 3]));
+                        __stcg(o + 1, make_float4(acc[k * 8 + 4], acc[k * 8 + 5], acc[k * 8 + 6], acc[k * 8 + 7]));
+                    }
+                }
+                __threadfence();
+            }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&done[s]);
+            }
+            if (++s == N) {
+                s = 0;
+                ph ^= 1u;
+            }
+        }
+        if (warp == 0) {
+            LAYER_STAMP(10);
+        }
+
+        // ---- D: y[cols of this CTA] = sum over CTAs of their partial y, fixed order (+ b_down) [+ sum over shards]
+        if (p.has_ffn) {
+            named_bar_sync(1, NC);  // every consumer is done with the ring: reuse it as scratch
+            if (tid == 0) {
+                unsigned spins = 0;
+                while (ld_u32_acquire_gpu(p.comm.seq + 3) < (unsigned) P) {
+                    if (++spins > SPIF_COMM_SPIN_LIMIT) {
+                        atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
+                        break;
+                    }
+                }
+            }
+            named_bar_sync(1, NC);
+            if (warp == 0) {
+                LAYER_STAMP(11);
+            }
+            const int n4 = p.n_embd >> 2;
+            const int c0 = (int) ((long long) c * n4 / P), c1 = (int) ((long long) (c + 1) * n4 / P);
+            const int ncol = c1 - c0;  // <= 16 (checked by the launcher)
+            const int G = NC >> 4, col = tid & 15, pg = tid >> 4;
+            float4 *  red  = reinterpret_cast<float4 *>(ring);            // [G][16]
+            float4 *  red2 = red + (size_t) G * 16;                       // [4][16]
+            float4    sacc = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (col < ncol) {
+                const float4 * base = reinterpret_cast<const float4 *>(p.partials) + c0 + col;
+                float4         v[6];
+#pragma unroll
+                for (int q = 0; q < 6; ++q) {
+                    const int pp = pg + q * G;
+                    v[q]         = (pp < P) ? __ldcg(base + (size_t) pp * n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int q = 0; q < 6; ++q) {
+                    sacc.x += v[q].x, sacc.y += v[q].y, sacc.z += v[q].z, sacc.w += v[q].w;
+                }
+                for (int pp = pg + 6 * G; pp < P; pp += G) {
+                    const float4 t = __ldcg(base + (size_t) pp * n4);
+                    sacc.x += t.x, sacc.y += t.y, sacc.z += t.z, sacc.w += t.w;
+                }
+            }
+            red[pg * 16 + col] = sacc;
+            named_bar_sync(1, NC);
+            if (tid < 64) {
+                const int j = tid >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
+                float4    t = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int g2 = lo; g2 < hi; ++g2) {
+                    const float4 v = red[g2 * 16 + col];
+                    t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
+                }
+                red2[j * 16 + col] = t;
+            }
+            named_bar_sync(1, NC);
+            if (tid < 16) {
+                const bool own = col < ncol;
+                float4     t   = red2[col];
+#pragma unroll
+                for (int j = 1; j < 4; ++j) {
+                    const float4 v = red2[j * 16 + col];
+                    t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
+                }
+                if (own && p.b_down) {
+                    const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0 + col);
+                    t.x += bb.x, t.y += bb.y, t.z += bb.z, t.w += bb.w;
+                }
+                t = spif_peer_allreduce_f4(p.comm, seq, t, c0 + col, own);
+                if (own) {
+                    reinterpret_cast<float4 *>(p.y)[c0 + col] = t;
+                }
+            }
+            if (c == 0 && warp == 1 % NW && p.stats_out) {
+                int nz = 0;
+                for (int q = lane; q < P; q += 32) {
+                    nz += __ldcg(p.cta_stats + q * 2 + 1);
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    nz += __shfl_xor_sync(0xffffffffu, nz, o);
+                }
+                if (lane == 0) {
+                    p.stats_out[0] = __ldcg(p.cta_stats + 0);
+                    p.stats_out[1] = nz;
+                    p.stats_out[2] = 0;
+                    p.stats_out[3] = 0;
+                }
+            }
+            if (warp == 0) {
+                LAYER_STAMP(12);
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        spif_comm_block_done(p.comm, seq, (unsigned) P);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// float mask -> block lists (the form the layer kernel consumes).  One warp per block of rows, ballot + popc, ascending.
+__global__ void __launch_bounds__(32) spif_mask_to_list_kernel(const float * __restrict__ mask, int m, float thr, int nblk,
+                                                               int32_t * __restrict__ hdr, int32_t * __restrict__ cnt,
+                                                               int32_t * __restrict__ rows) {
+    const int b = blockIdx.x, lane = threadIdx.x;
+    const int r0 = (int) ((long long) b * m / nblk), r1 = (int) ((long long) (b + 1) * m / nblk);
+    int       n = 0;
+    for (int base = r0; base < r1; base += 32) {
+        const int      row  = base + lane;
+        const bool     a    = (row < r1) && spif_is_active(__ldg(mask + row), thr);
+        const unsigned ball = __ballot_sync(0xffffffffu, a);
+        if (a) {
+            rows[r0 + n + __popc(ball & ((1u << lane) - 1u))] = row;
+        }
+        n += __popc(ball);
+    }
+    if (lane == 0) {
+        cnt[b] = n;
+        if (b == 0) {
+            hdr[0] = nblk;
+            hdr[1] = m;
+        }
+    }
+}
+
+size_t spif_active_list_bytes_impl(int m) {
+    return sizeof(int32_t) * ((size_t) SPIF_LIST_HDR + SPIF_LIST_MAX_BLOCKS + (size_t) (m > 0 ? m : 0));
+}
+
+int spif_launch_mask_to_list(const float * mask, int m, float thr, void * list, const spif_launch_ctx & ctx) {
+    SPIF_REQUIRE(mask && list, SPIF_E_NULL);
+    SPIF_REQUIRE(m > 0 && ((uintptr_t) list & 15) == 0, SPIF_E_SHAPE);
+    const int nblk = ctx.sm_count;
+    SPIF_REQUIRE(nblk <= SPIF_LIST_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
+    int32_t * hdr = (int32_t *) list;
+    spif_mask_to_list_kernel<<<nblk, 32, 0, ctx.stream>>>(mask, m, thr, nblk, hdr, hdr + SPIF_LIST_HDR,
+                                                          hdr + SPIF_LIST_HDR + SPIF_LIST_MAX_BLOCKS);
+    SPIF_CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+extern unsigned long long * g_spif_trace;
+
+template <typename WT, int VPT, int MAXT>
+static int launch_layer_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
+    auto kern = spif_layer_kernel<WT, VPT, MAXT>;
+    static unsigned long long done = 0;  // per instantiation: bit per device
+    const unsigned long long  bit  = 1ull << (device & 63);
+    if (!(done & bit)) {
+        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        done |= bit;
+    }
+    // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
+    int per_sm = 0;
+    SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+    SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(P);
+    cfg.blockDim           = dim3(threads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
+    return 0;
+}
+
+int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+                      const spif_shard_comm * comm, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
+    SPIF_REQUIRE(ffn != nullptr || pred != nullptr, SPIF_E_NULL);
+    SPIF_REQUIRE(comm != nullptr, SPIF_E_NULL);
+    LayerParams kp = {};
+    int         rc = spif_comm_to_dev(comm, kp.comm);
+    if (rc) {
+        return rc;
+    }
+    const int P = ctx.sm_count;
+    SPIF_REQUIRE(P >= 1 && P <= SPIF_LIST_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
+    int type = 0, n_embd = 0;
+    const float * x = nullptr;
+    if (ffn) {
+        SPIF_REQUIRE(ffn->n_tok == 1, SPIF_E_UNSUPPORTED);
+        SPIF_REQUIRE(ffn->type == SPIF_TYPE_F16 || ffn->type == SPIF_TYPE_BF16, SPIF_E_TYPE);
+        SPIF_REQUIRE(ffn->w_up && ffn->w_down_t && ffn->x && ffn->y && list_in, SPIF_E_NULL);
+        SPIF_REQUIRE(ffn->arch == SPIF_ARCH_RELU_UP || ffn->w_gate, SPIF_E_NULL);
+        SPIF_REQUIRE(ffn->arch >= SPIF_ARCH_PROSPARSE && ffn->arch <= SPIF_ARCH_SILU_GATED, SPIF_E_UNSUPPORTED);
+        SPIF_REQUIRE(ffn->m > 0 && ffn->n_ff >= ffn->m && (ffn->neuron_idx || ffn->m == ffn->n_ff), SPIF_E_SHAPE);
+        SPIF_REQUIRE((((uintptr_t) ffn->w_up | (uintptr_t) ffn->w_gate | (uintptr_t) ffn->w_down_t | (uintptr_t) ffn->x |
+                       (uintptr_t) ffn->y | (uintptr_t) ffn->b_down | (uintptr_t) list_in) & 15) == 0, SPIF_E_SHAPE);
+        type   = ffn->type;
+        n_embd = ffn->n_embd;
+        x      = ffn->x;
+    }
+    const spif_pred_args * pv = pred;
+    if (pv) {
+        SPIF_REQUIRE(pv->ptype == SPIF_TYPE_F16 || pv->ptype == SPIF_TYPE_BF16, SPIF_E_TYPE);
+        SPIF_REQUIRE(!ffn || pv->ptype == type, SPIF_E_UNSUPPORTED);  // one float codec per launch
+        SPIF_REQUIRE(pv->wpu && pv->wpd && pv->x, SPIF_E_NULL);
+        SPIF_REQUIRE(!ffn || pv->x == ffn->x, SPIF_E_UNSUPPORTED);    // look-ahead: the predictor reads the FFN's own input
+        SPIF_REQUIRE(!ffn || pv->n_embd == n_embd, SPIF_E_SHAPE);
+        SPIF_REQUIRE(pv->r > 0 && pv->r % 256 == 0 && pv->r <= pv->n_embd && pv->r % kp.comm.world == 0 && pv->m > 0, SPIF_E_SHAPE);
+        SPIF_REQUIRE((((uintptr_t) pv->wpu | (uintptr_t) pv->wpd | (uintptr_t) pv->x | (uintptr_t) list_out) & 15) == 0, SPIF_E_SHAPE);
+        type   = pv->ptype;
+        n_embd = pv->n_embd;
+        x      = pv->x;
+    }
+    SPIF_REQUIRE(n_embd > 0 && n_embd % 8 == 0, SPIF_E_SHAPE);
+    const int V = n_embd / 8;
+    SPIF_REQUIRE(V <= 1024, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE((n_embd / 4 + P - 1) / P <= 16, SPIF_E_UNSUPPORTED);  // column slice of the final sum
+    SPIF_REQUIRE(kp.comm.cap >= n_embd + (pv ? pv->r : 0), SPIF_E_WORKSPACE);
+
+    const int vpt = (V <= 992) ? 1 : 2;
+    kp.nw         = (V + 32 * vpt - 1) / (32 * vpt);
+    SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);  // n_embd >= 512: the final column-sliced sum uses 64 threads
+    const int threads = (kp.nw + 1) * 32;
+    kp.n_embd     = n_embd;
+    kp.V          = V;
+    kp.row_bytes  = n_embd * 2;
+    kp.x          = x;
+    kp.trace      = g_spif_trace;
+    if (ffn) {
+        kp.has_ffn    = 1;
+        kp.w_up       = (const unsigned char *) ffn->w_up;
+        kp.w_gate     = (const unsigned char *) ffn->w_gate;
+        kp.w_down     = (const unsigned char *) ffn->w_down_t;
+        kp.b_up       = ffn->b_up;
+        kp.b_gate     = ffn->b_gate;
+        kp.b_down     = ffn->b_down;
+        kp.y          = ffn->y;
+        kp.neuron_idx = ffn->neuron_idx;
+        kp.hidden_out = ffn->hidden_out;
+        kp.stats_out  = ffn->stats_out;
+        kp.m          = ffn->m;
+        kp.n_ff       = ffn->n_ff;
+        kp.arch       = ffn->arch;
+        kp.flags      = ffn->flags;
+        const int32_t * lh = (const int32_t *) list_in;
+        kp.lin_nblk   = P;  // lists on a device are always built with one block per SM
+        kp.lin_cnt    = lh + SPIF_LIST_HDR;
+        kp.lin_rows   = lh + SPIF_LIST_HDR + SPIF_LIST_MAX_BLOCKS;
+        const size_t part_bytes = sizeof(float) * (size_t) P * n_embd;
+        const size_t stat_bytes = sizeof(int32_t) * (size_t) P * 2;
+        SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= part_bytes + stat_bytes, SPIF_E_WORKSPACE);
+        kp.partials  = (float *) ws;
+        kp.cta_stats = (int32_t *) ((char *) ws + part_bytes);
+        kp.cap_ffn   = (ffn->m + P - 1) / P + 2;
+    } else {
+        kp.cap_ffn = 1;
+    }
+    if (pv) {
+        kp.has_pred   = 1;
+        kp.wpu        = (const unsigned char *) pv->wpu;
+        kp.wpd        = (const unsigned char *) pv->wpd;
+        kp.bpu        = pv->bpu;
+        kp.bpd        = pv->bpd;
+        kp.p_out      = pv->sparse_idx_out;
+        kp.logits_out = pv->logits_out;
+        kp.r          = pv->r;
+        kp.pm         = pv->m;
+        kp.Vr         = pv->r / 8;
+        kp.RP         = V / kp.Vr;
+        kp.WR         = kp.Vr / 32;
+        kp.thr_next   = pv->thr;
+        kp.pflags     = pv->flags;
+        if (!ffn) {
+            kp.flags = pv->flags & SPIF_FLAG_CPU_ROUNDING;  // x rounding of a predictor-only launch
+        }
+        if (list_out) {
+            int32_t * lh = (int32_t *) list_out;
+            kp.lout_hdr  = lh;
+            kp.lout_cnt  = lh + SPIF_LIST_HDR;
+            kp.lout_rows = lh + SPIF_LIST_HDR + SPIF_LIST_MAX_BLOCKS;
+        }
+        kp.cap_pd = (pv->m + P - 1) / P + 2;
+        kp.cap_pu = (pv->r + P - 1) / P + 2;
+    } else {
+        kp.cap_pd = 1, kp.cap_pu = 1;
+        kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
+    }
+    const int slot_bytes = 2 * kp.row_bytes;
+    int       nslots     = 12;
+    LayerSmem L          = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu);
+    while (nslots > 3 && L.total > (uint32_t) ctx.max_smem_optin) {
+        --nslots;
+        L = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu);
+    }
+    SPIF_REQUIRE(L.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
+    // the final column-sliced sum reuses the ring as scratch: [(G + 4) x 16] float4
+    SPIF_REQUIRE((size_t) nslots * slot_bytes >= (size_t) (kp.nw * 2 + 4) * 16 * 16, SPIF_E_SHAPE);
+    kp.nslots = nslots;
+    if (ffn && ffn->hidden_out) {
+        SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
+    }
+    const bool f16 = type == SPIF_TYPE_F16;
+    if (vpt == 1 && threads <= 704) {
+        return f16 ? launch_layer_t<spif_f16, 1, 704>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 1, 704>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    }
+    if (vpt == 1) {
+        return f16 ? launch_layer_t<spif_f16, 1, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 1, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    }
+    return f16 ? launch_layer_t<spif_f16, 2, 544>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                 launch_layer_t<spif_bf16, 2, 544>(kp, P, threads, L.total, ctx.device, ctx.stream);
+}

@@ -18,11 +18,11 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import FfnArgs, ShardCommStruct, check
+from ._lib import FfnArgs, PredArgs, ShardCommStruct, check
 
 GGML_TYPE_F32, GGML_TYPE_F16, GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_BF16 = 0, 1, 2, 8, 30
 ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
-FLAG_CPU_ROUNDING, FLAG_MASK_BY_ROW, FLAG_ATOMIC_DOWN, FLAG_MASK_STABLE, FLAG_PER_TOKEN = 1, 2, 4, 8, 16
+FLAG_CPU_ROUNDING, FLAG_MASK_BY_ROW, FLAG_MASK_STABLE, FLAG_PER_TOKEN = 1, 2, 8, 16
 SPARSE_THRESHOLD = 0.5  # SPIF_SPARSE_THRESHOLD, mm-sparse.cu:5-7
 
 
@@ -57,7 +57,7 @@ class ShardComm:
     the CUDA VMM / IPC handle exchange; the exchange itself is done by our kernels over NVLink peer stores).  world == 1
     works without torch.distributed (self-exchange; used by the single-GPU tests)."""
 
-    MAX_BLOCKS = 1024
+    SEQ_WORDS = 1024  # SPIF_COMM_SEQ_WORDS
 
     def __init__(self, cap_floats, group=None, device="cuda"):
         L = _lib.load()
@@ -77,7 +77,7 @@ class ShardComm:
             ptrs = [int(p) for p in self.handle.buffer_ptrs]
             torch.cuda.synchronize()
             torch.distributed.barrier(group)  # everybody's buffers are zero before anyone stores into them
-        self.seq = torch.zeros(self.MAX_BLOCKS, dtype=torch.int32, device=device)
+        self.seq = torch.zeros(self.SEQ_WORDS, dtype=torch.int32, device=device)
         c = ShardCommStruct()
         c.rank, c.world, c.cap_floats, c.reserved = rank, world, cap, 0
         for r in range(world):
@@ -85,6 +85,15 @@ class ShardComm:
         c.seq = self.seq.data_ptr()
         self.c = c
         self.rank, self.world, self.cap = rank, world, cap
+
+    def status(self):
+        """synchronises the current stream; 0 = every exchange completed, 1 = a peer timed out (outputs were NaN)"""
+        err = ctypes.c_int(0)
+        check(_lib.load().spif_shard_comm_status(ctypes.byref(self.c), ctypes.byref(err), _stream()), "spif_shard_comm_status")
+        return err.value
+
+    def epoch(self):
+        return int(self.seq[0].item())
 
 
 def shard_allreduce(y, comm):
@@ -117,7 +126,7 @@ def topk_mask(score, k, out=None):
     L = _lib.load()
     n_tok, n_ff = score.shape
     out = out if out is not None else torch.empty_like(score)
-    check(L.spif_topk_mask(_p(score), n_ff, n_tok, k, _p(out), None, 0, _stream()), "spif_topk_mask")
+    check(L.spif_topk_mask(_p(score), n_ff, n_tok, k, _p(out), _stream()), "spif_topk_mask")
     return out
 
 
@@ -204,6 +213,67 @@ def sparse_ffn(arch, w_type, up, gate, down_t, cur, sparse_idx, n_ff, neuron_idx
     if want_stats:
         res.append(stats)
     return res[0] if len(res) == 1 else tuple(res)
+
+
+class ActiveList:
+    """opaque device buffer holding one layer's active-row list (spif_active_list_bytes): produced by
+    sparse_ffn_lookahead or mask_to_list, consumed by the next sparse_ffn_lookahead"""
+    HDR, MAX_BLOCKS = 4, 1024
+
+    def __init__(self, m, device="cuda"):
+        self.m = int(m)
+        n = _lib.load().spif_active_list_bytes(self.m)
+        self.buf = torch.zeros(n // 4, dtype=torch.int32, device=device)
+
+    def rows(self):
+        """-> ascending active rows (host numpy), for tests"""
+        h = self.buf.cpu().numpy()
+        nblk = int(h[0])
+        cnt = h[self.HDR:self.HDR + nblk]
+        rows = h[self.HDR + self.MAX_BLOCKS:]
+        out = []
+        for b in range(nblk):
+            s = (b * self.m) // nblk
+            out.extend(rows[s:s + cnt[b]].tolist())
+        return out
+
+
+def mask_to_list(sparse_idx, thr=SPARSE_THRESHOLD, out=None):
+    """float mask indexed by row {m} -> ActiveList (spif_mask_to_list: ballot + popc per block of rows)"""
+    m = sparse_idx.numel()
+    out = out if out is not None else ActiveList(m, sparse_idx.device)
+    check(_lib.load().spif_mask_to_list(_p(sparse_idx), m, thr, _p(out.buf), _stream()), "spif_mask_to_list")
+    return out
+
+
+def sparse_ffn_lookahead(comm, ws, ffn=None, pred=None, list_in=None, list_out=None):
+    """spif_sparse_ffn_lookahead: the sparse FFN of one layer (ffn: dict of sparse_ffn's arguments arch, w_type, up, gate,
+    down_t, cur, n_ff, [neuron_idx, up_b, gate_b, down_b, flags, out, hidden_out, stats]) + the look-ahead predictor of
+    the next (pred: dict pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, m, [flags, thr, out, logits_out]) in
+    one launch; list_in / list_out are ActiveList objects."""
+    L = _lib.load()
+    fa = pa = None
+    if ffn is not None:
+        cur = ffn["cur"]
+        n_embd = cur.numel()
+        n_ff = ffn["n_ff"]
+        nidx = ffn.get("neuron_idx")
+        m = n_ff if nidx is None else nidx.numel()
+        fa = FfnArgs(arch=ffn["arch"], type=ffn["w_type"], n_embd=n_embd, n_ff=n_ff, m=m, n_tok=1, flags=ffn.get("flags", 0),
+                     thr=SPARSE_THRESHOLD, w_up=_p(ffn["up"]), w_gate=_p(ffn.get("gate")), w_down_t=_p(ffn["down_t"]),
+                     b_up=_p(ffn.get("up_b")), b_gate=_p(ffn.get("gate_b")), b_down=_p(ffn.get("down_b")), x=_p(cur),
+                     sparse_idx=None, neuron_idx=_p(nidx), y=_p(ffn["out"]), hidden_out=_p(ffn.get("hidden_out")),
+                     stats_out=_p(ffn.get("stats")))
+    if pred is not None:
+        cur = pred["cur"]
+        pa = PredArgs(ptype=pred["p_type"], n_embd=cur.numel(), r=pred["r"], m=pred["m"], flags=pred.get("flags", 0),
+                      thr=pred.get("thr", SPARSE_THRESHOLD), wpu=_p(pred["pred_up"]), bpu=_p(pred.get("pred_up_b")),
+                      wpd=_p(pred["pred_down"]), bpd=_p(pred.get("pred_down_b")), x=_p(cur),
+                      sparse_idx_out=_p(pred.get("out")), logits_out=_p(pred.get("logits_out")))
+    check(L.spif_sparse_ffn_lookahead(ctypes.byref(fa) if fa is not None else None, ctypes.byref(pa) if pa is not None else None,
+                                      _p(list_in.buf) if list_in is not None else None,
+                                      _p(list_out.buf) if list_out is not None else None, ctypes.byref(comm.c), ws.ptr,
+                                      ws.nbytes, _stream()), "spif_sparse_ffn_lookahead")
 
 
 def dfr_update(sparse_idx, dfr_scores, g, lam, ema=True, thr=SPARSE_THRESHOLD):

@@ -39,16 +39,18 @@ class FfnStack:
         # per-layer sum over the shards: "peer" = fused into the layer's partial-sum kernel over NVLink peer memory
         # (spif_sparse_ffn_sharded), "nccl" = one ncclAllReduce per layer
         self.comm = None
+        if group is None:
+            self.comm = ops.ShardComm(n_tok * n_embd + r, None, device)  # world 1: the layer kernel's control words + h1
         if group is not None and exchange == "peer":
             try:
-                comm = ops.ShardComm(n_tok * n_embd, group, device)
+                comm = ops.ShardComm(n_tok * n_embd + r, group, device)
             except Exception as e:  # symmetric memory not available here: every rank must take the same decision
                 comm = None
                 print(f"[sparkinfer_b200] peer exchange unavailable ({type(e).__name__}: {e}); using ncclAllReduce", flush=True)
             ok = torch.tensor([1 if comm is not None else 0], device=device)
             torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN, group=group)
             self.comm = comm if int(ok.item()) == 1 else None
-        self.exchange = "peer" if self.comm is not None else ("nccl" if group is not None else "none")
+        self.exchange = "none" if group is None else ("peer" if self.comm is not None else "nccl")
         self.flags = flags
         self.ws = ops.Workspace(n_embd, n_ff_local, n_tok, device)
         self.x = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)
@@ -64,6 +66,8 @@ class FfnStack:
         self._side = torch.cuda.Stream(device=device)
         # the predictor's hidden vector lives in the workspace: a predictor running concurrently with an FFN needs its own
         self.ws_pred = ops.Workspace(n_embd, n_ff_local, n_tok, device)
+        # active-row lists handed from launch to launch by the look-ahead layer kernel (double-buffered)
+        self.lists = [ops.ActiveList(n_ff_local, device), ops.ActiveList(n_ff_local, device)]
 
     # -- single pieces ------------------------------------------------------------------------------------------
     def predict(self, l, x_from):
@@ -82,7 +86,7 @@ class FfnStack:
         fl = self.flags | (ops.FLAG_MASK_STABLE if mask_stable else 0)
         ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=fl,
                        ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None,
-                       comm=self.comm if exchange else None)
+                       comm=self.comm if (exchange and self.group is not None) else None)
         return 2  # kernels: fused gate/up/act/down, partial reduction (+ shard exchange)
 
     def allreduce(self, l):
@@ -128,6 +132,62 @@ class FfnStack:
         self.launches_per_step = n
         return n
 
+    # -- look-ahead layer kernel: FFN(l) + predictor(l+1) in ONE launch (spif_sparse_ffn_lookahead) ------------------
+    def fused_supported(self):
+        return (self.n_tok == 1 and self.comm is not None and self.w_type == self.p_type and self.r % 256 == 0
+                and self.r <= self.n_embd and self.n_embd <= 8192 and self.w_type in (ops.GGML_TYPE_F16, ops.GGML_TYPE_BF16))
+
+    def _lookahead(self, l_ffn, l_pred, x_from, want_stats=False):
+        """one launch: the sparse FFN of layer l_ffn (None: none) and the predictor of layer l_pred (None: none), both
+        reading x[x_from]; the predictor's list goes to lists[l_pred % 2], the FFN reads lists[l_ffn % 2]"""
+        ffn = pred = None
+        n = 1
+        if l_ffn is not None:
+            w = self.layers[l_ffn]
+            ffn = dict(arch=self.arch, w_type=self.w_type, up=w.up, gate=w.gate, down_t=w.down_t, cur=self.x[l_ffn, 0],
+                       n_ff=self.m, flags=self.flags, out=self.y[l_ffn, 0], stats=self.stats[l_ffn, 0] if want_stats else None)
+        if l_pred is not None:
+            w = self.layers[l_pred]
+            pred = dict(pred_up=w.pred_up, pred_down=w.pred_down, pred_down_b=w.pred_down_b, cur=self.x[x_from, 0],
+                        p_type=self.p_type, r=self.r, m=self.m, flags=self.flags, out=self.p[l_pred, 0],
+                        logits_out=self.logits[0] if self.topk > 0 else None)
+        ops.sparse_ffn_lookahead(self.comm, self.ws, ffn=ffn, pred=pred,
+                                 list_in=self.lists[l_ffn % 2] if l_ffn is not None else None,
+                                 list_out=self.lists[l_pred % 2] if (l_pred is not None and self.topk == 0) else None)
+        if l_pred is not None and self.topk > 0:  # top-k configs: the list comes from the k largest logits of this shard
+            ops.topk_mask(self.logits, self.topk, out=self.p[l_pred])
+            ops.mask_to_list(self.p[l_pred, 0], out=self.lists[l_pred % 2])
+            n += 2
+        return n
+
+    def step_fused(self, want_stats=False):
+        """the reference's decode order (llama-graph.cpp:932-946) with ONE launch per layer: predictor(0) from x_0, then
+        FFN(l) + predictor(l+1) from x_l.  The true data edges hold by construction (single stream, launch l+1 after l)."""
+        n = self._lookahead(None, 0, 0)
+        for l in range(self.L):
+            n += self._lookahead(l, l + 1 if l + 1 < self.L else None, l, want_stats)
+        self.launches_per_step = n
+        return n
+
+    def ffn_only_fused(self, want_stats=False):
+        """the sparse FFNs alone through the layer kernel (pred == NULL), lists rebuilt from the masks in self.p"""
+        n = 0
+        for l in range(self.L):
+            ops.mask_to_list(self.p[l, 0], out=self.lists[l % 2])
+            w = self.layers[l]
+            ops.sparse_ffn_lookahead(self.comm, self.ws, ffn=dict(arch=self.arch, w_type=self.w_type, up=w.up, gate=w.gate,
+                                                                  down_t=w.down_t, cur=self.x[l, 0], n_ff=self.m, flags=self.flags,
+                                                                  out=self.y[l, 0], stats=self.stats[l, 0] if want_stats else None),
+                                     list_in=self.lists[l % 2])
+            n += 2
+        return n
+
+    def predict_only_fused(self):
+        n = self._lookahead(None, 0, 0)
+        for l in range(self.L - 1):
+            n += self._lookahead(None, l + 1, l)
+        return n
+
     def ffn_only_eager(self, want_stats=False):
         """the sparse FFNs alone, masks as left in self.p by the last full step"""
         n = 0
@@ -154,7 +214,7 @@ class FfnStack:
                 fn()
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
-        if fn == self.step_eager:
+        if fn in (self.step_eager, self.step_fused):
             self.graph = g
         return g
 

@@ -72,6 +72,7 @@ def parse_args():
                          "a real decode: kept for comparison only)")
     ap.add_argument("--parity-layers", type=int, default=4, help="layers of the timed stack checked against the CPU oracle")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the reference-CUDA-kernels leg (oracle/_ref/libspif_refcuda.so)")
     ap.add_argument("--no-scale-70b", action="store_true", help="N > 1: skip the relullama-70b scaling leg")
     ap.add_argument("--no-early-mask", action="store_true", help="do not use SPIF_FLAG_MASK_STABLE")
     return ap.parse_args()
@@ -460,12 +461,48 @@ def run_ours(a):
     }
     if scale_70b is not None:
         out["scale_70b"] = scale_70b
+    if world == 1 and not a.no_gpu_baseline:
+        out["gpu_baseline"] = gpu_baseline(a, st, wl, x_pool[0], device)
     if world == 1 and not a.no_batched:
         out["batched"] = batched_legs(a, st, wl, device)
     if world == 1 and not a.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(a, wl, iters=8, warmup=2)
     print(json.dumps(out), flush=True)
     leave()
+
+
+def gpu_baseline(a, st, wl, x0, device):
+    """the reference's OWN CUDA kernels (mm-sparse.cu, axpy-sparse.cu, mmvf.cu, unary.cu, binbcast.cu: compiled unmodified for
+    sm_100 into oracle/_ref/libspif_refcuda.so) on the SAME device-resident weights and inputs, in the reference's node
+    order on one stream, timed with CUDA events -- once through a CUDA graph (how a GGML_CUDA_GRAPHS build decodes) and once
+    as eager launches.  A reported baseline: the only place outside tests/ that loads anything from oracle/."""
+    import oracle_lib
+    import torch
+    if wl.get("topk") or not oracle_lib.RefCuda.available():
+        return {"unavailable": "no reference code path for this config" if wl.get("topk") else
+                "oracle/_ref/libspif_refcuda.so not built (needs /root/reference at build time)"}
+    rc = oracle_lib.RefCuda()
+    E, F, L, R = wl["n_embd"], wl["n_ff"], wl["n_layer"], a.rank
+    x = x0[:, 0].contiguous()
+    y = torch.zeros((L, E), dtype=torch.float32, device=device)
+    p_io = torch.zeros((L, F), dtype=torch.float32, device=device)
+    ly = st.layers
+    args = (wl["arch"], F16, F16, [w.up for w in ly], [w.gate for w in ly], [w.down_t for w in ly], [w.pred_up for w in ly],
+            [w.pred_down for w in ly], [w.pred_down_b for w in ly], x, y, p_io, E, F, R)
+    us_graph, us_eager = rc.stack(*args, with_pred=True, warmup=3, iters=20)
+    # the same kernels on OUR masks (no predictor): its y against ours, a reported third comparison (SURVEY.md 8c)
+    st.x.copy_(x0)
+    st.step_fused() if st.fused_supported() else st.step_eager()
+    torch.cuda.synchronize()
+    p_io.copy_(st.p[:, 0])
+    us_ffn_graph, _ = rc.stack(*args, with_pred=False, warmup=1, iters=10)
+    torch.cuda.synchronize()
+    ours = st.y[:, 0]
+    err = float(((y - ours).abs().amax(dim=1) / ours.abs().amax(dim=1).clamp_min(1e-30)).max().item())
+    return {"value": 1e6 / us_graph, "unit": "tok/s", "us_per_layer": us_graph / L, "eager_tok_s": 1e6 / us_eager,
+            "ffn_only_us_per_layer": us_ffn_graph / L, "kind": "reference CUDA kernels, sm_100 (unmodified sources), CUDA graph",
+            "what": rc.describe(), "max_rel_err_vs_ours_same_masks": err,
+            "note": "half2 accumulation (GGML_PREC_DEFAULT, mm-sparse.cu:355-361) and float atomics in the axpy (axpy-sparse.cu:84)"}
 
 
 def quick_leg(a, workload, rank, world, device, barrier):

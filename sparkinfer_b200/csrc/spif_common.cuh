@@ -52,18 +52,23 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t * bar, uint32_t b
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 
+// Blocking wait for a phase.  The suspend-time hint matters: without it try_wait returns after a short system-dependent
+// limit and the loop becomes a hot spin -- 20 spinning consumer warps took 5/6 of the issue slots of the scheduler that
+// also runs the producer warp, which then needed ~1 us per ring item (profiles/r2_layer_trace.txt: the "22 GB/s per SM
+// cap" of every mbarrier ring in this repo).  With the hint the thread sleeps in hardware until the phase completes.
 __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
+    const uint32_t addr  = smem_u32(bar);
+    const uint32_t ticks = 0x989680u;
     asm volatile(
         "{\n\t"
         ".reg .pred P1;\n\t"
         "SPIF_WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n\t"
         "@P1 bra SPIF_WAIT_DONE;\n\t"
         "bra SPIF_WAIT_LOOP;\n\t"
         "SPIF_WAIT_DONE:\n\t"
         "}" ::"r"(addr),
-        "r"(parity)
+        "r"(parity), "r"(ticks)
         : "memory");
 }
 
@@ -97,6 +102,13 @@ __device__ __forceinline__ void tma_load_1d(void * smem_dst, const void * gmem_s
             smem_u32(smem_dst)),
         "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
         : "memory");
+}
+
+__device__ __forceinline__ void tma_load_1d_nohint(void * smem_dst, const void * gmem_src, uint32_t bytes, uint64_t * bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 
 // named barrier among a subset of the CTA's warps

@@ -18,22 +18,24 @@
 //   * No second kernel for the partial sum (round 1: 3-4 us per layer, 10.7 % of the launch list).
 //   * One register budget: round 1's FFN and predictor grids fought for the SMs and overlapped by 2.7 us of 25.
 //
-// Data movement: ONE elected thread streams everything with 1-D TMA bulk copies (cp.async.bulk -> UBLKCP) into a ring of
-// slots of two rows each (13B: 10 x 20 KB = 200 KB in flight per SM, Little's law needs ~64 KB); completion by mbarrier
-// complete_tx.  Consumer warps own fixed 16-byte column slices of a row (x in registers), multiply whatever item arrives
-// (two rows -> two partial dots, reduced with ONE packed shuffle tree), publish per-warp partials in shared memory and
-// arrive on the slot's `done` barrier; they never wait for each other.  The producer warp doubles as the epilogue: it
-// retires items in order (cross-warp sum in a fixed order, bias, activation, sigmoid, list compaction), pushes the
-// W_down^T rows of neurons whose hidden value is non-zero into the queue, and refills the freed slot.
+// Data movement: ONE elected thread (the issuer warp) streams everything with 1-D TMA bulk copies (cp.async.bulk -> UBLKCP)
+// into a ring of slots of RPS = 4 (2 for rows > 12 KB) weight rows each (13B: 5 x 40 KB = 200 KB in flight per SM, Little's
+// law needs ~64 KB); completion by mbarrier complete_tx.  Consumer warps own fixed 16-byte column slices of a row (x in
+// registers), multiply whatever item arrives (RPS rows -> RPS partial dots, reduced with ONE packed shuffle tree), publish
+// per-warp partials in shared memory and arrive on the slot's `done` barrier; they never wait for each other.  A third
+// role, the epilogue warp, retires items in order (cross-warp sum in a fixed order, bias, activation, sigmoid, list
+// compaction), pushes the W_down^T rows of neurons whose hidden value is non-zero to the issuer's queue and frees the slot.
 //
 // Determinism: every sum has a fixed shape (packed shuffle tree per warp, fixed warp order, W_down^T rows in ascending
 // neuron order per CTA, partials in CTA order) -> run-to-run bit-stable, unlike axpy-sparse.cu:84 (float atomics).
 #include "spif_comm.cuh"
 
+#include <cstdlib>
+
 #define SPIF_LIST_MAX_BLOCKS 1024
 #define SPIF_LIST_HDR        4 /* int32: {nblk, m, 0, 0} */
 
-enum { IT_WPU2 = 0, IT_GU = 1, IT_DN2 = 2, IT_WPD2 = 3, IT_FLUSH = 4, IT_END = 5 };
+enum { IT_WPU = 0, IT_GU = 1, IT_DN = 2, IT_WPD = 3, IT_FLUSH = 4, IT_END = 5 };
 
 struct LayerParams {
     // ---- sparse FFN of this layer (has_ffn)
@@ -65,22 +67,24 @@ struct LayerParams {
     int                   has_ffn, has_pred;
     int                   n_embd, V, row_bytes;
     int                   m, n_ff, lin_nblk;
-    int                   r, pm, Vr, RP, WR;  // Vr = r/8 vectors per Wpd row, RP = Wpd rows per half slot, WR = warps per Wpd row
+    int                   r, pm, Vr, RP, WR;  // Vr = r/8 vectors per Wpd row, RP = Wpd rows per slot row, WR = 32-vector groups per Wpd row
     int                   nw;                 // consumer warps
     int                   nslots;
     int                   cap_ffn, cap_pd, cap_pu;
     float                 thr_next;           // threshold for the list of the next layer
     int                   arch, flags, pflags;
+    int                   l2_hint;            // 1: TMA copies carry an L2 evict_first policy
     spif_comm_dev         comm;
     unsigned long long *  trace;
 };
 
 struct LayerSmem {
-    uint32_t ring, full, done, desc, dalpha, part, list_row, list_neu, list_bu, list_bg, pend_row, pend_alpha, bpu_s, bpd_s,
-        lout_s, total;
+    uint32_t ring, full, done, freeb, desc, dalpha, part, ctl, list_row, list_neu, list_bu, list_bg, pend_row, pend_alpha, bpu_s,
+        bpd_s, lout_s, h1_s, blk_pre, total;
 };
 
-__host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int slot_bytes, int cap_ffn, int cap_pd, int cap_pu) {
+__host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int slot_bytes, int cap_ffn, int cap_pd, int cap_pu,
+                                                              int r, int nblk) {
     LayerSmem L;
     uint32_t  o = 0;
     auto      take = [&](uint32_t bytes, uint32_t align) {
@@ -92,9 +96,11 @@ __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int sl
     L.ring       = take((uint32_t) nslots * slot_bytes, 128);
     L.full       = take(8u * nslots, 8);
     L.done       = take(8u * nslots, 8);
+    L.freeb      = take(8u * nslots, 8);
     L.desc       = take(16u * nslots, 16);
-    L.dalpha     = take(8u * nslots, 8);
-    L.part       = take(4u * 64 * nslots, 16);
+    L.dalpha     = take(16u * nslots, 16);
+    L.part       = take(4u * 128 * nslots, 16);
+    L.ctl        = take(16u, 16);
     L.list_row   = take(4u * cap_ffn, 4);
     L.list_neu   = take(4u * cap_ffn, 4);
     L.list_bu    = take(4u * cap_ffn, 4);
@@ -104,6 +110,8 @@ __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int sl
     L.bpu_s      = take(4u * cap_pu, 4);
     L.bpd_s      = take(4u * cap_pd, 4);
     L.lout_s     = take(4u * cap_pd, 4);
+    L.h1_s       = take(4u * r, 16);
+    L.blk_pre    = take(4u * (nblk + 1), 4);
     L.total      = (o + 127) / 128 * 128;
     return L;
 }
@@ -113,8 +121,21 @@ __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int sl
         if (p.trace && lane == 0) {                                      \
             unsigned long long _t;                                       \
             asm volatile("mov.u64 %0, %globaltimer;" : "=l"(_t));        \
-            p.trace[(size_t) blockIdx.x * 16 + (k)] = _t;                \
+            p.trace[(size_t) blockIdx.x * 512 + (k)] = _t;               \
         }                                                                \
+    } while (0)
+
+// per-item stamps (debug): [16 + 4*q + {0: type, 1: issued, 2: landed (consumer warp 0), 3: retired}] for q < 120, in SM
+// clock cycles (clock64: cheap; %globaltimer ticks every 256 ns).  [15] = the CTA's clock at kernel entry.
+#define ITEM_STAMP(q, j, val)                                                        \
+    do {                                                                             \
+        if (p.trace && lane == 0 && (q) < 120) {                                     \
+            unsigned long long _t = (val);                                           \
+            if (_t == 0) {                                                           \
+                _t = (unsigned long long) clock64();                                 \
+            }                                                                        \
+            p.trace[(size_t) blockIdx.x * 512 + 16 + 4 * (q) + (j)] = _t;            \
+        }                                                                            \
     } while (0)
 
 // lanes 0..15 return the warp sum of a, lanes 16..31 the warp sum of b: two reductions for the price of one tree
@@ -129,23 +150,66 @@ __device__ __forceinline__ float reduce2(float a, float b, int lane) {
     keep += __shfl_xor_sync(0xffffffffu, keep, 1);
     return keep;
 }
+// four reductions with six shuffles: lanes [8j, 8j+8) return the warp sum of v[j]
+__device__ __forceinline__ float reduce4(float v0, float v1, float v2, float v3, int lane) {
+    const bool hi = (lane & 16) != 0, h8 = (lane & 8) != 0;
+    float k0 = (hi ? v2 : v0) + __shfl_xor_sync(0xffffffffu, hi ? v0 : v2, 16);
+    float k1 = (hi ? v3 : v1) + __shfl_xor_sync(0xffffffffu, hi ? v1 : v3, 16);
+    float m  = (h8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, h8 ? k0 : k1, 8);
+    m += __shfl_xor_sync(0xffffffffu, m, 4);
+    m += __shfl_xor_sync(0xffffffffu, m, 2);
+    m += __shfl_xor_sync(0xffffffffu, m, 1);
+    return m;
+}
 
-template <typename WT, int VPT, int MAXT>
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ int ld_volatile_s32(const int * p) {
+    return *reinterpret_cast<const volatile int *>(p);
+}
+__device__ __forceinline__ void st_volatile_s32(int * p, int v) {
+    *reinterpret_cast<volatile int *>(p) = v;
+}
+
+template <typename WT> __device__ __forceinline__ float dot8(const uint4 & wv, const float * xv) {
+    float w[8];
+    unpack8<WT>(wv, w);
+    float s0 = w[0] * xv[0], s1 = w[1] * xv[1];
+    s0 = fmaf(w[2], xv[2], s0), s1 = fmaf(w[3], xv[3], s1);
+    s0 = fmaf(w[4], xv[4], s0), s1 = fmaf(w[5], xv[5], s1);
+    s0 = fmaf(w[6], xv[6], s0), s1 = fmaf(w[7], xv[7], s1);
+    return s0 + s1;
+}
+
+// Warp roles: [0, NW) consumers, NW = TMA issuer, NW + 1 = epilogue.  RPS = weight rows per ring slot (one queue item).
+//   issuer    waits for a free slot, decides what goes in (pending W_down^T rows first, then the static stream Wpu -> gate/up ->
+//             Wpd), issues the bulk copies.  Nothing else: a single warp executes ~1 dependent instruction per 5 cycles, so the
+//             first version (issue + retire in one warp, ~1 us per item) capped the SM at 20 GB/s (profiles/r2_layer_trace.txt).
+//   consumers multiply the RPS rows of an item with x (or the predictor's hidden vector), RPS partial dots -> one packed
+//             shuffle tree -> per-warp partials in shared memory -> arrive on done[slot].
+//   epilogue  retires items in order: cross-warp sums (fixed order), bias / activation / sigmoid / list compaction, pushes
+//             W_down^T rows of non-zero hidden values to the issuer's queue, frees the slot.
+template <typename WT, int VPT, int RPS, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NW = p.nw, NC = NW * 32;
     const int P = gridDim.x, c = blockIdx.x;
     const int N = p.nslots;
-    const int slot_bytes = 2 * p.row_bytes;
+    const int slot_bytes = RPS * p.row_bytes;
 
-    const LayerSmem L = layer_smem_layout(N, slot_bytes, p.cap_ffn, p.cap_pd, p.cap_pu);
+    const LayerSmem L = layer_smem_layout(N, slot_bytes, p.cap_ffn, p.cap_pd, p.cap_pu, p.has_pred ? p.r : 0, p.lin_nblk);
     unsigned char * ring       = smem + L.ring;
     uint64_t *      full       = reinterpret_cast<uint64_t *>(smem + L.full);
     uint64_t *      done       = reinterpret_cast<uint64_t *>(smem + L.done);
+    uint64_t *      freeb      = reinterpret_cast<uint64_t *>(smem + L.freeb);
     int4 *          desc       = reinterpret_cast<int4 *>(smem + L.desc);
-    float *         dalpha     = reinterpret_cast<float *>(smem + L.dalpha);  // [N][2]
-    float *         part       = reinterpret_cast<float *>(smem + L.part);    // [N][2][32]
+    float *         dalpha     = reinterpret_cast<float *>(smem + L.dalpha);  // [N][4]
+    float *         part       = reinterpret_cast<float *>(smem + L.part);    // [N][4][32]
+    int *           ctl        = reinterpret_cast<int *>(smem + L.ctl);       // [0] pend_tail, [1] gu items retired
     int *           list_row   = reinterpret_cast<int *>(smem + L.list_row);
     int *           list_neu   = reinterpret_cast<int *>(smem + L.list_neu);
     float *         list_bu    = reinterpret_cast<float *>(smem + L.list_bu);
@@ -155,12 +219,19 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
     float *         bpu_s      = reinterpret_cast<float *>(smem + L.bpu_s);
     float *         bpd_s      = reinterpret_cast<float *>(smem + L.bpd_s);
     int *           lout_s     = reinterpret_cast<int *>(smem + L.lout_s);
+    float *         h1_s       = reinterpret_cast<float *>(smem + L.h1_s);
+    int *           blk_pre    = reinterpret_cast<int *>(smem + L.blk_pre);
 
     if (tid == 0) {
+        if (p.trace) {
+            p.trace[(size_t) blockIdx.x * 512 + 15] = (unsigned long long) clock64();
+        }
         for (int s = 0; s < N; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&done[s], NW);
+            mbar_init(&freeb[s], 1);
         }
+        ctl[0] = 0, ctl[1] = 0;
         mbar_fence_init();
     }
     __syncthreads();
@@ -180,147 +251,152 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         pa = (int) ((long long) c * p.pm / P);
         pb = (int) ((long long) (c + 1) * p.pm / P);
     }
+    const int neu_per_gu = gated ? RPS / 2 : RPS;  // neurons per gate/up item
 
     if (warp == NW) {
-        // =========================================== producer + epilogue warp ===========================================
-        const uint64_t pol = l2_policy_evict_first();
-        for (int i = lane; i < rb - ra; i += 32) {
-            bpu_s[i] = p.bpu ? __ldg(p.bpu + ra + i) : 0.f;
-        }
-        for (int i = lane; i < pb - pa; i += 32) {
-            bpd_s[i] = p.bpd ? __ldg(p.bpd + pa + i) : 0.f;
-        }
-        __syncwarp();
+        // ================================================= TMA issuer warp =================================================
+        const uint64_t pol  = l2_policy_evict_first();
+        const bool     hint = p.l2_hint != 0;
+        auto tma = [&](void * dst, const void * src, uint32_t bytes, uint64_t * bar) {
+            if (hint) {
+                tma_load_1d(dst, src, bytes, bar, pol);
+            } else {
+                tma_load_1d_nohint(dst, src, bytes, bar);
+            }
+        };
+        int      q = 0, s = 0;
+        unsigned fph = 0;          // phase of free[s] to wait for once q >= N
+        int      a_next = ra, b_next = 0, b_end = 0, c_next = pa;
+        int      pend_head = 0, gu_issued = 0, total_active = 0;
+        bool     flushed = false, list_ready = !p.has_ffn;
+        const uint32_t wrow = (uint32_t) p.r * 2;
 
-        int  q_issue = 0, q_done = 0;
-        int  a_next = ra, b_next = 0, b_end = 0, c_next = pa;
-        int  pend_head = 0, pend_tail = 0, gu_inflight = 0;
-        int  n_nonzero = 0, cnt_out = 0, total_active = 0;
-        bool flushed = false, ended = false, list_ready = !p.has_ffn;
-        const int rows_per_wpd = 2 * p.RP;
-
-        // issue one item into slot q % N; returns false if nothing can be issued right now
-        auto issue_next = [&]() -> bool {
-            const int s  = q_issue % N;
-            const int np = pend_tail - pend_head;
-            int       type = -1;
-            if (np >= 2) {
-                type = IT_DN2;
+        // returns 1 if an item was issued, 0 if nothing can be issued right now, -1 after END
+        auto issue_next = [&]() -> int {
+            int gu_ret = 0, np = 0;
+            if (p.has_ffn) {
+                gu_ret = ld_volatile_s32(ctl + 1);
+                __threadfence_block();
+                np = ld_volatile_s32(ctl + 0) - pend_head;  // read AFTER gu_ret: covers every push of the retired items
+            }
+            const bool gu_all_issued = list_ready && b_next >= b_end;
+            const bool gu_all_done   = gu_all_issued && gu_ret == gu_issued;
+            int        type          = -1;
+            if (np >= RPS || (np >= 2 && !gu_all_done) || (np >= 1 && gu_all_done)) {
+                type = IT_DN;
             } else if (a_next < rb) {
-                type = IT_WPU2;
+                type = IT_WPU;
             } else if (!list_ready) {
-                return false;
+                return 0;
             } else if (b_next < b_end) {
                 type = IT_GU;
-            } else if (np == 1 && gu_inflight == 0) {
-                type = IT_DN2;
-            } else if (p.has_ffn && !flushed && gu_inflight == 0 && np == 0) {
+            } else if (p.has_ffn && !flushed && gu_all_done && np == 0) {
                 type = IT_FLUSH;
             } else if (c_next < pb) {
-                type = IT_WPD2;
-            } else if (q_done == q_issue && np == 0 && gu_inflight == 0 && (flushed || !p.has_ffn)) {
+                type = IT_WPD;
+            } else if (flushed || !p.has_ffn) {
                 type = IT_END;
             } else {
-                return false;
+                return 0;  // gate/up items still in flight: their W_down^T rows may follow
+            }
+            if (q >= N) {
+                mbar_wait(&freeb[s], fph);
             }
             unsigned char * dst = ring + (size_t) s * slot_bytes;
-            switch (type) {
-                case IT_WPU2: {
-                    const int n = min(2, rb - a_next);
-                    if (lane == 0) {
-                        desc[s] = make_int4(IT_WPU2, a_next, n, 0);
+            if (lane == 0) {
+                switch (type) {
+                    case IT_WPU: {
+                        const int n = min(RPS, rb - a_next);
+                        desc[s]     = make_int4(IT_WPU, a_next, n, 0);
                         mbar_arrive_expect_tx(&full[s], (uint32_t) n * p.row_bytes);
+                        tma(dst, p.wpu + (size_t) a_next * p.row_bytes, (uint32_t) n * p.row_bytes, &full[s]);  // rows are adjacent
+                    } break;
+                    case IT_GU: {
+                        const int n = min(neu_per_gu, b_end - b_next);
+                        desc[s]     = make_int4(IT_GU, b_next, n, 0);
+                        mbar_arrive_expect_tx(&full[s], (uint32_t) (gated ? 2 * n : n) * p.row_bytes);
                         for (int j = 0; j < n; ++j) {
-                            tma_load_1d(dst + (size_t) j * p.row_bytes, p.wpu + (size_t) (a_next + j) * p.row_bytes, p.row_bytes,
-                                        &full[s], pol);
-                        }
-                    }
-                    a_next += n;
-                } break;
-                case IT_GU: {
-                    const int n = gated ? 1 : min(2, b_end - b_next);
-                    if (lane == 0) {
-                        desc[s] = make_int4(IT_GU, b_next, n, 0);
-                        mbar_arrive_expect_tx(&full[s], (uint32_t) (gated ? 2 : n) * p.row_bytes);
-                        if (gated) {
-                            const size_t off = (size_t) list_row[b_next] * p.row_bytes;
-                            tma_load_1d(dst, p.w_up + off, p.row_bytes, &full[s], pol);
-                            tma_load_1d(dst + p.row_bytes, p.w_gate + off, p.row_bytes, &full[s], pol);
-                        } else {
-                            for (int j = 0; j < n; ++j) {
-                                tma_load_1d(dst + (size_t) j * p.row_bytes, p.w_up + (size_t) list_row[b_next + j] * p.row_bytes,
-                                            p.row_bytes, &full[s], pol);
+                            const size_t off = (size_t) list_row[b_next + j] * p.row_bytes;
+                            if (gated) {
+                                tma(dst + (size_t) (2 * j) * p.row_bytes, p.w_up + off, p.row_bytes, &full[s]);
+                                tma(dst + (size_t) (2 * j + 1) * p.row_bytes, p.w_gate + off, p.row_bytes, &full[s]);
+                            } else {
+                                tma(dst + (size_t) j * p.row_bytes, p.w_up + off, p.row_bytes, &full[s]);
                             }
                         }
-                    }
-                    b_next += n;
-                    ++gu_inflight;
-                } break;
-                case IT_DN2: {
-                    const int n = min(2, np);
-                    if (lane == 0) {
-                        desc[s] = make_int4(IT_DN2, n, 0, 0);
+                    } break;
+                    case IT_DN: {
+                        const int n = min(RPS, np);
+                        desc[s]     = make_int4(IT_DN, n, 0, 0);
                         mbar_arrive_expect_tx(&full[s], (uint32_t) n * p.row_bytes);
                         for (int j = 0; j < n; ++j) {
-                            dalpha[s * 2 + j] = pend_alpha[pend_head + j];
-                            tma_load_1d(dst + (size_t) j * p.row_bytes, p.w_down + (size_t) pend_row[pend_head + j] * p.row_bytes,
-                                        p.row_bytes, &full[s], pol);
+                            dalpha[s * 4 + j] = pend_alpha[pend_head + j];
+                            tma(dst + (size_t) j * p.row_bytes, p.w_down + (size_t) pend_row[pend_head + j] * p.row_bytes, p.row_bytes,
+                                &full[s]);
                         }
-                    }
-                    pend_head += n;
-                } break;
-                case IT_WPD2: {
-                    const int n  = min(rows_per_wpd, pb - c_next);
-                    const int n0 = min(p.RP, n), n1 = n - n0;
-                    if (lane == 0) {
-                        desc[s] = make_int4(IT_WPD2, c_next, n0, n1);
-                        const uint32_t wrow = (uint32_t) p.r * 2;
+                    } break;
+                    case IT_WPD: {
+                        const int n = min(RPS * p.RP, pb - c_next);
+                        desc[s]     = make_int4(IT_WPD, c_next, n, 0);
                         mbar_arrive_expect_tx(&full[s], (uint32_t) n * wrow);
-                        tma_load_1d(dst, p.wpd + (size_t) c_next * wrow, (uint32_t) n0 * wrow, &full[s], pol);
-                        if (n1 > 0) {
-                            tma_load_1d(dst + p.row_bytes, p.wpd + (size_t) (c_next + n0) * wrow, (uint32_t) n1 * wrow, &full[s], pol);
+                        for (int j = 0, left = n; left > 0; ++j, left -= p.RP) {  // RP rows of Wpd per slot row
+                            tma(dst + (size_t) j * p.row_bytes, p.wpd + (size_t) (c_next + j * p.RP) * wrow,
+                                (uint32_t) min(left, p.RP) * wrow, &full[s]);
                         }
-                    }
-                    c_next += n;
-                } break;
-                case IT_FLUSH:
-                    if (lane == 0) {
-                        desc[s] = make_int4(IT_FLUSH, 0, 0, 0);
+                    } break;
+                    case IT_FLUSH:
+                        desc[s] = make_int4(IT_FLUSH, total_active, 0, 0);
                         mbar_arrive(&full[s]);
-                    }
-                    flushed = true;
-                    break;
-                default: /* IT_END */
-                    if (lane == 0) {
+                        break;
+                    default:
                         desc[s] = make_int4(IT_END, 0, 0, 0);
                         mbar_arrive(&full[s]);
-                    }
-                    ended = true;
-                    break;
+                        break;
+                }
             }
-            ++q_issue;
-            __syncwarp();  // desc / dalpha written by lane 0 are read by every lane at retire time
-            return true;
+            switch (type) {
+                case IT_WPU: a_next += min(RPS, rb - a_next); break;
+                case IT_GU: b_next += min(neu_per_gu, b_end - b_next); ++gu_issued; break;
+                case IT_DN: pend_head += min(RPS, np); break;
+                case IT_WPD: c_next += min(RPS * p.RP, pb - c_next); break;
+                case IT_FLUSH: flushed = true; break;
+                default: break;
+            }
+            ITEM_STAMP(q, 0, (unsigned long long) (type + 1));
+            ITEM_STAMP(q, 1, 0);
+            ++q;
+            if (++s == N) {
+                s = 0;
+                fph ^= (q > N) ? 1u : 0u;
+            }
+            return type == IT_END ? -1 : 1;
         };
 
         // ---- before the programmatic-dependent-launch wait: the predictor up-projection rows are already on their way
-        while (q_issue < N && a_next < rb) {
+        while (q < N && a_next < rb) {
             issue_next();
         }
         LAYER_STAMP(0);
         pdl_wait_prior_grid();
         pdl_launch_dependents();
         LAYER_STAMP(1);
-        seq = spif_comm_call_seq(p.comm);
-        const uint32_t par = seq & 1u;
 
         // ---- my share of this layer's active rows: ranks [c*A/P, (c+1)*A/P) of the concatenated block lists
         if (p.has_ffn) {
-            const int nb = p.lin_nblk, kb = (nb + 31) / 32;
+            // lane L owns blocks [L*kb, (L+1)*kb): all counts are requested at once (one L2 round trip), one warp scan, the
+            // exclusive prefix of every block goes to shared memory; then one lane per list entry finds its block by binary
+            // search and fetches the row (second round trip, all entries in parallel)
+            const int nb = p.lin_nblk, kb = (nb + 31) / 32;  // kb <= 8 (checked by the launcher: nblk <= 256)
             const int b0 = min(lane * kb, nb), b1 = min(b0 + kb, nb);
+            int       cb[8];
             int       local = 0;
-            for (int b = b0; b < b1; ++b) {
-                local += __ldcg(p.lin_cnt + b);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                cb[j] = (b0 + j < b1) ? __ldcg(p.lin_cnt + b0 + j) : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                local += cb[j];
             }
             int incl = local;
 #pragma unroll
@@ -329,24 +405,34 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                 incl += (lane >= o) ? t : 0;
             }
             total_active = __shfl_sync(0xffffffffu, incl, 31);
-            const int lo = (int) ((long long) c * total_active / P), hi = (int) ((long long) (c + 1) * total_active / P);
-            b_end        = hi - lo;
             int pbk      = incl - local;
-            for (int b = b0; b < b1; ++b) {
-                const int cb = __ldcg(p.lin_cnt + b);
-                const int s0 = max(pbk, lo), s1 = min(pbk + cb, hi);
-                if (s0 < s1) {
-                    const int start_b = (int) ((long long) b * p.m / nb);
-                    for (int i = s0; i < s1; ++i) {
-                        list_row[i - lo] = __ldcg(p.lin_rows + start_b + (i - pbk));
-                    }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (b0 + j < b1) {
+                    blk_pre[b0 + j] = pbk;
                 }
-                pbk += cb;
+                pbk += cb[j];
+            }
+            if (lane == 31) {
+                blk_pre[nb] = total_active;
             }
             __syncwarp();
+            const int lo = (int) ((long long) c * total_active / P), hi = (int) ((long long) (c + 1) * total_active / P);
+            b_end        = hi - lo;
             for (int j = lane; j < b_end; j += 32) {
-                const int row = list_row[j];
+                const int rank = lo + j;
+                int       bl = 0, bh = nb;  // blk_pre[bl] <= rank < blk_pre[bh]
+                while (bh - bl > 1) {
+                    const int mid = (bl + bh) >> 1;
+                    if (blk_pre[mid] <= rank) {
+                        bl = mid;
+                    } else {
+                        bh = mid;
+                    }
+                }
+                const int row = __ldcg(p.lin_rows + (int) ((long long) bl * p.m / nb) + (rank - blk_pre[bl]));
                 const int neu = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
+                list_row[j]   = row;
                 list_neu[j]   = neu;
                 list_bu[j]    = p.b_up ? __ldg(p.b_up + neu) : 0.f;
                 list_bg[j]    = p.b_gate ? __ldg(p.b_gate + neu) : 0.f;
@@ -355,40 +441,70 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             list_ready = true;
         }
         LAYER_STAMP(2);
-
-        // ---- retire item q (in order): cross-warp sums in a fixed order + the epilogue of its kind
-        auto retire = [&](int q) {
-            const int      s   = q % N;
-            const unsigned ph  = (unsigned) (q / N) & 1u;
+        for (;;) {
+            const int rc = issue_next();
+            if (rc < 0) {
+                break;
+            }
+            if (rc == 0) {
+                __nanosleep(64);
+            }
+        }
+        LAYER_STAMP(5);
+    } else if (warp == NW + 1) {
+        // ================================================== epilogue warp ==================================================
+        for (int i = lane; i < rb - ra; i += 32) {
+            bpu_s[i] = p.bpu ? __ldg(p.bpu + ra + i) : 0.f;
+        }
+        for (int i = lane; i < pb - pa; i += 32) {
+            bpd_s[i] = p.bpd ? __ldg(p.bpd + pa + i) : 0.f;
+        }
+        __syncwarp();
+        pdl_wait_prior_grid();
+        pdl_launch_dependents();
+        seq                = spif_comm_call_seq(p.comm);
+        const uint32_t par = seq & 1u;
+        int            pend_tail = 0, gu_retired = 0, n_nonzero = 0, cnt_out = 0;
+        int            s = 0, q = 0;
+        unsigned       ph = 0;
+        for (;; ++q) {
             mbar_wait(&done[s], ph);
+            ITEM_STAMP(q, 3, 0);
             const int4    d  = desc[s];
-            const float * ps = part + s * 64;
-            if (d.x == IT_WPU2 || d.x == IT_GU) {
-                const float a0 = (lane < NW) ? ps[lane] : 0.f;
-                const float a1 = (lane < NW) ? ps[32 + lane] : 0.f;
-                const float k  = reduce2(a0, a1, lane);
-                const float s0 = __shfl_sync(0xffffffffu, k, 0), s1 = __shfl_sync(0xffffffffu, k, 16);
-                if (d.x == IT_WPU2) {
+            const float * ps = part + s * 128;
+            if (d.x == IT_END) {
+                break;
+            }
+            if (d.x == IT_WPU || d.x == IT_GU) {
+                float k;
+                if (RPS == 4) {
+                    const float a0 = (lane < NW) ? ps[lane] : 0.f, a1 = (lane < NW) ? ps[32 + lane] : 0.f;
+                    const float a2 = (lane < NW) ? ps[64 + lane] : 0.f, a3 = (lane < NW) ? ps[96 + lane] : 0.f;
+                    k              = reduce4(a0, a1, a2, a3, lane);  // lanes [8j, 8j+8): row j
+                } else {
+                    const float a0 = (lane < NW) ? ps[lane] : 0.f, a1 = (lane < NW) ? ps[32 + lane] : 0.f;
+                    k              = reduce2(a0, a1, lane);          // lanes [16j, 16j+16): row j
+                }
+                constexpr int LPR = 32 / RPS;  // lanes per row sum
+                if (d.x == IT_WPU) {
                     // h1[row] = relu(Wpu[row] . x + bpu[row])  (llama-graph.cpp:871-880), published to every shard
-                    if (lane < d.z) {
-                        const int   row = d.y + lane;
-                        float       z   = (lane == 0 ? s0 : s1) + bpu_s[row - ra];
-                        z               = (z > 0.f) ? z : 0.f;
+                    const int j = lane / LPR;
+                    if ((lane % LPR) == 0 && j < d.z) {
+                        const int row = d.y + j;
+                        float     z   = k + bpu_s[row - ra];
+                        z             = (z > 0.f) ? z : 0.f;
                         const size_t off = ((size_t) par * world + p.comm.rank) * p.comm.cap + h1_off + row;
                         for (int r = 0; r < world; ++r) {
                             st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
                         }
                     }
                 } else {
-                    --gu_inflight;
-                    const int nn = d.z;
-                    for (int j = 0; j < nn; ++j) {  // gated: one neuron (u, g); ungated: up to two neurons (u0, u1)
-                        const int i   = d.y + j;
-                        float     u   = (gated || j == 0) ? s0 : s1;
-                        float     g   = gated ? s1 : 0.f;
-                        u += list_bu[i];
-                        g += list_bg[i];
-                        float h = spif_activation(p.arch, g, u);
+                    // gated: slot rows (up_0, gate_0, up_1, gate_1); ungated: (up_0 .. up_{RPS-1})
+                    for (int j = 0; j < d.z; ++j) {
+                        const int   i = d.y + j;
+                        const float u = __shfl_sync(0xffffffffu, k, (gated ? 2 * j : j) * LPR) + list_bu[i];
+                        const float g = gated ? __shfl_sync(0xffffffffu, k, (2 * j + 1) * LPR) + list_bg[i] : 0.f;
+                        float       h = spif_activation(p.arch, g, u);
                         if (lane == 0 && p.hidden_out) {
                             p.hidden_out[list_neu[i]] = h;
                         }
@@ -404,20 +520,27 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                             ++n_nonzero;
                         }
                     }
-                    __syncwarp();
+                    ++gu_retired;
+                    if (lane == 0) {
+                        __threadfence_block();
+                        st_volatile_s32(ctl + 0, pend_tail);
+                        __threadfence_block();
+                        st_volatile_s32(ctl + 1, gu_retired);
+                    }
                 }
-            } else if (d.x == IT_WPD2) {
-                const int row0 = d.y, n0 = d.z, n = d.z + d.w;
+            } else if (d.x == IT_WPD) {
+                const int row0 = d.y, n = d.z;
                 for (int base = 0; base < n; base += 32) {
                     const int  idx   = base + lane;
                     const bool valid = idx < n;
                     float      z     = 0.f;
                     if (valid) {
-                        const int     half = idx >= n0 ? 1 : 0;
-                        const int     rho  = idx - half * n0;
-                        const float * pp   = ps + half * 32 + rho * p.WR;
-                        for (int j = 0; j < p.WR; ++j) {  // fixed order
-                            z += pp[j];
+                        // Wpd row idx of the item lives in slot row j = idx / RP; its 32-vector groups are g0 .. g0 + WR - 1
+                        // of that slot row; group g was reduced by consumer warp g % NW for its vector k = g / NW
+                        const int j = idx / p.RP, g0 = (idx - j * p.RP) * p.WR;
+                        for (int t = 0; t < p.WR; ++t) {  // fixed order
+                            const int g = g0 + t, k = g / NW, w = g - k * NW;
+                            z += ps[(j * VPT + k) * 32 + w];
                         }
                         z += bpd_s[row0 - pa + idx];
                     }
@@ -440,35 +563,22 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             } else if (d.x == IT_FLUSH) {
                 // every consumer thread has stored its slice of the partial y and fenced; publish the count
                 if (lane == 0) {
-                    p.cta_stats[c * 2 + 0] = total_active;
+                    p.cta_stats[c * 2 + 0] = d.y;
                     p.cta_stats[c * 2 + 1] = n_nonzero;
                     __threadfence();
                     atomicAdd(p.comm.seq + 3, 1u);
                 }
                 LAYER_STAMP(4);
             }
-        };
-
-        bool first_gu = true;
-        while (!ended) {
-            while (q_issue - q_done < N && !ended) {
-                if (!issue_next()) {
-                    break;
-                }
-                if (first_gu && gu_inflight > 0) {
-                    first_gu = false;
-                    LAYER_STAMP(3);
-                }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&freeb[s]);
             }
-            if (ended) {
-                break;
-            }
-            if (q_done < q_issue) {
-                retire(q_done);
-                ++q_done;
+            if (++s == N) {
+                s = 0;
+                ph ^= 1u;
             }
         }
-        LAYER_STAMP(5);
         // ---- the next layer's active-row list: this block's rows in ascending order + its count
         if (p.has_pred && p.lout_cnt) {
             __syncwarp();
@@ -494,10 +604,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         pdl_wait_prior_grid();
         pdl_launch_dependents();
         seq = spif_comm_call_seq(p.comm);
+        bool vok[VPT];
 #pragma unroll
         for (int k = 0; k < VPT; ++k) {
             const int v = tid + k * NC;
-            if (v < p.V) {
+            vok[k]      = v < p.V;
+            if (vok[k]) {
                 const float4 a = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v);
                 const float4 b = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v + 1);
                 xr[k * 8 + 0] = a.x, xr[k * 8 + 1] = a.y, xr[k * 8 + 2] = a.z, xr[k * 8 + 3] = a.w;
@@ -510,86 +622,99 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                 }
             }
         }
-        bool h1_loaded = false;
-        int  s = 0;
-        unsigned ph = 0;
-        bool first = true;
-        for (;;) {
+        const uint32_t ring_s  = smem_u32(ring) + (uint32_t) tid * 16u;  // my first vector of slot 0, row 0
+        const uint32_t koff    = (uint32_t) NC * 16u;                    // my next vector (VPT == 2)
+        const uint32_t rbytes  = (uint32_t) p.row_bytes;
+        bool           h1_loaded = false;
+        int            s = 0, qc = 0;
+        unsigned       ph = 0;
+        uint32_t       slot_s = ring_s;
+        for (;; ++qc) {
             mbar_wait(&full[s], ph);
-            if (first) {
-                first = false;
-                if (warp == 0) {
+            if (warp == 0) {
+                if (qc == 0) {
                     LAYER_STAMP(8);
                 }
+                ITEM_STAMP(qc, 2, 0);
             }
-            const int4            d    = desc[s];
-            const unsigned char * slot = ring + (size_t) s * slot_bytes;
-            if (d.x == IT_END) {
-                break;
-            }
-            if (d.x == IT_WPU2 || d.x == IT_GU) {
-                float a = 0.f, b = 0.f;
+            const int4 d = desc[s];
+            float *    pw = part + s * 128 + warp;
+            if (d.x == IT_WPU || d.x == IT_GU) {
+                float v[RPS];
+#pragma unroll
+                for (int r = 0; r < RPS; ++r) {
+                    v[r] = 0.f;
+                }
 #pragma unroll
                 for (int k = 0; k < VPT; ++k) {
-                    const int v = tid + k * NC;
-                    if (v < p.V) {
-                        float w[8];
-                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+                    if (vok[k]) {
+                        uint4 w[RPS];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            a = fmaf(w[e], xr[k * 8 + e], a);
+                        for (int r = 0; r < RPS; ++r) {
+                            w[r] = lds128(slot_s + r * rbytes + k * koff);
                         }
-                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            b = fmaf(w[e], xr[k * 8 + e], b);
+                        for (int r = 0; r < RPS; ++r) {
+                            v[r] += dot8<WT>(w[r], xr + k * 8);
                         }
                     }
                 }
-                const bool two = (d.x == IT_GU) ? (gated || d.z == 2) : (d.z == 2);
-                b              = two ? b : 0.f;  // the second half of the slot was not loaded
-                const float k2 = reduce2(a, b, lane);
-                if ((lane & 15) == 0) {
-                    part[s * 64 + (lane >> 4) * 32 + warp] = k2;
+                // rows that were not loaded hold stale bytes: their sums are never read by the epilogue (NaN bits stay in
+                // their own lane group of the packed tree)
+                float k2;
+                if (RPS == 4) {
+                    k2 = reduce4(v[0], v[1], v[2], v[3], lane);
+                    if ((lane & 7) == 0) {
+                        pw[(lane >> 3) * 32] = k2;
+                    }
+                } else {
+                    k2 = reduce2(v[0], v[1], lane);
+                    if ((lane & 15) == 0) {
+                        pw[(lane >> 4) * 32] = k2;
+                    }
                 }
-            } else if (d.x == IT_DN2) {
-                const float al0 = dalpha[s * 2], al1 = (d.y == 2) ? dalpha[s * 2 + 1] : 0.f;
+            } else if (d.x == IT_DN) {
+                const float4 al = *reinterpret_cast<const float4 *>(dalpha + s * 4);
+                const float  alv[4] = { al.x, al.y, al.z, al.w };
 #pragma unroll
                 for (int k = 0; k < VPT; ++k) {
-                    const int v = tid + k * NC;
-                    if (v < p.V) {
-                        float w[8];
-                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+                    if (vok[k]) {
+                        uint4 w[RPS];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            acc[k * 8 + e] = fmaf(w[e], al0, acc[k * 8 + e]);
+                        for (int r = 0; r < RPS; ++r) {
+                            w[r] = lds128(slot_s + r * rbytes + k * koff);
                         }
-                        if (d.y == 2) {
-                            unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                acc[k * 8 + e] = fmaf(w[e], al1, acc[k * 8 + e]);
+                        for (int r = 0; r < RPS; ++r) {
+                            if (r < d.y) {  // uniform: ascending neuron order, a fixed FMA chain per element
+                                float f[8];
+                                unpack8<WT>(w[r], f);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    acc[k * 8 + e] = fmaf(f[e], alv[r], acc[k * 8 + e]);
+                                }
                             }
                         }
                     }
                 }
-            } else if (d.x == IT_WPD2) {
+            } else if (d.x == IT_WPD) {
                 if (!h1_loaded) {
                     // the hidden vector of the predictor: {value, seq} words, complete once every CTA (of every shard) has
-                    // retired its Wpu rows -- they were first in everybody's queue
-                    h1_loaded          = true;
-                    const uint32_t par = seq & 1u;
-#pragma unroll
-                    for (int k = 0; k < VPT; ++k) {
-                        const int v = tid + k * NC;
-                        if (v < p.V) {
-                            const int     col   = v % p.Vr;
-                            const int     owner = (col * 8) / (p.r / world);
-                            const uint2 * src   = p.comm.data[p.comm.rank] + ((size_t) par * world + owner) * p.comm.cap + h1_off + col * 8;
+                    // retired its Wpu rows -- they were first in everybody's queue.  ONE warp polls (all threads polling
+                    // floods the L2 with 95 K spinning loads and starves the producers' stores: 100 us per launch), the
+                    // values go through shared memory.
+                    h1_loaded = true;
+                    if (warp == 0) {
+                        const uint32_t par = seq & 1u;
+                        const int      rw  = p.r / world;  // rows per owner rank
+                        unsigned       spins = 0;
+                        for (int base = 0; base < p.r; base += 256) {  // 8 words per lane per pass
+                            const int     row   = base + lane * 8;
+                            const int     owner = row / rw;
+                            const uint2 * src   = p.comm.data[p.comm.rank] + ((size_t) par * world + owner) * p.comm.cap + h1_off + row;
                             uint2         w8[8];
-                            bool          ok    = false;
-                            unsigned      spins = 0;
-                            while (!ok) {
+                            bool          ok = false;
+                            while (true) {
 #pragma unroll
                                 for (int e = 0; e < 8; e += 2) {
                                     ld_word2_sys(src + e, w8[e], w8[e + 1]);
@@ -599,20 +724,32 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                                 for (int e = 0; e < 8; ++e) {
                                     ok = ok && (w8[e].y == seq);
                                 }
-                                if (++spins > SPIF_COMM_SPIN_LIMIT) {
+                                if (__all_sync(0xffffffffu, ok) || ++spins > SPIF_COMM_SPIN_LIMIT) {
                                     break;
                                 }
+                                __nanosleep(100);
                             }
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                float hv = ok ? __uint_as_float(w8[e].x) : __uint_as_float(0x7fc00000u);
+                                h1_s[row + e] = ok ? __uint_as_float(w8[e].x) : __uint_as_float(0x7fc00000u);
+                            }
+                            if (!ok) {
+                                atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
+                            }
+                        }
+                    }
+                    named_bar_sync(2, NC);
+#pragma unroll
+                    for (int k = 0; k < VPT; ++k) {
+                        if (vok[k]) {
+                            const int col = (tid + k * NC) % p.Vr;
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                float hv = h1_s[col * 8 + e];
                                 if (p.pflags & SPIF_FLAG_CPU_ROUNDING) {
                                     hv = round_through<WT>(hv);
                                 }
                                 hr[k * 8 + e] = hv;
-                            }
-                            if (!ok) {
-                                atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
                             }
                         }
                     }
@@ -620,37 +757,38 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                         LAYER_STAMP(9);
                     }
                 }
+                // slot row r holds RP rows of Wpd back to back; my vector k of that slot row belongs to one of them (the same
+                // one for the whole warp): RPS * VPT partial dots per item, one per (slot row, vector)
+                float v[RPS * VPT];
 #pragma unroll
                 for (int k = 0; k < VPT; ++k) {
-                    const int v = tid + k * NC;
-                    float     a = 0.f, b = 0.f;
-                    if (v < p.V) {
-                        float w[8];
-                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + (size_t) v * 16), w);
+                    uint4 w[RPS];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            a = fmaf(w[e], hr[k * 8 + e], a);
-                        }
-                        unpack8<WT>(*reinterpret_cast<const uint4 *>(slot + p.row_bytes + (size_t) v * 16), w);
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            b = fmaf(w[e], hr[k * 8 + e], b);
-                        }
+                    for (int r = 0; r < RPS; ++r) {
+                        w[r] = vok[k] ? lds128(slot_s + r * rbytes + k * koff) : make_uint4(0u, 0u, 0u, 0u);
                     }
-                    b              = (d.w > 0) ? b : 0.f;
-                    const float k2 = reduce2(a, b, lane);
-                    const int   g  = warp + k * NW;  // 32-vector group of the slot half
-                    if ((lane & 15) == 0 && g < 32) {
-                        part[s * 64 + (lane >> 4) * 32 + g] = k2;
+#pragma unroll
+                    for (int r = 0; r < RPS; ++r) {
+                        v[r * VPT + k] = dot8<WT>(w[r], hr + k * 8);
                     }
                 }
-            } else { /* IT_FLUSH: this CTA's partial y */
+                if (RPS * VPT == 4) {
+                    const float k2 = reduce4(v[0], v[1], v[2], v[3], lane);
+                    if ((lane & 7) == 0) {
+                        pw[(lane >> 3) * 32] = k2;
+                    }
+                } else {
+                    const float k2 = reduce2(v[0], v[1], lane);
+                    if ((lane & 15) == 0) {
+                        pw[(lane >> 4) * 32] = k2;
+                    }
+                }
+            } else if (d.x == IT_FLUSH) { /* this CTA's partial y */
                 float * prt = p.partials + (size_t) c * p.n_embd;
 #pragma unroll
                 for (int k = 0; k < VPT; ++k) {
-                    const int v = tid + k * NC;
-                    if (v < p.V) {
-                        float4 * o = reinterpret_cast<float4 *>(prt) + 2 * v;
+                    if (vok[k]) {
+                        float4 * o = reinterpret_cast<float4 *>(prt) + 2 * (tid + k * NC);
                         __stcg(o, make_float4(acc[k * 8 + 0], acc[k * 8 + 1], acc[k * 8 + 2], acc[k * 8 + 3]));
                         __stcg(o + 1, make_float4(acc[k * 8 + 4], acc[k * 8 + 5], acc[k * 8 + 6], acc[k * 8 + 7]));
                     }
@@ -661,9 +799,14 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             if (lane == 0) {
                 mbar_arrive(&done[s]);
             }
+            if (d.x == IT_END) {
+                break;
+            }
+            slot_s += (uint32_t) slot_bytes;
             if (++s == N) {
                 s = 0;
                 ph ^= 1u;
+                slot_s = ring_s;
             }
         }
         if (warp == 0) {
@@ -811,9 +954,9 @@ int spif_launch_mask_to_list(const float * mask, int m, float thr, void * list, 
 // ---------------------------------------------------------------------------------------------------------------
 extern unsigned long long * g_spif_trace;
 
-template <typename WT, int VPT, int MAXT>
+template <typename WT, int VPT, int RPS, int MAXT>
 static int launch_layer_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
-    auto kern = spif_layer_kernel<WT, VPT, MAXT>;
+    auto kern = spif_layer_kernel<WT, VPT, RPS, MAXT>;
     static unsigned long long done = 0;  // per instantiation: bit per device
     const unsigned long long  bit  = 1ull << (device & 63);
     if (!(done & bit)) {
@@ -848,7 +991,7 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         return rc;
     }
     const int P = ctx.sm_count;
-    SPIF_REQUIRE(P >= 1 && P <= SPIF_LIST_MAX_BLOCKS, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE(P >= 1 && P <= 256, SPIF_E_UNSUPPORTED);  // block counts of a list: 8 per lane of the producer warp
     int type = 0, n_embd = 0;
     const float * x = nullptr;
     if (ffn) {
@@ -883,15 +1026,17 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     SPIF_REQUIRE((n_embd / 4 + P - 1) / P <= 16, SPIF_E_UNSUPPORTED);  // column slice of the final sum
     SPIF_REQUIRE(kp.comm.cap >= n_embd + (pv ? pv->r : 0), SPIF_E_WORKSPACE);
 
-    const int vpt = (V <= 992) ? 1 : 2;
+    const int vpt = (V <= 960) ? 1 : 2;
     kp.nw         = (V + 32 * vpt - 1) / (32 * vpt);
     SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);  // n_embd >= 512: the final column-sliced sum uses 64 threads
-    const int threads = (kp.nw + 1) * 32;
+    const int threads = (kp.nw + 2) * 32;  // consumers + TMA issuer + epilogue
     kp.n_embd     = n_embd;
     kp.V          = V;
     kp.row_bytes  = n_embd * 2;
     kp.x          = x;
     kp.trace      = g_spif_trace;
+    static const int k_hint = [] { const char * e = getenv("SPIF_LAYER_L2_HINT"); return e ? atoi(e) : 0; }();
+    kp.l2_hint    = k_hint;
     if (ffn) {
         kp.has_ffn    = 1;
         kp.w_up       = (const unsigned char *) ffn->w_up;
@@ -909,7 +1054,6 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.arch       = ffn->arch;
         kp.flags      = ffn->flags;
         const int32_t * lh = (const int32_t *) list_in;
-        kp.lin_nblk   = P;  // lists on a device are always built with one block per SM
         kp.lin_cnt    = lh + SPIF_LIST_HDR;
         kp.lin_rows   = lh + SPIF_LIST_HDR + SPIF_LIST_MAX_BLOCKS;
         const size_t part_bytes = sizeof(float) * (size_t) P * n_embd;
@@ -951,29 +1095,36 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.cap_pd = 1, kp.cap_pu = 1;
         kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
     }
-    const int slot_bytes = 2 * kp.row_bytes;
+    kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
+    const int rps        = (vpt == 1 && kp.row_bytes <= 12288) ? 4 : 2;  // weight rows per ring slot
+    const int slot_bytes = rps * kp.row_bytes;
     int       nslots     = 12;
-    LayerSmem L          = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu);
+    LayerSmem L          = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P);
     while (nslots > 3 && L.total > (uint32_t) ctx.max_smem_optin) {
         --nslots;
-        L = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu);
+        L = layer_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P);
     }
     SPIF_REQUIRE(L.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
     // the final column-sliced sum reuses the ring as scratch: [(G + 4) x 16] float4
     SPIF_REQUIRE((size_t) nslots * slot_bytes >= (size_t) (kp.nw * 2 + 4) * 16 * 16, SPIF_E_SHAPE);
+    SPIF_REQUIRE(!pv || rps * vpt * 32 >= 1, SPIF_E_SHAPE);
     kp.nslots = nslots;
     if (ffn && ffn->hidden_out) {
         SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
     }
     const bool f16 = type == SPIF_TYPE_F16;
-    if (vpt == 1 && threads <= 704) {
-        return f16 ? launch_layer_t<spif_f16, 1, 704>(kp, P, threads, L.total, ctx.device, ctx.stream) :
-                     launch_layer_t<spif_bf16, 1, 704>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    if (vpt == 2) {
+        return f16 ? launch_layer_t<spif_f16, 2, 2, 576>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 2, 2, 576>(kp, P, threads, L.total, ctx.device, ctx.stream);
     }
-    if (vpt == 1) {
-        return f16 ? launch_layer_t<spif_f16, 1, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
-                     launch_layer_t<spif_bf16, 1, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    if (rps == 2) {
+        return f16 ? launch_layer_t<spif_f16, 1, 2, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 1, 2, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);
     }
-    return f16 ? launch_layer_t<spif_f16, 2, 544>(kp, P, threads, L.total, ctx.device, ctx.stream) :
-                 launch_layer_t<spif_bf16, 2, 544>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    if (threads <= 704) {
+        return f16 ? launch_layer_t<spif_f16, 1, 4, 704>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 1, 4, 704>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    }
+    return f16 ? launch_layer_t<spif_f16, 1, 4, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                 launch_layer_t<spif_bf16, 1, 4, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);
 }

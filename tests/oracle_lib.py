@@ -234,6 +234,48 @@ class Ref:
         return y, up, gate, hid
 
 
+class RefCuda:
+    """the reference's own CUDA kernels for the path, compiled unmodified for sm_100 (oracle/_ref/libspif_refcuda.so, built by
+    oracle/Makefile from /root/reference).  GPU baseline of bench.py and a third, reported comparison; never the product."""
+
+    PATH = os.path.join(ORACLE_DIR, "_ref", "libspif_refcuda.so")
+
+    @classmethod
+    def available(cls):
+        return os.path.exists(cls.PATH)
+
+    def __init__(self):
+        self.lib = ctypes.CDLL(self.PATH)
+        self.lib.spif_refcuda_describe.restype = ctypes.c_char_p
+        self._stack = self.lib.spif_refcuda_stack
+        self._stack.restype = c_i
+        self._stack.argtypes = [c_i, c_i, c_i, c_i] + [c_vp] * 9 + [c_i, c_i, c_i, c_i, c_i, c_i, c_vp]
+
+    def describe(self):
+        return self.lib.spif_refcuda_describe().decode()
+
+    def stack(self, arch, wtype, ptype, w_up, w_gate, w_down, wpu, wpd, bpd, x, y, p_io, n_embd, n_ff, r, with_pred=True,
+              warmup=3, iters=10):
+        """all tensors are torch CUDA tensors (lists per layer for the weights; x, y [L, n_embd], p_io [L, n_ff] float32).
+        -> (us per step through a CUDA graph, us per step eager)"""
+        nl = len(w_up)
+
+        def arr(lst):
+            if lst is None:
+                return None
+            a = (ctypes.c_void_p * nl)(*[ctypes.c_void_p(t.data_ptr()) for t in lst])
+            return a
+
+        keep = [arr(w_up), arr(w_gate), arr(w_down), arr(wpu), arr(wpd), arr(bpd)]
+        out = (ctypes.c_double * 2)()
+        rc = self._stack(arch, wtype, ptype, nl, *[ctypes.cast(k, c_vp) if k is not None else None for k in keep],
+                         ctypes.c_void_p(x.data_ptr()), ctypes.c_void_p(y.data_ptr()), ctypes.c_void_p(p_io.data_ptr()),
+                         n_embd, n_ff, r, 1 if with_pred else 0, warmup, iters, ctypes.cast(out, c_vp))
+        if rc != 0:
+            raise RuntimeError(f"spif_refcuda_stack failed: {rc}")
+        return float(out[0]), float(out[1])
+
+
 def stack_time(lib, arch, wtype, ptype, w_up, w_gate, w_down, wpu, wpd, bpd, x, n_embd, n_ff, r, n_tok,
                n_threads, warmup, iters, want_y=False):
     """time one decode step over a stack of layers on the CPU (lib = Oracle() or Ref()). returns (median_us, y|None)"""

@@ -100,7 +100,8 @@ def test_lookahead_predictor_only(oracle, ptype, n_embd, r, m):
     assert np.abs(z_gpu - z_ref[0]).max() < 1e-4 * max(1.0, np.abs(z_ref).max())
     flips = (p_gpu < 0.5) != (p_ref[0] < 0.5)
     assert np.all(np.abs(z_ref[0][flips]) < 1e-4), f"{flips.sum()} flips, worst |logit| {np.abs(z_ref[0][flips]).max()}"
-    assert np.abs(p_gpu - p_ref[0]).max() < 1e-5
+    # (a last-bit difference in an h1 element can cross a rounding boundary of the weight type: 2^-11 F16, 2^-8 BF16)
+    assert np.abs(p_gpu - p_ref[0]).max() < (1e-5 if ptype == F16 else 2e-4)
     # the list is bit-exact for the kernel's OWN sigmoid output (mask convention !(p < 0.5))
     assert lst.rows() == np.nonzero(~(p_gpu < 0.5))[0].tolist()
     assert comm.status() == 0

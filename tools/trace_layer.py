@@ -58,7 +58,7 @@ def main():
     torch.cuda.synchronize()
     print(f"graph replay: {e0.elapsed_time(e1) / 20 * 1e3 / L:.2f} us per layer ({L} layers + 1 predictor-only launch)")
     # traced eager steps: one trace buffer per launch (launch 0 = predictor only)
-    traces = [torch.zeros((P, 16), dtype=torch.int64, device=dev) for _ in range(L + 1)]
+    traces = [torch.zeros((P, 512), dtype=torch.int64, device=dev) for _ in range(L + 1)]
     for rep in range(a.reps):
         for t in traces:
             t.zero_()
@@ -87,6 +87,18 @@ def main():
         gap = "" if prev_end is None else f" gap_from_prev_end {(t0 - prev_end) / 1e3:5.2f}"
         print(f"launch {i}: total {(end - t0) / 1e3:6.2f} us start_spread {(t[:, 0].max() - t0) / 1e3:5.2f}{gap} | med/max since first CTA start: " + " | ".join(line))
         prev_end = end
+        if i in (0, 2, L):  # per-item timeline of the median CTA and CTA 0
+            names_t = {1: "WPU", 2: "GU", 3: "DN", 4: "WPD", 5: "FLUSH", 6: "END"}
+            for cta in (0, 77):
+                row = t[cta]
+                items = []
+                for q in range(120):
+                    ty = int(row[16 + 4 * q])
+                    if ty == 0:
+                        break
+                    iss, lnd, ret = [(row[16 + 4 * q + j] - row[15]) / 1965.0 if row[16 + 4 * q + j] > 0 else float("nan") for j in (1, 2, 3)]
+                    items.append(f"{names_t.get(ty, ty)}:{iss:.1f}/{lnd:.1f}/{ret:.1f}")
+                print(f"   cta {cta} items (issued/landed/retired, us since CTA entry at 1965 MHz): " + " ".join(items))
 
 
 if __name__ == "__main__":

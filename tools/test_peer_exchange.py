@@ -63,6 +63,76 @@ def main():
         assert err < 1e-5, err
     out["fused_layer_parity"] = "ok"
 
+    # ---- ONE comm, the three forms interleaved, odd call counts (the sequence number is per comm and per call,
+    # not per block, so launch shapes may differ from call to call)
+    T8 = 8
+    x8 = torch.randn((T8, E), device=dev, generator=g)
+    p8 = torch.where(torch.rand((T8, F), device=dev, generator=g) < 0.15, 0.9, 0.1).float()
+    ws8 = sp.Workspace(E, F, T8)
+    y8_full = sp.sparse_ffn(sp.ARCH_PROSPARSE, sp.GGML_TYPE_F16, up.view(torch.uint8), gate.view(torch.uint8),
+                            down.view(torch.uint8), x8, p8, F, ws=ws8)
+    mcomm = sp.ShardComm(T8 * E + 256, group, dev)
+    calls = 0
+    for it in range(5):
+        v = torch.randn(4 * 1280, device=dev, generator=torch.Generator(device=dev).manual_seed(500 + rank + it))
+        ref = v.clone()
+        dist.all_reduce(ref)
+        got = sp.shard_allreduce(v.clone(), mcomm)                                   # stand-alone form: 5 blocks
+        assert float((got - ref).abs().max() / ref.abs().max()) < 1e-6
+        calls += 1
+        y = sp.sparse_ffn(sp.ARCH_PROSPARSE, sp.GGML_TYPE_F16, sh(up), sh(gate), sh(down), x, p, F, neuron_idx=rows, ws=ws,
+                          comm=mcomm)                                                 # fused into the partial sum: n_tok = 1
+        assert float((y - y_full).abs().max() / y_full.abs().max()) < 1e-5
+        calls += 1
+        if it % 2 == 0:
+            y8 = sp.sparse_ffn(sp.ARCH_PROSPARSE, sp.GGML_TYPE_F16, sh(up), sh(gate), sh(down), x8, p8, F, neuron_idx=rows,
+                               ws=ws8, comm=mcomm)                                    # union GEMM + stand-alone form: n_tok = 8
+            assert float((y8 - y8_full).abs().max() / y8_full.abs().max()) < 2e-3     # x / hidden rounded to F16 there
+            calls += 1
+        # look-ahead layer kernel on the same comm: FFN on this rank's rows (list in row space) + exchange
+        lst = sp.mask_to_list(p[0, rows.long()].contiguous())
+        yl = torch.empty((E,), device=dev)
+        sp.sparse_ffn_lookahead(mcomm, ws, ffn=dict(arch=sp.ARCH_PROSPARSE, w_type=sp.GGML_TYPE_F16, up=sh(up), gate=sh(gate),
+                                                    down_t=sh(down), cur=x[0], n_ff=F, neuron_idx=rows, out=yl), list_in=lst)
+        assert float((yl - y_full[0]).abs().max() / y_full.abs().max()) < 1e-5
+        calls += 1
+    assert mcomm.status() == 0 and mcomm.epoch() == calls, (mcomm.status(), mcomm.epoch(), calls)
+    out["mixed_forms_one_comm"] = {"calls": calls, "status": 0}
+
+    # ---- sharded look-ahead chain: every rank computes r / world rows of the predictor's hidden vector and its own Wpd rows;
+    # the masks of all shards together == the unsharded predictor's mask, y == the unsharded layer
+    R = 256
+    wpu = torch.empty((R, E), dtype=torch.float16, device=dev).normal_(0, E ** -0.5, generator=g)
+    wpd = torch.empty((F, R), dtype=torch.float16, device=dev).normal_(0, R ** -0.5, generator=g)
+    bpd = torch.full((F,), -0.9, device=dev)
+    ccomm = sp.ShardComm(E + R, group, dev)
+    one = sp.ShardComm(E + R, None, dev)
+    p_full = torch.empty((F,), device=dev)
+    sp.sparse_ffn_lookahead(one, ws, pred=dict(pred_up=wpu.view(torch.uint8), pred_down=wpd.view(torch.uint8), pred_down_b=bpd,
+                                               cur=x[0], p_type=sp.GGML_TYPE_F16, r=R, m=F, out=p_full), list_out=sp.ActiveList(F))
+    y_un = sp.sparse_ffn(sp.ARCH_PROSPARSE, sp.GGML_TYPE_F16, up.view(torch.uint8), gate.view(torch.uint8),
+                         down.view(torch.uint8), x, p_full[None], F, ws=ws)
+    m_loc = rows.numel()
+    lists = [sp.ActiveList(m_loc, dev), sp.ActiveList(m_loc, dev)]
+    p_loc = torch.empty((m_loc,), device=dev)
+    yl = torch.empty((E,), device=dev)
+    pred = dict(pred_up=wpu.view(torch.uint8), pred_down=sh(wpd), pred_down_b=bpd[rows.long()].contiguous(), cur=x[0],
+                p_type=sp.GGML_TYPE_F16, r=R, m=m_loc, out=p_loc)
+    for it in range(3):
+        sp.sparse_ffn_lookahead(ccomm, ws, pred=pred, list_out=lists[0])
+        sp.sparse_ffn_lookahead(ccomm, ws, ffn=dict(arch=sp.ARCH_PROSPARSE, w_type=sp.GGML_TYPE_F16, up=sh(up), gate=sh(gate),
+                                                    down_t=sh(down), cur=x[0], n_ff=F, neuron_idx=rows, out=yl),
+                                pred=pred, list_in=lists[0], list_out=lists[1])
+        torch.cuda.synchronize()
+        flips = int(((p_loc < 0.5) != (p_full[rows.long()] < 0.5)).sum())
+        assert flips == 0 or float((p_loc - p_full[rows.long()]).abs().max()) < 1e-4, flips
+        assert float((yl - y_un[0]).abs().max() / y_un.abs().max()) < 1e-5
+        gathered = [torch.empty_like(yl) for _ in range(world)]
+        dist.all_gather(gathered, yl)
+        assert all(torch.equal(gathered[0], t) for t in gathered), "layer output differs between ranks"
+    assert ccomm.status() == 0
+    out["sharded_lookahead_chain"] = "ok"
+
     # ---- timing: 40 exchanges of a 13B-sized y per graph (one decode step's worth)
     n, reps = 5120, 40
     ys = [torch.randn(n, device=dev) for _ in range(reps)]

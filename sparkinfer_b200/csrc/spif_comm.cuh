@@ -15,7 +15,7 @@
 //
 // Local control words (comm.seq, uint32, zero-initialised by the caller):
 //   [0] epoch   [1] blocks that have finished the current call   [2] sticky error (SPIF_COMM_ERR_*)   [3] layer kernel:
-//   CTAs whose partial y is written   [4..7] reserved
+//   CTAs whose partial y is written   [4] layer kernel: CTAs whose predictor rows are sent (a hint)   [5..7] reserved
 // A peer that does not answer within the spin bound sets the error word, and the affected outputs are NaN: a wrong sum is
 // never returned silently.  spif_shard_comm_status() reads the error word.
 #pragma once
@@ -69,6 +69,7 @@ __device__ __forceinline__ void spif_comm_block_done(const spif_comm_dev & c, ui
     if (old == n_blocks - 1u) {
         c.seq[1] = 0u;
         c.seq[3] = 0u;
+        c.seq[4] = 0u;
         __threadfence();
         c.seq[0] = seq;
     }

@@ -72,6 +72,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity) {
         : "memory");
 }
 
+// the same without the suspend-time hint (default, short, system-dependent limit): for single waiting warps
+__device__ __forceinline__ void mbar_wait_spin(uint64_t * bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P1;\n\t"
+        "SPIF_WAITS_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra SPIF_WAITS_DONE;\n\t"
+        "bra SPIF_WAITS_LOOP;\n\t"
+        "SPIF_WAITS_DONE:\n\t"
+        "}" ::"r"(addr),
+        "r"(parity)
+        : "memory");
+}
+
 // non-blocking probe of a phase: true if the phase with this parity has completed
 __device__ __forceinline__ bool mbar_test(uint64_t * bar, uint32_t parity) {
     uint32_t ok;

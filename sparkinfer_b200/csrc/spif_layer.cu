@@ -74,13 +74,14 @@ struct LayerParams {
     float                 thr_next;           // threshold for the list of the next layer
     int                   arch, flags, pflags;
     int                   l2_hint;            // 1: TMA copies carry an L2 evict_first policy
+    int                   dbg;                // SPIF_LAYER_DEBUG bit 0: consumers skip the arithmetic (streaming floor; wrong results)
     spif_comm_dev         comm;
     unsigned long long *  trace;
 };
 
 struct LayerSmem {
     uint32_t ring, full, done, freeb, desc, dalpha, part, ctl, list_row, list_neu, list_bu, list_bg, pend_row, pend_alpha, bpu_s,
-        bpd_s, lout_s, h1_s, blk_pre, total;
+        bpd_s, lout_s, h1_s, blk_pre, hred, total;
 };
 
 __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int slot_bytes, int cap_ffn, int cap_pd, int cap_pu,
@@ -100,7 +101,7 @@ __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int sl
     L.desc       = take(16u * nslots, 16);
     L.dalpha     = take(16u * nslots, 16);
     L.part       = take(4u * 128 * nslots, 16);
-    L.ctl        = take(16u, 16);
+    L.ctl        = take(64u, 16);  // int[4] {pend_tail, gu items retired, -, -}, mbarrier h1 ready, mbarrier partial y stored
     L.list_row   = take(4u * cap_ffn, 4);
     L.list_neu   = take(4u * cap_ffn, 4);
     L.list_bu    = take(4u * cap_ffn, 4);
@@ -112,6 +113,7 @@ __host__ __device__ static inline LayerSmem layer_smem_layout(int nslots, int sl
     L.lout_s     = take(4u * cap_pd, 4);
     L.h1_s       = take(4u * r, 16);
     L.blk_pre    = take(4u * (nblk + 1), 4);
+    L.hred       = take(16u * 4 * 16, 16);  // helper warps' scratch of the column-sliced sum
     L.total      = (o + 127) / 128 * 128;
     return L;
 }
@@ -184,7 +186,155 @@ template <typename WT> __device__ __forceinline__ float dot8(const uint4 & wv, c
     return s0 + s1;
 }
 
-// Warp roles: [0, NW) consumers, NW = TMA issuer, NW + 1 = epilogue.  RPS = weight rows per ring slot (one queue item).
+// floor(a * b / d) for a * b < 2^32 (checked by the launcher).  A 64-bit division is a ~100-instruction dependent chain: six of
+// them at kernel entry cost 1.4 us before the first TMA copy was issued (profiles/r2_layer_trace.txt, v2).
+__device__ __forceinline__ int share(int a, int b, int d) {
+    return (int) ((unsigned) a * (unsigned) b / (unsigned) d);
+}
+
+// D: y[columns of this CTA] = sum over all CTAs of their partial y (+ b_down) [+ sum over the shards].  The SHAPE of the sum does
+// not depend on who executes it: G virtual groups, group g adds the partials of CTAs g, g + G, g + 2G, ... in ascending order;
+// quarter j adds its groups [j*G/4, (j+1)*G/4) in ascending order; the four quarters are added in order.  WIDE: 16 * G threads,
+// one group each (one L2 round trip; scratch [(G + 4)][16] float4).  !WIDE: 64 threads, one quarter each in registers (scratch
+// [4][16] float4) -- slower, but it runs in the shadow of the predictor stream.  Both give the same bits.
+__device__ __forceinline__ float4 layer_group_sum(const float4 * base, int g, int G, int P, int n4) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int pp0 = g; pp0 < P; pp0 += 4 * G) {
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int pp = pp0 + q * G;
+            v[q]         = (pp < P) ? __ldcg(base + (size_t) pp * n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            s.x += v[q].x, s.y += v[q].y, s.z += v[q].z, s.w += v[q].w;
+        }
+    }
+    return s;
+}
+
+// out of line: its 8 x 4 words in flight must not set the register budget of the streaming loops
+__device__ __noinline__ float4 layer_allreduce_f4(const spif_comm_dev & c, uint32_t seq, float4 v, int idx4, bool has_value) {
+    return spif_peer_allreduce_f4(c, seq, v, idx4, has_value);
+}
+
+template <bool WIDE>
+__device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t, int nthr, int bar_id, float4 * scratch,
+                                                   uint32_t seq, int G) {
+    const int P = gridDim.x, c = blockIdx.x, lane = t & 31;
+    if (t == 0) {  // every CTA has published its partial y
+        unsigned spins = 0;
+        while (ld_u32_acquire_gpu(p.comm.seq + 3) < (unsigned) P) {
+            if (++spins > SPIF_COMM_SPIN_LIMIT) {
+                atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
+                break;
+            }
+            if (!WIDE) {
+                __nanosleep(200);
+            }
+        }
+    }
+    named_bar_sync(bar_id, nthr);
+    if (t < 32) {
+        LAYER_STAMP(11);
+    }
+    const int      n4 = p.n_embd >> 2;
+    const int      c0 = share(c, n4, P), c1 = share(c + 1, n4, P);
+    const int      ncol = c1 - c0;  // <= 16 (checked by the launcher)
+    const int      col  = t & 15;
+    const float4 * base = reinterpret_cast<const float4 *>(p.partials) + c0 + col;
+    float4 *       red2;
+    if (WIDE) {
+        const int pg   = t >> 4;
+        float4 *  red  = scratch;                 // [G][16]
+        red2           = red + (size_t) G * 16;   // [4][16]
+        red[pg * 16 + col] = (col < ncol) ? layer_group_sum(base, pg, G, P, n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        named_bar_sync(bar_id, nthr);
+        if (t < 64) {
+            const int j = t >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
+            float4    a = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int g = lo; g < hi; ++g) {
+                const float4 v = red[g * 16 + col];
+                a.x += v.x, a.y += v.y, a.z += v.z, a.w += v.w;
+            }
+            red2[j * 16 + col] = a;
+        }
+    } else {
+        const int j = t >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
+        red2        = scratch;
+        float4 a    = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (col < ncol && 4 * G >= P) {  // two groups = 8 loads in flight per thread (same order of additions as below)
+            for (int g = lo; g < hi; g += 2) {
+                const bool two = g + 1 < hi;
+                float4     v[8];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int pp = g + q * G;
+                    v[q]         = (pp < P) ? __ldcg(base + (size_t) pp * n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    v[4 + q]     = (two && pp + 1 < P) ? __ldcg(base + (size_t) (pp + 1) * n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    s0.x += v[q].x, s0.y += v[q].y, s0.z += v[q].z, s0.w += v[q].w;
+                    s1.x += v[4 + q].x, s1.y += v[4 + q].y, s1.z += v[4 + q].z, s1.w += v[4 + q].w;
+                }
+                a.x += s0.x, a.y += s0.y, a.z += s0.z, a.w += s0.w;
+                if (two) {
+                    a.x += s1.x, a.y += s1.y, a.z += s1.z, a.w += s1.w;
+                }
+            }
+        } else if (col < ncol) {
+            for (int g = lo; g < hi; ++g) {
+                const float4 v = layer_group_sum(base, g, G, P, n4);
+                a.x += v.x, a.y += v.y, a.z += v.z, a.w += v.w;
+            }
+        }
+        red2[j * 16 + col] = a;
+    }
+    named_bar_sync(bar_id, nthr);
+    if (t < 16) {
+        const bool own = col < ncol;
+        float4     a   = red2[col];
+#pragma unroll
+        for (int j = 1; j < 4; ++j) {
+            const float4 v = red2[j * 16 + col];
+            a.x += v.x, a.y += v.y, a.z += v.z, a.w += v.w;
+        }
+        if (own && p.b_down) {
+            const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0 + col);
+            a.x += bb.x, a.y += bb.y, a.z += bb.z, a.w += bb.w;
+        }
+        a = layer_allreduce_f4(p.comm, seq, a, c0 + col, own);
+        if (own) {
+            reinterpret_cast<float4 *>(p.y)[c0 + col] = a;
+        }
+    }
+    if (c == 0 && (t >> 5) == 1 && p.stats_out) {
+        int nz = 0;
+        for (int q = lane; q < P; q += 32) {
+            nz += __ldcg(p.cta_stats + q * 2 + 1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            nz += __shfl_xor_sync(0xffffffffu, nz, o);
+        }
+        if (lane == 0) {
+            p.stats_out[0] = __ldcg(p.cta_stats + 0);
+            p.stats_out[1] = nz;
+            p.stats_out[2] = 0;
+            p.stats_out[3] = 0;
+        }
+    }
+    if (t < 32) {
+        LAYER_STAMP(12);
+    }
+}
+
+#define SPIF_LAYER_HELPER_WARPS 2
+
+// Warp roles: [0, NW) consumers, NW = TMA issuer, NW + 1 = epilogue, NW + 2 .. NW + 3 = helpers.  RPS = weight rows per ring slot (one queue item).
 //   issuer    waits for a free slot, decides what goes in (pending W_down^T rows first, then the static stream Wpu -> gate/up ->
 //             Wpd), issues the bulk copies.  Nothing else: a single warp executes ~1 dependent instruction per 5 cycles, so the
 //             first version (issue + retire in one warp, ~1 us per item) capped the SM at 20 GB/s (profiles/r2_layer_trace.txt).
@@ -192,8 +342,11 @@ template <typename WT> __device__ __forceinline__ float dot8(const uint4 & wv, c
 //             shuffle tree -> per-warp partials in shared memory -> arrive on done[slot].
 //   epilogue  retires items in order: cross-warp sums (fixed order), bias / activation / sigmoid / list compaction, pushes
 //             W_down^T rows of non-zero hidden values to the issuer's queue, frees the slot.
+//   helpers   everything that waits on OTHER CTAs, off the streaming path: poll the predictor's hidden vector (words from every
+//             CTA of every shard) into shared memory; publish this CTA's partial y (fence + counter); when a predictor stream
+//             is still running, the column-sliced sum over all CTAs' partial y [+ the shard exchange] in its shadow.
 template <typename WT, int VPT, int RPS, int MAXT>
-__global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p) {
+__global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const __grid_constant__ LayerParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NW = p.nw, NC = NW * 32;
@@ -210,6 +363,11 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
     float *         dalpha     = reinterpret_cast<float *>(smem + L.dalpha);  // [N][4]
     float *         part       = reinterpret_cast<float *>(smem + L.part);    // [N][4][32]
     int *           ctl        = reinterpret_cast<int *>(smem + L.ctl);       // [0] pend_tail, [1] gu items retired
+    uint64_t *      h1bar      = reinterpret_cast<uint64_t *>(smem + L.ctl + 16);
+    uint64_t *      flushbar   = reinterpret_cast<uint64_t *>(smem + L.ctl + 24);
+    uint64_t *      listbar    = reinterpret_cast<uint64_t *>(smem + L.ctl + 32);
+    int *           dbgflag    = reinterpret_cast<int *>(smem + L.ctl + 40);
+    float4 *        hred       = reinterpret_cast<float4 *>(smem + L.hred);
     int *           list_row   = reinterpret_cast<int *>(smem + L.list_row);
     int *           list_neu   = reinterpret_cast<int *>(smem + L.list_neu);
     float *         list_bu    = reinterpret_cast<float *>(smem + L.list_bu);
@@ -225,6 +383,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
     if (tid == 0) {
         if (p.trace) {
             p.trace[(size_t) blockIdx.x * 512 + 15] = (unsigned long long) clock64();
+            LAYER_STAMP(7);
         }
         for (int s = 0; s < N; ++s) {
             mbar_init(&full[s], 1);
@@ -232,6 +391,10 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             mbar_init(&freeb[s], 1);
         }
         ctl[0] = 0, ctl[1] = 0;
+        dbgflag[0] = 0;
+        mbar_init(h1bar, 32);
+        mbar_init(flushbar, 1);
+        mbar_init(listbar, 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -245,11 +408,11 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
     // my shares of the dense predictor matrices (weights: independent of the previous kernel)
     int ra = 0, rb = 0, pa = 0, pb = 0;
     if (p.has_pred) {
-        const int R0 = (int) ((long long) p.comm.rank * p.r / world), R1 = (int) ((long long) (p.comm.rank + 1) * p.r / world);
-        ra = R0 + (int) ((long long) c * (R1 - R0) / P);
-        rb = R0 + (int) ((long long) (c + 1) * (R1 - R0) / P);
-        pa = (int) ((long long) c * p.pm / P);
-        pb = (int) ((long long) (c + 1) * p.pm / P);
+        const int rw = p.r / world, R0 = p.comm.rank * rw;  // r % world == 0 (launcher)
+        ra = R0 + share(c, rw, P);
+        rb = R0 + share(c + 1, rw, P);
+        pa = share(c, p.pm, P);
+        pb = share(c + 1, p.pm, P);
     }
     const int neu_per_gu = gated ? RPS / 2 : RPS;  // neurons per gate/up item
 
@@ -274,6 +437,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         // returns 1 if an item was issued, 0 if nothing can be issued right now, -1 after END
         auto issue_next = [&]() -> int {
             int gu_ret = 0, np = 0;
+            if (!list_ready && mbar_test(listbar, 0)) {  // the helper warp has built this CTA's row list
+                list_ready   = true;
+                b_end        = ctl[2];
+                total_active = ctl[3];
+                LAYER_STAMP(2);
+            }
             if (p.has_ffn) {
                 gu_ret = ld_volatile_s32(ctl + 1);
                 __threadfence_block();
@@ -286,21 +455,19 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                 type = IT_DN;
             } else if (a_next < rb) {
                 type = IT_WPU;
-            } else if (!list_ready) {
-                return 0;
-            } else if (b_next < b_end) {
-                type = IT_GU;
-            } else if (p.has_ffn && !flushed && gu_all_done && np == 0) {
+            } else if (list_ready && b_next < b_end) {
+                type = IT_GU;  // the head of the longest dependency chain (gate/up -> hidden -> W_down^T -> partial y -> sum)
+            } else if (p.has_ffn && list_ready && !flushed && gu_all_done && np == 0) {
                 type = IT_FLUSH;
-            } else if (c_next < pb) {
-                type = IT_WPD;
+            } else if (c_next < pb && list_ready) {
+                type = IT_WPD;  // dense, known at entry, needs only h1 (a helper warp collects it meanwhile)
             } else if (flushed || !p.has_ffn) {
                 type = IT_END;
             } else {
                 return 0;  // gate/up items still in flight: their W_down^T rows may follow
             }
             if (q >= N) {
-                mbar_wait(&freeb[s], fph);
+                mbar_wait_spin(&freeb[s], fph);
             }
             unsigned char * dst = ring + (size_t) s * slot_bytes;
             if (lane == 0) {
@@ -372,7 +539,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             return type == IT_END ? -1 : 1;
         };
 
-        // ---- before the programmatic-dependent-launch wait: the predictor up-projection rows are already on their way
+        // ---- before the programmatic-dependent-launch wait: the predictor up-projection rows are already on their way.
+        // (Not the Wpd rows: consumers take items in order, a Wpd item ahead of the gate/up items makes those wait for h1; and
+        // the TMA unit accepts ~80 KB of outstanding copies, then the issuing thread blocks -- v3 trace, profiles/.)
         while (q < N && a_next < rb) {
             issue_next();
         }
@@ -381,66 +550,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         pdl_launch_dependents();
         LAYER_STAMP(1);
 
-        // ---- my share of this layer's active rows: ranks [c*A/P, (c+1)*A/P) of the concatenated block lists
-        if (p.has_ffn) {
-            // lane L owns blocks [L*kb, (L+1)*kb): all counts are requested at once (one L2 round trip), one warp scan, the
-            // exclusive prefix of every block goes to shared memory; then one lane per list entry finds its block by binary
-            // search and fetches the row (second round trip, all entries in parallel)
-            const int nb = p.lin_nblk, kb = (nb + 31) / 32;  // kb <= 8 (checked by the launcher: nblk <= 256)
-            const int b0 = min(lane * kb, nb), b1 = min(b0 + kb, nb);
-            int       cb[8];
-            int       local = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                cb[j] = (b0 + j < b1) ? __ldcg(p.lin_cnt + b0 + j) : 0;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                local += cb[j];
-            }
-            int incl = local;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, incl, o);
-                incl += (lane >= o) ? t : 0;
-            }
-            total_active = __shfl_sync(0xffffffffu, incl, 31);
-            int pbk      = incl - local;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if (b0 + j < b1) {
-                    blk_pre[b0 + j] = pbk;
-                }
-                pbk += cb[j];
-            }
-            if (lane == 31) {
-                blk_pre[nb] = total_active;
-            }
-            __syncwarp();
-            const int lo = (int) ((long long) c * total_active / P), hi = (int) ((long long) (c + 1) * total_active / P);
-            b_end        = hi - lo;
-            for (int j = lane; j < b_end; j += 32) {
-                const int rank = lo + j;
-                int       bl = 0, bh = nb;  // blk_pre[bl] <= rank < blk_pre[bh]
-                while (bh - bl > 1) {
-                    const int mid = (bl + bh) >> 1;
-                    if (blk_pre[mid] <= rank) {
-                        bl = mid;
-                    } else {
-                        bh = mid;
-                    }
-                }
-                const int row = __ldcg(p.lin_rows + (int) ((long long) bl * p.m / nb) + (rank - blk_pre[bl]));
-                const int neu = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
-                list_row[j]   = row;
-                list_neu[j]   = neu;
-                list_bu[j]    = p.b_up ? __ldg(p.b_up + neu) : 0.f;
-                list_bg[j]    = p.b_gate ? __ldg(p.b_gate + neu) : 0.f;
-            }
-            __syncwarp();
-            list_ready = true;
-        }
-        LAYER_STAMP(2);
         for (;;) {
             const int rc = issue_next();
             if (rc < 0) {
@@ -464,11 +573,14 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         pdl_launch_dependents();
         seq                = spif_comm_call_seq(p.comm);
         const uint32_t par = seq & 1u;
+        if (p.has_pred && rb == ra && lane == 0) {
+            atomicAdd(p.comm.seq + 4, 1u);  // no Wpu rows here: nothing to wait for from this CTA
+        }
         int            pend_tail = 0, gu_retired = 0, n_nonzero = 0, cnt_out = 0;
         int            s = 0, q = 0;
         unsigned       ph = 0;
         for (;; ++q) {
-            mbar_wait(&done[s], ph);
+            mbar_wait_spin(&done[s], ph);
             ITEM_STAMP(q, 3, 0);
             const int4    d  = desc[s];
             const float * ps = part + s * 128;
@@ -497,6 +609,13 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                         for (int r = 0; r < world; ++r) {
                             st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
                         }
+                    }
+                    if (d.y + d.z >= rb) {  // hint for the pollers: this CTA's words are on their way (not a release: every
+                        __syncwarp();       // word carries its own sequence number)
+                        if (lane == 0) {
+                            atomicAdd(p.comm.seq + 4, 1u);
+                        }
+                        LAYER_STAMP(13);
                     }
                 } else {
                     // gated: slot rows (up_0, gate_0, up_1, gate_1); ungated: (up_0 .. up_{RPS-1})
@@ -561,12 +680,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                     cnt_out += __popc(ball);
                 }
             } else if (d.x == IT_FLUSH) {
-                // every consumer thread has stored its slice of the partial y and fenced; publish the count
+                // every consumer thread has stored its slice of the partial y (their arrivals on done[s] ordered the stores
+                // before this point); a helper thread makes them visible to the other CTAs (fence + counter) off this path
                 if (lane == 0) {
                     p.cta_stats[c * 2 + 0] = d.y;
                     p.cta_stats[c * 2 + 1] = n_nonzero;
-                    __threadfence();
-                    atomicAdd(p.comm.seq + 3, 1u);
+                    mbar_arrive(flushbar);
                 }
                 LAYER_STAMP(4);
             }
@@ -594,7 +713,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             }
         }
         LAYER_STAMP(6);
-    } else {
+    } else if (warp < NW) {
         // ================================================ consumer warps ================================================
         float xr[VPT * 8], acc[VPT * 8], hr[VPT * 8];
 #pragma unroll
@@ -639,7 +758,8 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             }
             const int4 d = desc[s];
             float *    pw = part + s * 128 + warp;
-            if (d.x == IT_WPU || d.x == IT_GU) {
+            if (p.dbg & 1) {
+            } else if (d.x == IT_WPU || d.x == IT_GU) {
                 float v[RPS];
 #pragma unroll
                 for (int r = 0; r < RPS; ++r) {
@@ -699,46 +819,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                 }
             } else if (d.x == IT_WPD) {
                 if (!h1_loaded) {
-                    // the hidden vector of the predictor: {value, seq} words, complete once every CTA (of every shard) has
-                    // retired its Wpu rows -- they were first in everybody's queue.  ONE warp polls (all threads polling
-                    // floods the L2 with 95 K spinning loads and starves the producers' stores: 100 us per launch), the
-                    // values go through shared memory.
+                    // the hidden vector of the predictor, collected by the helper warps while the first items streamed
                     h1_loaded = true;
-                    if (warp == 0) {
-                        const uint32_t par = seq & 1u;
-                        const int      rw  = p.r / world;  // rows per owner rank
-                        unsigned       spins = 0;
-                        for (int base = 0; base < p.r; base += 256) {  // 8 words per lane per pass
-                            const int     row   = base + lane * 8;
-                            const int     owner = row / rw;
-                            const uint2 * src   = p.comm.data[p.comm.rank] + ((size_t) par * world + owner) * p.comm.cap + h1_off + row;
-                            uint2         w8[8];
-                            bool          ok = false;
-                            while (true) {
-#pragma unroll
-                                for (int e = 0; e < 8; e += 2) {
-                                    ld_word2_sys(src + e, w8[e], w8[e + 1]);
-                                }
-                                ok = true;
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) {
-                                    ok = ok && (w8[e].y == seq);
-                                }
-                                if (__all_sync(0xffffffffu, ok) || ++spins > SPIF_COMM_SPIN_LIMIT) {
-                                    break;
-                                }
-                                __nanosleep(100);
-                            }
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                h1_s[row + e] = ok ? __uint_as_float(w8[e].x) : __uint_as_float(0x7fc00000u);
-                            }
-                            if (!ok) {
-                                atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
-                            }
-                        }
-                    }
-                    named_bar_sync(2, NC);
+                    mbar_wait(h1bar, 0);
 #pragma unroll
                     for (int k = 0; k < VPT; ++k) {
                         if (vok[k]) {
@@ -752,9 +835,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                                 hr[k * 8 + e] = hv;
                             }
                         }
-                    }
-                    if (warp == 0) {
-                        LAYER_STAMP(9);
                     }
                 }
                 // slot row r holds RP rows of Wpd back to back; my vector k of that slot row belongs to one of them (the same
@@ -793,7 +873,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
                         __stcg(o + 1, make_float4(acc[k * 8 + 4], acc[k * 8 + 5], acc[k * 8 + 6], acc[k * 8 + 7]));
                     }
                 }
-                __threadfence();
             }
             __syncwarp();
             if (lane == 0) {
@@ -813,93 +892,134 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
             LAYER_STAMP(10);
         }
 
-        // ---- D: y[cols of this CTA] = sum over CTAs of their partial y, fixed order (+ b_down) [+ sum over shards]
-        if (p.has_ffn) {
+        // ---- D (launches without a predictor stream to hide it behind: all consumer threads, one L2 round trip)
+        if (p.has_ffn && (!p.has_pred || !(p.dbg & 4))) {
             named_bar_sync(1, NC);  // every consumer is done with the ring: reuse it as scratch
-            if (tid == 0) {
-                unsigned spins = 0;
-                while (ld_u32_acquire_gpu(p.comm.seq + 3) < (unsigned) P) {
-                    if (++spins > SPIF_COMM_SPIN_LIMIT) {
-                        atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
-                        break;
+            layer_sum_partials<true>(p, tid, NC, 1, reinterpret_cast<float4 *>(ring), seq, 2 * NW);
+        }
+    } else {
+        // ================================================== helper warps ==================================================
+        const int ht = tid - (NW + 2) * 32, HT = 32 * SPIF_LAYER_HELPER_WARPS;
+        pdl_wait_prior_grid();
+        pdl_launch_dependents();
+        seq = spif_comm_call_seq(p.comm);
+        // ---- my share of this layer's active rows: ranks [c*A/P, (c+1)*A/P) of the concatenated block lists
+        if (p.has_ffn && ht >= 32) {
+            // lane L owns blocks [L*kb, (L+1)*kb): all counts are requested at once (one L2 round trip), one warp scan, the
+            // exclusive prefix of every block goes to shared memory; then one lane per list entry finds its block by binary
+            // search and fetches the row (second round trip, all entries in parallel)
+            const int nb = p.lin_nblk, kb = (nb + 31) / 32;  // kb <= 8 (checked by the launcher: nblk <= 256)
+            const int b0 = min(lane * kb, nb), b1 = min(b0 + kb, nb);
+            int       cb[8];
+            int       local = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                cb[j] = (b0 + j < b1) ? __ldcg(p.lin_cnt + b0 + j) : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                local += cb[j];
+            }
+            int incl = local;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                incl += (lane >= o) ? t : 0;
+            }
+            const int total_active = __shfl_sync(0xffffffffu, incl, 31);
+            int pbk      = incl - local;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (b0 + j < b1) {
+                    blk_pre[b0 + j] = pbk;
+                }
+                pbk += cb[j];
+            }
+            if (lane == 31) {
+                blk_pre[nb] = total_active;
+            }
+            __syncwarp();
+            const int lo = share(c, total_active, P), hi = share(c + 1, total_active, P);
+            const int b_end = hi - lo;
+            for (int j = lane; j < b_end; j += 32) {
+                const int rank = lo + j;
+                int       bl = 0, bh = nb;  // blk_pre[bl] <= rank < blk_pre[bh]
+                while (bh - bl > 1) {
+                    const int mid = (bl + bh) >> 1;
+                    if (blk_pre[mid] <= rank) {
+                        bl = mid;
+                    } else {
+                        bh = mid;
                     }
                 }
+                const int row = __ldcg(p.lin_rows + share(bl, p.m, nb) + (rank - blk_pre[bl]));
+                const int neu = p.neuron_idx ? __ldg(p.neuron_idx + row) : row;
+                list_row[j]   = row;
+                list_neu[j]   = neu;
+                list_bu[j]    = p.b_up ? __ldg(p.b_up + neu) : 0.f;
+                list_bg[j]    = p.b_gate ? __ldg(p.b_gate + neu) : 0.f;
             }
-            named_bar_sync(1, NC);
-            if (warp == 0) {
-                LAYER_STAMP(11);
+            __syncwarp();
+            if (lane == 0) {
+                ctl[2] = b_end;
+                ctl[3] = total_active;
+                mbar_arrive(listbar);  // release: the issuer's test_wait acquires the list
             }
-            const int n4 = p.n_embd >> 2;
-            const int c0 = (int) ((long long) c * n4 / P), c1 = (int) ((long long) (c + 1) * n4 / P);
-            const int ncol = c1 - c0;  // <= 16 (checked by the launcher)
-            const int G = NC >> 4, col = tid & 15, pg = tid >> 4;
-            float4 *  red  = reinterpret_cast<float4 *>(ring);            // [G][16]
-            float4 *  red2 = red + (size_t) G * 16;                       // [4][16]
-            float4    sacc = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (col < ncol) {
-                const float4 * base = reinterpret_cast<const float4 *>(p.partials) + c0 + col;
-                float4         v[6];
+        }
+        if (p.has_pred && ht < 32) {
+            // the hidden vector of the predictor: {value, seq} words, complete once every CTA (of every shard) has retired its
+            // Wpu rows -- first in everybody's queue.  Few threads poll (all threads polling floods the L2 with spinning loads
+            // and starves the producers' stores: 100 us per launch in the first version), 8 words per thread per pass.
+            const uint32_t par = seq & 1u;
+            const int      rw  = p.r / world;  // rows per owner rank
+            unsigned       spins = 0;
+            // one word is polled until every CTA of THIS shard has sent its rows (148 pollers x 8 KB of words per round used a
+            // quarter of the L2's request rate and cost 2.7 us per layer); the words themselves are then read, normally once
+            while (ld_u32_relaxed_gpu(p.comm.seq + 4) < (unsigned) P && ++spins < SPIF_COMM_SPIN_LIMIT) {
+                __nanosleep(100);
+            }
+            LAYER_STAMP(14);
+            for (int row = ht * 16; row < p.r; row += 512) {  // 16 words per thread per pass (r % 256 == 0: whole threads)
+                const int     owner = row / rw;
+                const uint2 * src   = p.comm.data[p.comm.rank] + ((size_t) par * world + owner) * p.comm.cap + h1_off + row;
+                uint2         w16[16];
+                bool          ok = false;
+                while (true) {
 #pragma unroll
-                for (int q = 0; q < 6; ++q) {
-                    const int pp = pg + q * G;
-                    v[q]         = (pp < P) ? __ldcg(base + (size_t) pp * n4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
+                    for (int e = 0; e < 16; e += 2) {
+                        ld_word2_sys(src + e, w16[e], w16[e + 1]);
+                    }
+                    ok = true;
 #pragma unroll
-                for (int q = 0; q < 6; ++q) {
-                    sacc.x += v[q].x, sacc.y += v[q].y, sacc.z += v[q].z, sacc.w += v[q].w;
-                }
-                for (int pp = pg + 6 * G; pp < P; pp += G) {
-                    const float4 t = __ldcg(base + (size_t) pp * n4);
-                    sacc.x += t.x, sacc.y += t.y, sacc.z += t.z, sacc.w += t.w;
-                }
-            }
-            red[pg * 16 + col] = sacc;
-            named_bar_sync(1, NC);
-            if (tid < 64) {
-                const int j = tid >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
-                float4    t = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int g2 = lo; g2 < hi; ++g2) {
-                    const float4 v = red[g2 * 16 + col];
-                    t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
-                }
-                red2[j * 16 + col] = t;
-            }
-            named_bar_sync(1, NC);
-            if (tid < 16) {
-                const bool own = col < ncol;
-                float4     t   = red2[col];
-#pragma unroll
-                for (int j = 1; j < 4; ++j) {
-                    const float4 v = red2[j * 16 + col];
-                    t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
-                }
-                if (own && p.b_down) {
-                    const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0 + col);
-                    t.x += bb.x, t.y += bb.y, t.z += bb.z, t.w += bb.w;
-                }
-                t = spif_peer_allreduce_f4(p.comm, seq, t, c0 + col, own);
-                if (own) {
-                    reinterpret_cast<float4 *>(p.y)[c0 + col] = t;
-                }
-            }
-            if (c == 0 && warp == 1 % NW && p.stats_out) {
-                int nz = 0;
-                for (int q = lane; q < P; q += 32) {
-                    nz += __ldcg(p.cta_stats + q * 2 + 1);
+                    for (int e = 0; e < 16; ++e) {
+                        ok = ok && (w16[e].y == seq);
+                    }
+                    if (ok || ++spins > SPIF_COMM_SPIN_LIMIT) {
+                        break;
+                    }
+                    __nanosleep(100);
                 }
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    nz += __shfl_xor_sync(0xffffffffu, nz, o);
+                for (int e = 0; e < 16; ++e) {
+                    h1_s[row + e] = ok ? __uint_as_float(w16[e].x) : __uint_as_float(0x7fc00000u);
                 }
-                if (lane == 0) {
-                    p.stats_out[0] = __ldcg(p.cta_stats + 0);
-                    p.stats_out[1] = nz;
-                    p.stats_out[2] = 0;
-                    p.stats_out[3] = 0;
+                if (!ok) {
+                    atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
                 }
             }
-            if (warp == 0) {
-                LAYER_STAMP(12);
+            mbar_arrive(h1bar);  // release: the consumers' wait acquires h1_s
+            if (ht < 32) {
+                LAYER_STAMP(9);
+            }
+        }
+        if (p.has_ffn) {
+            if (ht == 0) {
+                mbar_wait(flushbar, 0);  // the epilogue warp has seen every consumer's arrival after its partial-y stores
+                __threadfence();
+                atomicAdd(p.comm.seq + 3, 1u);
+            }
+            if (p.has_pred && (p.dbg & 4)) {
+                layer_sum_partials<false>(p, ht, HT, 3, hred, seq, 2 * NW);
             }
         }
     }
@@ -908,6 +1028,8 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const LayerParams p
         spif_comm_block_done(p.comm, seq, (unsigned) P);
     }
 }
+
+#include "spif_layer_direct.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
 // float mask -> block lists (the form the layer kernel consumes).  One warp per block of rows, ballot + popc, ascending.
@@ -981,6 +1103,33 @@ static int launch_layer_t(const LayerParams & kp, int P, int threads, size_t sme
     return 0;
 }
 
+template <typename WT, int VPT, int RPS, int MAXT>
+static int launch_layer2_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
+    auto kern = spif_layer2_kernel<WT, VPT, RPS, MAXT>;
+    static unsigned long long done = 0;  // per instantiation: bit per device
+    const unsigned long long  bit  = 1ull << (device & 63);
+    if (!(done & bit)) {
+        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        done |= bit;
+    }
+    // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
+    int per_sm = 0;
+    SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+    SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(P);
+    cfg.blockDim           = dim3(threads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
+    return 0;
+}
+
 int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
                       const spif_shard_comm * comm, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
     SPIF_REQUIRE(ffn != nullptr || pred != nullptr, SPIF_E_NULL);
@@ -1026,10 +1175,13 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     SPIF_REQUIRE((n_embd / 4 + P - 1) / P <= 16, SPIF_E_UNSUPPORTED);  // column slice of the final sum
     SPIF_REQUIRE(kp.comm.cap >= n_embd + (pv ? pv->r : 0), SPIF_E_WORKSPACE);
 
-    const int vpt = (V <= 960) ? 1 : 2;
+    const int vpt = (V <= 896) ? 1 : 2;
     kp.nw         = (V + 32 * vpt - 1) / (32 * vpt);
     SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);  // n_embd >= 512: the final column-sliced sum uses 64 threads
-    const int threads = (kp.nw + 2) * 32;  // consumers + TMA issuer + epilogue
+    const int threads = (kp.nw + 2 + SPIF_LAYER_HELPER_WARPS) * 32;  // consumers + TMA issuer + epilogue + helpers
+    // share(): every a * b / d on the device is done in 32 bits
+    const long long max_dim = std::max<long long>(std::max<long long>(ffn ? ffn->m : 0, pv ? pv->m : 0), std::max(n_embd, pv ? pv->r : 0));
+    SPIF_REQUIRE((long long) (P + 1) * max_dim < (1ll << 31), SPIF_E_UNSUPPORTED);
     kp.n_embd     = n_embd;
     kp.V          = V;
     kp.row_bytes  = n_embd * 2;
@@ -1037,6 +1189,8 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     kp.trace      = g_spif_trace;
     static const int k_hint = [] { const char * e = getenv("SPIF_LAYER_L2_HINT"); return e ? atoi(e) : 0; }();
     kp.l2_hint    = k_hint;
+    static const int k_dbg = [] { const char * e = getenv("SPIF_LAYER_DEBUG"); return e ? atoi(e) : 0; }();
+    kp.dbg        = k_dbg;
     if (ffn) {
         kp.has_ffn    = 1;
         kp.w_up       = (const unsigned char *) ffn->w_up;
@@ -1096,6 +1250,26 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
     }
     kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
+    static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 1; }();
+    if (k_impl == 1) {  // version 4: warp-autonomous register-direct streaming (spif_layer_direct.cuh)
+        const int        threads2 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
+        const Layer2Smem L2       = layer2_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw, 4);
+        SPIF_REQUIRE(L2.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
+        if (ffn && ffn->hidden_out) {
+            SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
+        }
+        const bool h16 = type == SPIF_TYPE_F16;
+        if (vpt == 2) {
+            return h16 ? launch_layer2_t<spif_f16, 2, 2, 640>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
+                         launch_layer2_t<spif_bf16, 2, 2, 640>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
+        }
+        if (threads2 <= 736) {
+            return h16 ? launch_layer2_t<spif_f16, 1, 4, 736>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
+                         launch_layer2_t<spif_bf16, 1, 4, 736>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
+        }
+        return h16 ? launch_layer2_t<spif_f16, 1, 4, 1024>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
+                     launch_layer2_t<spif_bf16, 1, 4, 1024>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
+    }
     const int rps        = (vpt == 1 && kp.row_bytes <= 12288) ? 4 : 2;  // weight rows per ring slot
     const int slot_bytes = rps * kp.row_bytes;
     int       nslots     = 12;
@@ -1114,16 +1288,16 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     }
     const bool f16 = type == SPIF_TYPE_F16;
     if (vpt == 2) {
-        return f16 ? launch_layer_t<spif_f16, 2, 2, 576>(kp, P, threads, L.total, ctx.device, ctx.stream) :
-                     launch_layer_t<spif_bf16, 2, 2, 576>(kp, P, threads, L.total, ctx.device, ctx.stream);
+        return f16 ? launch_layer_t<spif_f16, 2, 2, 640>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 2, 2, 640>(kp, P, threads, L.total, ctx.device, ctx.stream);
     }
     if (rps == 2) {
         return f16 ? launch_layer_t<spif_f16, 1, 2, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
                      launch_layer_t<spif_bf16, 1, 2, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);
     }
-    if (threads <= 704) {
-        return f16 ? launch_layer_t<spif_f16, 1, 4, 704>(kp, P, threads, L.total, ctx.device, ctx.stream) :
-                     launch_layer_t<spif_bf16, 1, 4, 704>(kp, P, threads, L.total, ctx.device, ctx.stream);
+    if (threads <= 768) {
+        return f16 ? launch_layer_t<spif_f16, 1, 4, 768>(kp, P, threads, L.total, ctx.device, ctx.stream) :
+                     launch_layer_t<spif_bf16, 1, 4, 768>(kp, P, threads, L.total, ctx.device, ctx.stream);
     }
     return f16 ? launch_layer_t<spif_f16, 1, 4, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream) :
                  launch_layer_t<spif_bf16, 1, 4, 1024>(kp, P, threads, L.total, ctx.device, ctx.stream);

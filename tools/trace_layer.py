@@ -71,26 +71,28 @@ def main():
     setter(None)
     # producer stamps: 0 pre-wait prefetch issued, 1 wait done, 2 list built, 3 first GU issued, 4 flush retired, 5 loop done, 6 list out
     # consumer stamps: 8 first item, 9 h1 loaded, 10 END seen, 11 partials complete, 12 y written
-    names = {1: "wait", 2: "list", 3: "gu0", 8: "c.first", 4: "flush", 9: "c.h1", 5: "p.end", 10: "c.end", 11: "c.parts", 12: "c.y"}
+    names = {7: "entry", 0: "prewait", 1: "wait", 14: "poll0", 2: "list", 8: "c.first", 13: "h1.sent", 9: "h1.got", 4: "flush", 5: "p.end", 10: "c.end", 6: "l.out", 11: "c.parts", 12: "c.y"}
     prev_end = None
     for i, t in enumerate(traces):
         t = t.cpu().numpy().astype(np.float64)
-        t0 = t[:, 0][t[:, 0] > 0].min()
+        t0 = t[:, 7][t[:, 7] > 0].min()
         line = []
         for k, nm in names.items():
             col = t[:, k]
             ok = col > 0
             if ok.any():
                 rel = (col[ok] - t0) / 1e3
-                line.append(f"{nm} {np.median(rel):5.2f}/{rel.max():5.2f}")
+                line.append(f"{nm} {rel.min():5.2f}/{np.median(rel):5.2f}/{rel.max():5.2f}")
         end = max(t[:, 12].max(), t[:, 6].max(), t[:, 10].max())
         gap = "" if prev_end is None else f" gap_from_prev_end {(t0 - prev_end) / 1e3:5.2f}"
-        print(f"launch {i}: total {(end - t0) / 1e3:6.2f} us start_spread {(t[:, 0].max() - t0) / 1e3:5.2f}{gap} | med/max since first CTA start: " + " | ".join(line))
+        print(f"launch {i}: total {(end - t0) / 1e3:6.2f} us start_spread {(t[:, 7].max() - t0) / 1e3:5.2f}{gap} | min/med/max since first CTA entry: " + " | ".join(line))
         prev_end = end
         if i in (0, 2, L):  # per-item timeline of the median CTA and CTA 0
             names_t = {1: "WPU", 2: "GU", 3: "DN", 4: "WPD", 5: "FLUSH", 6: "END"}
-            for cta in (0, 77):
+            slow = int(np.argmax(t[:, 13])) if t[:, 13].max() > 0 else int(np.argmax(t[:, 4]))
+            for cta in (0, 77, slow):
                 row = t[cta]
+                print(f"   cta {cta}: " + " ".join(f"{nm}={(row[k] - t0) / 1e3:.2f}" for k, nm in names.items() if row[k] > 0))
                 items = []
                 for q in range(120):
                     ty = int(row[16 + 4 * q])

@@ -1030,6 +1030,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const __grid_consta
 }
 
 #include "spif_layer_direct.cuh"
+#include "spif_layer_stream.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
 // float mask -> block lists (the form the layer kernel consumes).  One warp per block of rows, ballot + popc, ascending.
@@ -1116,6 +1117,33 @@ static int launch_layer2_t(const LayerParams & kp, int P, int threads, size_t sm
     int per_sm = 0;
     SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
     SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(P);
+    cfg.blockDim           = dim3(threads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
+    return 0;
+}
+
+template <typename WT, int VPT, int MAXT>
+static int launch_layer3_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
+    auto kern = spif_layer3_kernel<WT, VPT, MAXT>;
+    static unsigned long long done = 0;  // per instantiation: bit per device
+    const unsigned long long  bit  = 1ull << (device & 63);
+    if (!(done & bit)) {
+        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
+        int per_sm = 0;
+        SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+        SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
+        done |= bit;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = dim3(P);
     cfg.blockDim           = dim3(threads);
@@ -1250,7 +1278,26 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
     }
     kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
-    static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 1; }();
+    static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 2; }();
+    if (k_impl == 2) {  // version 5: static schedule of register-direct row batches (spif_layer_stream.cuh)
+        const int        threads3 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
+        const Layer3Smem L3       = layer3_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw);
+        SPIF_REQUIRE(L3.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
+        if (ffn && ffn->hidden_out) {
+            SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
+        }
+        const bool h16 = type == SPIF_TYPE_F16;
+        if (vpt == 2) {
+            return h16 ? launch_layer3_t<spif_f16, 2, 640>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
+                         launch_layer3_t<spif_bf16, 2, 640>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
+        }
+        if (threads3 <= 736) {
+            return h16 ? launch_layer3_t<spif_f16, 1, 736>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
+                         launch_layer3_t<spif_bf16, 1, 736>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
+        }
+        return h16 ? launch_layer3_t<spif_f16, 1, 1024>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
+                     launch_layer3_t<spif_bf16, 1, 1024>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
+    }
     if (k_impl == 1) {  // version 4: warp-autonomous register-direct streaming (spif_layer_direct.cuh)
         const int        threads2 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
         const Layer2Smem L2       = layer2_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw, 4);

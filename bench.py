@@ -74,6 +74,9 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the reference-CUDA-kernels leg (oracle/_ref/libspif_refcuda.so)")
     ap.add_argument("--no-scale-70b", action="store_true", help="N > 1: skip the relullama-70b scaling leg")
+    ap.add_argument("--activations", default="f32", choices=["f32", "weight"],
+                    help="f32: x / hidden values stay F32 (flags 0); weight: rounded to the weight type like the reference CPU "
+                         "ops, ggml-cpu.c:1832-1856 (SPIF_FLAG_CPU_ROUNDING): exact f16 x f16 products, F32 accumulation")
     ap.add_argument("--no-early-mask", action="store_true", help="do not use SPIF_FLAG_MASK_STABLE")
     return ap.parse_args()
 
@@ -191,7 +194,8 @@ def build_stack(a, wl, rank, world, device):
                                    pred_down=half(m, R, R ** -0.5), pred_down_b=bpd, m=m))
     group = torch.distributed.group.WORLD if world > 1 else None
     st = FfnStack(wl["arch"], sp.GGML_TYPE_F16, sp.GGML_TYPE_F16, E, m, R, layers, n_tok=1, group=group, device=device,
-                  exchange=a.exchange, topk=int(a.rho * m) if wl.get("topk") else 0)
+                  exchange=a.exchange, topk=int(a.rho * m) if wl.get("topk") else 0,
+                  flags=sp.FLAG_CPU_ROUNDING if a.activations == "weight" else 0)
     st.shard_maps = shard_maps
     return st, expect
 
@@ -438,7 +442,9 @@ def run_ours(a):
                    "schedule": schedule + (": one launch per layer, FFN(l) + predictor(l+1); predictor(l+1) reads x_l, launch l+1 "
                                            "follows launch l on one stream (the reference graph's data edges)" if fused else ""),
                    "l2": "inputs larger than L2: distinct weights per layer, %.1f GB touched per step" %
-                         ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool},
+                         ((ffn_bytes + pred_bytes) / 1e9), "x_pool": a.pool,
+                   "activations": "rounded to the weight type like the reference CPU ops (ggml-cpu.c:1832-1856), exact products, "
+                                  "F32 accumulation" if a.activations == "weight" else "F32 (weights converted to F32 per element)"},
         "e2e": {"value": 1e3 / (ms_e2e / a.steps), "unit": "tok/s", "h2d_bytes_per_step": 4 * L * E,
                 "d2h_bytes_per_step": 4 * L * E},
         "gpu_launches": launches_per_step * a.steps,

@@ -31,6 +31,7 @@
 #include "spif_comm.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 #define SPIF_LIST_MAX_BLOCKS 1024
 #define SPIF_LIST_HDR        4 /* int32: {nblk, m, 0, 0} */
@@ -250,7 +251,13 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
         float4 *  red  = scratch;                 // [G][16]
         red2           = red + (size_t) G * 16;   // [4][16]
         red[pg * 16 + col] = (col < ncol) ? layer_group_sum(base, pg, G, P, n4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (t < 32) {
+            LAYER_STAMP(3);
+        }
         named_bar_sync(bar_id, nthr);
+        if (t < 32) {
+            LAYER_STAMP(5);
+        }
         if (t < 64) {
             const int j = t >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
             float4    a = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1131,9 +1138,13 @@ static int launch_layer2_t(const LayerParams & kp, int P, int threads, size_t sm
     return 0;
 }
 
-template <typename WT, int VPT, int MAXT>
+template <typename WT, int VPT, int MAXT, bool RND, bool TRACE = false>
 static int launch_layer3_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
-    auto kern = spif_layer3_kernel<WT, VPT, MAXT>;
+    constexpr bool can_trace = VPT == 1 && !RND && std::is_same<WT, spif_f16>::value;
+    if (!TRACE && can_trace && kp.trace) {  // tools/trace_layer.py: per-item time stamps
+        return launch_layer3_t<WT, VPT, MAXT, RND, can_trace>(kp, P, threads, smem, device, stream);
+    }
+    auto kern = spif_layer3_kernel<WT, VPT, MAXT, TRACE, RND>;
     static unsigned long long done = 0;  // per instantiation: bit per device
     const unsigned long long  bit  = 1ull << (device & 63);
     if (!(done & bit)) {
@@ -1279,7 +1290,11 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     }
     kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
     static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 2; }();
-    if (k_impl == 2) {  // version 5: static schedule of register-direct row batches (spif_layer_stream.cuh)
+    if (k_impl == 2) {  // version 5: static schedule of row batches, cp.async staging per thread (spif_layer_stream.cuh)
+        // one 16-byte vector per thread up to 10 KB rows, two above: the staging of DEPTH items of 4 vectors per thread must fit
+        const int vpt3 = (V <= 640) ? 1 : 2;
+        kp.nw          = (V + 32 * vpt3 - 1) / (32 * vpt3);
+        SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);
         const int        threads3 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
         const Layer3Smem L3       = layer3_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw);
         SPIF_REQUIRE(L3.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
@@ -1287,16 +1302,17 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
             SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
         }
         const bool h16 = type == SPIF_TYPE_F16;
-        if (vpt == 2) {
-            return h16 ? launch_layer3_t<spif_f16, 2, 640>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
-                         launch_layer3_t<spif_bf16, 2, 640>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
+        // x, the hidden values and the predictor's hidden vector all rounded to the weight type (the reference CPU arithmetic):
+        // exact products by one instruction per element (fhfma2)
+        const bool rnd = (!ffn || (ffn->flags & SPIF_FLAG_CPU_ROUNDING)) && (!pv || (pv->flags & SPIF_FLAG_CPU_ROUNDING));
+#define SPIF_L3_GO(WT_, VPT_, MAXT_)                                                                                       \
+    (rnd ? launch_layer3_t<WT_, VPT_, MAXT_, true>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :                    \
+           launch_layer3_t<WT_, VPT_, MAXT_, false>(kp, P, threads3, L3.total, ctx.device, ctx.stream))
+        if (vpt3 == 2) {
+            return h16 ? SPIF_L3_GO(spif_f16, 2, 640) : SPIF_L3_GO(spif_bf16, 2, 640);
         }
-        if (threads3 <= 736) {
-            return h16 ? launch_layer3_t<spif_f16, 1, 736>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
-                         launch_layer3_t<spif_bf16, 1, 736>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
-        }
-        return h16 ? launch_layer3_t<spif_f16, 1, 1024>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :
-                     launch_layer3_t<spif_bf16, 1, 1024>(kp, P, threads3, L3.total, ctx.device, ctx.stream);
+        return h16 ? SPIF_L3_GO(spif_f16, 1, 736) : SPIF_L3_GO(spif_bf16, 1, 736);
+#undef SPIF_L3_GO
     }
     if (k_impl == 1) {  // version 4: warp-autonomous register-direct streaming (spif_layer_direct.cuh)
         const int        threads2 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers

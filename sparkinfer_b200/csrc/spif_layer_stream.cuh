@@ -7,26 +7,28 @@
 //   * cp.async staging (v4): 22 M warp instructions per launch (address selection per 16 bytes, polling): issue-bound, 33 us.
 //   * tools/ubench/stream_rows.cu: plain 128-bit loads straight into registers, 8 rows in flight per thread, warps running
 //     free of each other, reach 6.5 TB/s -- the best of all load paths, with no staging at all.
-// So: no ring, no issuer, no dynamic queue.  The work of a CTA is a fixed sequence of ITEMS of 8 row slices per thread
-// (8 x 16 B in flight per thread, 80 KB per SM at 13B):
+// So: no ring, no issuer, no dynamic queue.  The work of a CTA is a fixed sequence of ITEMS of 4 row slices per thread,
+// two items in flight per thread (8 x 16 B, 80 KB per SM at 13B): the loads of item t+1 are issued before item t is used,
+// so a short item (the last rows of a phase) costs its bytes, not a memory round trip:
 //
 //     Wpu rows -> [row list ready] -> gate/up rows -> first Wpd item -> [hidden values known] -> W_down^T rows of the
 //     non-zero hidden values -> partial y stored -> remaining Wpd rows -> column-sliced sum of all CTAs' partial y
 //
 // Every consumer warp walks this sequence on its own (it owns the 16-byte column slices [32w, 32w+32) of every row): issue
-// the 8 loads of an item, multiply, one packed shuffle tree for the 8 partial dots, 8 floats into a small ring in shared
-// memory, one mbarrier arrival.  Warps never wait for each other inside an item type; the three points where the sequence
+// the 4 loads of the next item, multiply the current one, one packed shuffle tree for its 4 partial dots, 4 floats into a
+// small ring in shared memory, one mbarrier arrival.  Warps never wait for each other inside an item type; the three points where the sequence
 // depends on other warps / CTAs (row list, hidden values, the predictor's hidden vector) sit behind other streaming work.
 // The epilogue warp retires the partial dots in the canonical order Wpu -> gate/up -> Wpd (bias, activation, sigmoid,
 // compaction); helper warps do everything that waits on other CTAs (row list, h1 gather, partial-y publication).
 // Determinism: fixed shuffle tree, fixed warp order, W_down^T rows in ascending neuron order, partials in CTA order.
 #pragma once
 
-#define SPIF_L3_K 8 /* depth of the partial-dot ring (reduce items between the consumer warps and the epilogue warp) */
+#define SPIF_L3_DEPTH 4 /* items in flight per consumer thread (cp.async groups) */
+#define SPIF_L3_K 16 /* depth of the partial-dot ring (reduce items between the consumer warps and the epilogue warp) */
 
 struct Layer3Smem {
-    uint32_t done, part, ctl, list_row, list_neu, list_bu, list_bg, pend_row, pend_alpha, bpu_s, bpd_s, lout_s, h1_s, blk_pre,
-        red, total;
+    uint32_t done, part, ctl, list_row, list_neu, list_bu, list_bg, tab_a, tab_b, tab_c, tab_d, bpu_s, bpd_s, lout_s, h1_s, blk_pre,
+        red, wdesc, stage, total;
 };
 
 __host__ __device__ static inline Layer3Smem layer3_smem_layout(int cap_ffn, int cap_pd, int cap_pu, int r, int nblk, int nw) {
@@ -39,49 +41,74 @@ __host__ __device__ static inline Layer3Smem layer3_smem_layout(int cap_ffn, int
         return r;
     };
     L.done       = take(8u * SPIF_L3_K, 8);
-    L.part       = take(4u * 256 * SPIF_L3_K, 16);  // [K][8][32]
+    L.part       = take(4u * 128 * SPIF_L3_K, 16);  // [K][4][32]
     L.ctl        = take(96u, 16);  // int[8] {pend_tail, -, b_end, total_active, items retired, ...}, 4 mbarriers at +32
     L.list_row   = take(4u * cap_ffn, 4);
     L.list_neu   = take(4u * cap_ffn, 4);
     L.list_bu    = take(4u * cap_ffn, 4);
     L.list_bg    = take(4u * cap_ffn, 4);
-    L.pend_row   = take(4u * cap_ffn, 4);
-    L.pend_alpha = take(4u * cap_ffn, 4);
+    L.tab_a      = take(16u * (cap_pu + 4), 16);       // Wpu rows
+    L.tab_b      = take(16u * (2 * cap_ffn + 4), 16);  // gate/up rows
+    L.tab_c      = take(16u * (cap_pd + 4), 16);       // Wpd virtual rows (at most one per Wpd row)
+    L.tab_d      = take(16u * (cap_ffn + 4), 16);      // W_down^T rows
     L.bpu_s      = take(4u * cap_pu, 4);
     L.bpd_s      = take(4u * cap_pd, 4);
     L.lout_s     = take(4u * cap_pd, 4);
     L.h1_s       = take(4u * r, 16);
     L.blk_pre    = take(4u * (nblk + 1), 4);
     L.red        = take(16u * (2 * nw + 4) * 16, 16);  // scratch of the column-sliced sum
+    L.wdesc      = take(8u * SPIF_L3_DEPTH * nw, 16);  // per warp: {type, table address} of its items in flight
+    L.stage      = take(16u * SPIF_L3_DEPTH * 4 * nw * 32, 128);  // [DEPTH][4 vectors per thread][NC] x 16 B
     L.total      = (o + 127) / 128 * 128;
     return L;
 }
 
-// eight warp reductions with nine shuffles: every lane of group g = lane >> 2 returns the warp sum of v[g]
-__device__ __forceinline__ float reduce8(const float (&v)[8], int lane) {
-    const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0;
-    float      a[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        a[i] = (b4 ? v[4 + i] : v[i]) + __shfl_xor_sync(0xffffffffu, b4 ? v[i] : v[4 + i], 16);
-    }
-    float b[2];
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        b[i] = (b3 ? a[2 + i] : a[i]) + __shfl_xor_sync(0xffffffffu, b3 ? a[i] : a[2 + i], 8);
-    }
-    float c = (b2 ? b[1] : b[0]) + __shfl_xor_sync(0xffffffffu, b2 ? b[0] : b[1], 4);
-    c += __shfl_xor_sync(0xffffffffu, c, 2);
-    c += __shfl_xor_sync(0xffffffffu, c, 1);
-    return c;
+// ---- exact f16 x f16 (bf16 x bf16) products accumulated in F32 by ONE instruction per element (fma.rn.f32.f16 -> FHFMA):
+// with SPIF_FLAG_CPU_ROUNDING x / the hidden values are values of the weight type (ggml-cpu.c:1832-1856), so the 8
+// conversions per 16 bytes of weights disappear and the results are bit-identical to convert + FFMA (both round once).
+template <typename WT> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<spif_f16>(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+template <> __device__ __forceinline__ uint32_t pack2<spif_bf16>(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+template <typename WT> __device__ __forceinline__ void fhfma2(float & s0, float & s1, uint32_t w, uint32_t x);
+template <> __device__ __forceinline__ void fhfma2<spif_f16>(float & s0, float & s1, uint32_t w, uint32_t x) {
+    asm("{\n\t.reg .b16 a0, a1, b0, b1;\n\tmov.b32 {a0, a1}, %2;\n\tmov.b32 {b0, b1}, %3;\n\t"
+        "fma.rn.f32.f16 %0, a0, b0, %0;\n\tfma.rn.f32.f16 %1, a1, b1, %1;\n\t}"
+        : "+f"(s0), "+f"(s1) : "r"(w), "r"(x));
+}
+template <> __device__ __forceinline__ void fhfma2<spif_bf16>(float & s0, float & s1, uint32_t w, uint32_t x) {
+    asm("{\n\t.reg .b16 a0, a1, b0, b1;\n\tmov.b32 {a0, a1}, %2;\n\tmov.b32 {b0, b1}, %3;\n\t"
+        "fma.rn.f32.bf16 %0, a0, b0, %0;\n\tfma.rn.f32.bf16 %1, a1, b1, %1;\n\t}"
+        : "+f"(s0), "+f"(s1) : "r"(w), "r"(x));
+}
+// same order of additions as dot8: even elements in one chain, odd elements in the other
+template <typename WT> __device__ __forceinline__ float dot8h(const uint4 & wv, const uint32_t * xh) {
+    float s0 = 0.f, s1 = 0.f;
+    fhfma2<WT>(s0, s1, wv.x, xh[0]);
+    fhfma2<WT>(s0, s1, wv.y, xh[1]);
+    fhfma2<WT>(s0, s1, wv.z, xh[2]);
+    fhfma2<WT>(s0, s1, wv.w, xh[3]);
+    return s0 + s1;
 }
 
+// A row of the schedule: {global address lo, hi, valid bytes of the row (0: no row), alpha of a W_down^T row}.  Tables in shared
+// memory, one per source: Wpu rows and Wpd "virtual rows" (RP adjacent Wpd rows = row_bytes) are filled at kernel entry, the
+// gate/up table by the helper warp that fetches the active-row list, the W_down^T table by the epilogue warp as it retires
+// the hidden values.  Every table is padded with empty rows to whole items.
+enum { T_DOT = 0, T_DOTH = 1, T_AXPY = 2, T_FLUSH = 3, T_NONE = 4, T_END = 5 };
+
 // Warp roles: [0, NW) consumers, NW = epilogue, NW + 1 .. NW + 2 = helpers (row list, h1 gather, partial-y publication).
-// An item is RPI = 8 / VPT rows: every consumer thread holds 8 x 16 bytes of it.
-template <typename WT, int VPT, int MAXT>
+// An item is RPI = 4 / VPT rows (4 x 16 bytes per consumer thread); a thread keeps two items in flight.
+template <typename WT, int VPT, int MAXT, bool TRACE, bool RND>
 __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_constant__ LayerParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int RPI = 8 / VPT;
+    constexpr int RPI   = 4 / VPT;  // rows per item: 4 x 16 bytes per thread
+    constexpr int DEPTH = SPIF_L3_DEPTH;
     constexpr int K   = SPIF_L3_K;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NW = p.nw, NC = NW * 32;
@@ -89,18 +116,19 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
 
     const Layer3Smem L = layer3_smem_layout(p.cap_ffn, p.cap_pd, p.cap_pu, p.has_pred ? p.r : 0, p.lin_nblk, NW);
     uint64_t * done       = reinterpret_cast<uint64_t *>(smem + L.done);
-    float *    part       = reinterpret_cast<float *>(smem + L.part);  // [K][8][32]
+    float *    part       = reinterpret_cast<float *>(smem + L.part);  // [K][4][32]
     int *      ctl        = reinterpret_cast<int *>(smem + L.ctl);
     uint64_t * h1bar      = reinterpret_cast<uint64_t *>(smem + L.ctl + 32);
     uint64_t * flushbar   = reinterpret_cast<uint64_t *>(smem + L.ctl + 40);
     uint64_t * listbar    = reinterpret_cast<uint64_t *>(smem + L.ctl + 48);
-    uint64_t * dnbar      = reinterpret_cast<uint64_t *>(smem + L.ctl + 56);
     int *      list_row   = reinterpret_cast<int *>(smem + L.list_row);
     int *      list_neu   = reinterpret_cast<int *>(smem + L.list_neu);
     float *    list_bu    = reinterpret_cast<float *>(smem + L.list_bu);
     float *    list_bg    = reinterpret_cast<float *>(smem + L.list_bg);
-    int *      pend_row   = reinterpret_cast<int *>(smem + L.pend_row);
-    float *    pend_alpha = reinterpret_cast<float *>(smem + L.pend_alpha);
+    uint4 *    tab_a      = reinterpret_cast<uint4 *>(smem + L.tab_a);
+    uint4 *    tab_b      = reinterpret_cast<uint4 *>(smem + L.tab_b);
+    uint4 *    tab_c      = reinterpret_cast<uint4 *>(smem + L.tab_c);
+    uint4 *    tab_d      = reinterpret_cast<uint4 *>(smem + L.tab_d);
     float *    bpu_s      = reinterpret_cast<float *>(smem + L.bpu_s);
     float *    bpd_s      = reinterpret_cast<float *>(smem + L.bpd_s);
     int *      lout_s     = reinterpret_cast<int *>(smem + L.lout_s);
@@ -113,20 +141,22 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
         if (p.trace) {
             p.trace[(size_t) blockIdx.x * 512 + 15] = (unsigned long long) clock64();
         }
-        for (int s = 0; s < K; ++s) {
-            mbar_init(&done[s], NW);
-        }
-        mbar_init(h1bar, 64);
-        mbar_init(flushbar, NW + 1);
-        mbar_init(listbar, 1);
-        mbar_init(dnbar, 1);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            ctl[i] = 0;
+    }
+    if (tid < K + 3) {  // one barrier per thread: 19 serial mbarrier.init cost 0.3 us of every launch
+        if (tid < K) {
+            mbar_init(&done[tid], NW);
+        } else if (tid == K) {
+            mbar_init(h1bar, 64);
+        } else if (tid == K + 1) {
+            mbar_init(flushbar, NW + 1);
+        } else {
+            mbar_init(listbar, 1);
         }
         mbar_fence_init();
     }
-    __syncthreads();
+    if (tid >= 32 && tid < 40) {
+        ctl[tid - 32] = 0;
+    }
 
     const bool gated    = (p.arch != SPIF_ARCH_RELU_UP);
     const bool rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
@@ -147,81 +177,255 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
     const int n_wpu = (rb - ra + RPI - 1) / RPI;             // items of Wpu rows
     const int wpi   = RPI * p.RP;                            // Wpd rows per item (RP of them = one "virtual row" of row_bytes)
     const int n_wpd = (pb - pa + wpi - 1) / wpi;
-    const int n_wpd1 = p.has_ffn ? min(n_wpd, 1) : n_wpd;    // Wpd items streamed while the hidden values are being retired
+
+    // ---- the two tables that are known at entry (weights only: the first Wpu items are issued before the PDL wait)
+    const uint32_t row_bytes = (uint32_t) p.row_bytes, wrow_bytes = (uint32_t) p.r * 2;
+    const uint32_t tabA_s = smem_u32(tab_a), tabB_s = smem_u32(tab_b), tabC_s = smem_u32(tab_c), tabD_s = smem_u32(tab_d);
+    for (int i = tid; i < n_wpu * RPI; i += blockDim.x) {
+        const unsigned long long a = (unsigned long long) (p.wpu + (size_t) (ra + i) * row_bytes);
+        tab_a[i] = make_uint4((uint32_t) a, (uint32_t) (a >> 32), (ra + i < rb) ? row_bytes : 0u, 0u);
+    }
+    for (int i = tid; i < n_wpd * RPI; i += blockDim.x) {
+        const int                row = pa + i * p.RP;  // first Wpd row of virtual row i
+        const unsigned long long a   = (unsigned long long) (p.wpd + (size_t) row * wrow_bytes);
+        tab_c[i] = make_uint4((uint32_t) a, (uint32_t) (a >> 32), (uint32_t) max(0, min(p.RP, pb - row)) * wrow_bytes, 0u);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        LAYER_STAMP(0);
+    }
 
     if (warp < NW) {
         // ================================================ consumer warps ================================================
-        float    xr[VPT * 8], acc[VPT * 8];
+        // vr: x while Wpu / gate/up items are consumed, then (x is dead) my 8 (16) values of the predictor's hidden vector
+        // (RND: both are values of the weight type, kept as packed pairs in vh -- see fhfma2)
+        float    vr[VPT * 8], acc[VPT * 8];
+        uint32_t vh[VPT * 4];
         uint32_t toff[VPT];
-        bool     vok[VPT], pok[VPT];
-        int      wrow[VPT];
 #pragma unroll
         for (int k = 0; k < VPT; ++k) {
-            const int v = tid + k * NC;
-            vok[k]      = v < p.V;
-            toff[k]     = (uint32_t) v * 16u;
-            wrow[k]     = v / p.Vr;                  // Wpd: which of the RP rows of a virtual row my vector belongs to
-            pok[k]      = vok[k] && wrow[k] < p.RP;
+            toff[k] = (uint32_t) (tid + k * NC) * 16u;
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-                xr[k * 8 + e] = 0.f, acc[k * 8 + e] = 0.f;
+                vr[k * 8 + e] = 0.f, acc[k * 8 + e] = 0.f;
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                vh[k * 4 + e] = 0u;
             }
         }
-        const uint32_t row_bytes = (uint32_t) p.row_bytes, wrow_bytes = (uint32_t) p.r * 2;
-        const uint4    zero4     = make_uint4(0u, 0u, 0u, 0u);
-        uint4          w[RPI][VPT];
-        int            kseq = 0, qstamp = 0;
+        // my 16 bytes of (slot, row j, vector k): consecutive threads are consecutive in shared memory (conflict-free both ways);
+        // a thread only ever reads back what it copied itself, so the staging needs no barrier -- cp.async groups are the
+        // whole pipeline: DEPTH items in flight per thread, completion in order (cp.async.wait_group)
+        const uint32_t stage_s = smem_u32(smem + L.stage) + (uint32_t) tid * 16u;
+        const uint32_t jstride = (uint32_t) NC * 16u, sstride = jstride * (RPI * VPT);
+        const uint32_t desc_s  = smem_u32(smem + L.wdesc) + (uint32_t) warp * (DEPTH * 8u);  // {type | name << 8, table address}
 
-        auto load_wpu = [&](int i) {
-            const int a = ra + i * RPI, n = min(RPI, rb - a);
-#pragma unroll
-            for (int j = 0; j < RPI; ++j) {
-                const unsigned char * src = p.wpu + (size_t) (a + j) * row_bytes;
-#pragma unroll
-                for (int k = 0; k < VPT; ++k) {
-                    w[j][k] = (j < n && vok[k]) ? ldg_stream_v4(src + toff[k]) : zero4;
+        // ---- which item next?  Priority: Wpu rows (the predictor's hidden vector has the longest way to go: every CTA of every
+        // shard) > W_down^T rows whose hidden values the epilogue warp has retired (4 table rows at a time, so the partial y is
+        // complete -- and on its way to the other CTAs -- right after the last gate/up item) > gate/up rows > Wpd rows (dense,
+        // the cover for everything that waits on other CTAs).  Nothing here blocks: when no table is ready the slot gets an
+        // empty item and the items already in flight are consumed meanwhile.
+        int      a_left = n_wpu, b_left = p.has_ffn ? -1 : 0, c_left = n_wpd, d_next = 0;
+        bool     flushed = !p.has_ffn;
+        uint32_t a_ptr = tabA_s, b_ptr = tabB_s, c_ptr = tabC_s;
+        auto pick = [&](int & ty, uint32_t & pt) {
+            if (a_left > 0) {
+                ty = T_DOT | (1 << 8), pt = a_ptr;
+                --a_left, a_ptr += RPI * 16u;
+                return;
+            }
+            if (b_left < 0) {  // my share of the active-row list: a helper warp builds the gate/up table
+                if (!mbar_test(listbar, 0)) {
+                    return;
                 }
+                b_left = ctl[5];
+            }
+            if (!flushed) {
+                const int final_rows = ld_acquire_cta_s32(ctl + 1);  // > 0: every gate/up item retired, rows incl. padding + 1
+                const int rows       = final_rows > 0 ? final_rows - 1 : ld_acquire_cta_s32(ctl + 0);
+                if ((d_next + 1) * RPI <= rows) {
+                    ty = T_AXPY | (3 << 8), pt = tabD_s + (uint32_t) d_next * (RPI * 16u);
+                    ++d_next;
+                    return;
+                }
+                if (final_rows > 0) {  // the W_down^T rows are all issued: my slice of the partial y follows them
+                    ty      = T_FLUSH | (5 << 8);
+                    flushed = true;
+                    return;
+                }
+            }
+            if (b_left > 0) {
+                ty = T_DOT | (2 << 8), pt = b_ptr;
+                --b_left, b_ptr += RPI * 16u;
+                return;
+            }
+            if (c_left > 0) {
+                ty = T_DOTH | (4 << 8), pt = c_ptr;
+                --c_left, c_ptr += RPI * 16u;
+                return;
+            }
+            if (flushed) {
+                ty = T_END | (6 << 8);
             }
         };
-        // RPI x VPT partial dots of the item against vec (x or the predictor's hidden vector) -> slot kidx % K of the ring
-        auto dot_deposit = [&](const float * vec, int kidx) {
-            float v[8];
+
+        int  qi = 0, qc = 0, kseq = 0;
+        auto issue = [&](int slot) {
+            int      ty = T_NONE | (7 << 8);
+            uint32_t pt = 0;
+            pick(ty, pt);
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(desc_s + (uint32_t) slot * 8u), "r"(ty), "r"(pt) : "memory");
+            if (TRACE && warp == 0 && (ty & 0xff) != T_END) {
+                ITEM_STAMP(qi, 0, (unsigned long long) (ty >> 8));
+                ITEM_STAMP(qi, 1, 0);
+                ++qi;
+            }
+            if ((ty & 0xff) <= T_AXPY) {  // an item with rows: table entries {address, valid bytes, alpha}
+                const uint32_t dst = stage_s + (uint32_t) slot * sstride;
 #pragma unroll
-            for (int j = 0; j < RPI; ++j) {
+                for (int j = 0; j < RPI; ++j) {
+                    const uint4                 e   = lds128(pt + j * 16u);
+                    const unsigned char * const src = reinterpret_cast<const unsigned char *>(((unsigned long long) e.y << 32) | e.x);
+#pragma unroll
+                    for (int k = 0; k < VPT; ++k) {  // rows that are not there: 0 bytes are read (the address is a valid one)
+                        cp_async_16(dst + (uint32_t) (j * VPT + k) * jstride, src + toff[k], toff[k] < e.z ? 16 : 0);
+                    }
+                }
+            }
+            cp_async_commit();  // also for items without rows: one group per item keeps wait_group in step
+        };
+
+        bool h1_ready = false;
+        auto consume = [&](int slot) -> bool {  // false: the END item
+            int      ty;
+            uint32_t pt;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(ty), "=r"(pt) : "r"(desc_s + (uint32_t) slot * 8u) : "memory");
+            ty &= 0xff;
+            if (ty == T_END) {
+                return false;
+            }
+            if (TRACE && warp == 0) {
+                ITEM_STAMP(qc, 2, 0);
+            }
+            if (ty <= T_AXPY) {
+                uint4 w[RPI][VPT];
+#pragma unroll
+                for (int j = 0; j < RPI; ++j) {
+#pragma unroll
+                    for (int k = 0; k < VPT; ++k) {
+                        w[j][k] = lds128(stage_s + (uint32_t) slot * sstride + (uint32_t) (j * VPT + k) * jstride);
+                    }
+                }
+                if (ty == T_AXPY) {
+                    // table order = ascending neuron order: a fixed FMA chain per element; missing rows are zeros times zero
+#pragma unroll
+                    for (int j = 0; j < RPI; ++j) {
+                        float alpha;
+                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(alpha) : "r"(pt + j * 16u + 12u));
+#pragma unroll
+                        for (int k = 0; k < VPT; ++k) {
+                            if (RND) {  // alpha is a value of the weight type (the epilogue warp rounded it)
+                                const uint32_t a2 = pack2<WT>(alpha, alpha);
+                                fhfma2<WT>(acc[k * 8 + 0], acc[k * 8 + 1], w[j][k].x, a2);
+                                fhfma2<WT>(acc[k * 8 + 2], acc[k * 8 + 3], w[j][k].y, a2);
+                                fhfma2<WT>(acc[k * 8 + 4], acc[k * 8 + 5], w[j][k].z, a2);
+                                fhfma2<WT>(acc[k * 8 + 6], acc[k * 8 + 7], w[j][k].w, a2);
+                            } else {
+                                float f[8];
+                                unpack8<WT>(w[j][k], f);
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    acc[k * 8 + e] = fmaf(f[e], alpha, acc[k * 8 + e]);
+                                }
+                            }
+                        }
+                    }
+                } else {
+                    if (ty == T_DOTH && !h1_ready) {
+                        // the hidden vector of the predictor, gathered by the helper warps while the rows above streamed
+                        h1_ready = true;
+                        mbar_wait(h1bar, 0);
+#pragma unroll
+                        for (int k = 0; k < VPT; ++k) {
+                            const int    v    = tid + k * NC;
+                            const int    hcol = (v < p.RP * p.Vr) ? v % p.Vr : 0;
+                            const float4 h0   = *reinterpret_cast<const float4 *>(h1_s + hcol * 8);
+                            const float4 h1v  = *reinterpret_cast<const float4 *>(h1_s + hcol * 8 + 4);
+                            if (RND) {
+                                vh[k * 4 + 0] = pack2<WT>(h0.x, h0.y), vh[k * 4 + 1] = pack2<WT>(h0.z, h0.w);
+                                vh[k * 4 + 2] = pack2<WT>(h1v.x, h1v.y), vh[k * 4 + 3] = pack2<WT>(h1v.z, h1v.w);
+                                continue;
+                            }
+                            vr[k * 8 + 0] = h0.x, vr[k * 8 + 1] = h0.y, vr[k * 8 + 2] = h0.z, vr[k * 8 + 3] = h0.w;
+                            vr[k * 8 + 4] = h1v.x, vr[k * 8 + 5] = h1v.y, vr[k * 8 + 6] = h1v.z, vr[k * 8 + 7] = h1v.w;
+                            if (p.pflags & SPIF_FLAG_CPU_ROUNDING) {
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) {
+                                    vr[k * 8 + e] = round_through<WT>(vr[k * 8 + e]);
+                                }
+                            }
+                        }
+                    }
+                    // RPI x VPT = 4 partial dots -> one packed shuffle tree -> slot kseq % K of the ring -> one arrival
+                    float v0, v1, v2, v3;
+                    auto dotv = [&](const uint4 & wv, int k) -> float {
+                        return RND ? dot8h<WT>(wv, vh + k * 4) : dot8<WT>(wv, vr + k * 8);
+                    };
+                    if (VPT == 1) {
+                        v0 = dotv(w[0][0], 0), v1 = dotv(w[1 % RPI][0], 0);
+                        v2 = dotv(w[2 % RPI][0], 0), v3 = dotv(w[3 % RPI][0], 0);
+                    } else {
+                        v0 = dotv(w[0][0], 0), v1 = dotv(w[0][VPT - 1], VPT - 1);
+                        v2 = dotv(w[1 % RPI][0], 0), v3 = dotv(w[1 % RPI][VPT - 1], VPT - 1);
+                    }
+                    const float s = reduce4(v0, v1, v2, v3, lane);  // lanes [8q, 8q+8): partial q = row * VPT + vector
+                    if (kseq >= K) {  // the epilogue warp must be done with item kseq - K (it trails by one or two items)
+                        while (kseq - ld_volatile_s32(ctl + 4) >= K) {
+                            __nanosleep(20);
+                        }
+                    }
+                    const int ks = kseq & (K - 1);
+                    if ((lane & 7) == 0) {
+                        part[ks * 128 + (lane >> 3) * 32 + warp] = s;
+                    }
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive(&done[ks]);
+                    }
+                    ++kseq;
+                }
+            } else if (ty == T_FLUSH) {
+                // my slice of this CTA's partial y; a helper thread publishes it (fence + counter) off this path
+                float * prt = p.partials + (size_t) c * p.n_embd;
 #pragma unroll
                 for (int k = 0; k < VPT; ++k) {
-                    v[j * VPT + k] = dot8<WT>(w[j][k], vec + k * 8);
+                    if (toff[k] < row_bytes) {
+                        float4 * o = reinterpret_cast<float4 *>(prt) + 2 * (tid + k * NC);
+                        __stcg(o, make_float4(acc[k * 8 + 0], acc[k * 8 + 1], acc[k * 8 + 2], acc[k * 8 + 3]));
+                        __stcg(o + 1, make_float4(acc[k * 8 + 4], acc[k * 8 + 5], acc[k * 8 + 6], acc[k * 8 + 7]));
+                    }
                 }
-            }
-            const float s = reduce8(v, lane);
-            if (kidx >= K) {  // the epilogue warp must be done with item kidx - K (it trails by one or two items)
-                while (kidx - ld_volatile_s32(ctl + 4) >= K) {
-                    __nanosleep(20);
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(flushbar);
                 }
+            } else {
+                __nanosleep(100);  // an empty item: a table is not ready yet
             }
-            if ((lane & 3) == 0) {
-                part[(kidx % K) * 256 + (lane >> 2) * 32 + warp] = s;
+            if (TRACE && warp == 0) {
+                ITEM_STAMP(qc, 3, 0);
+                ++qc;
             }
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(&done[kidx % K]);
-            }
+            return true;
         };
-#define L3_STAMP_BEGIN(ty)                                        \
-    if (warp == 0) {                                              \
-        ITEM_STAMP(qstamp, 0, (unsigned long long) (ty));         \
-        ITEM_STAMP(qstamp, 1, 0);                                 \
-    }
-#define L3_STAMP_END()               \
-    if (warp == 0) {                 \
-        ITEM_STAMP(qstamp, 3, 0);    \
-        ++qstamp;                    \
-    }
 
-        // ---- Wpu rows: the first item is on its way before the programmatic-dependent-launch wait (weights only)
-        L3_STAMP_BEGIN(D_WPU);
-        if (n_wpu > 0) {
-            load_wpu(0);
+        // ---- DEPTH - 1 items are in flight before the first one is used.  Wpu items are weights only: they are on their way
+        // before the programmatic-dependent-launch wait; x is read after it.
+        int n_issued = 0;
+        while (n_issued < DEPTH - 1 && n_issued < n_wpu) {
+            issue(n_issued);
+            ++n_issued;
         }
         pdl_wait_prior_grid();
         pdl_launch_dependents();
@@ -231,151 +435,42 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
         seq = spif_comm_call_seq(p.comm);
 #pragma unroll
         for (int k = 0; k < VPT; ++k) {
-            if (vok[k]) {
+            if (toff[k] < row_bytes) {
                 const int    v = tid + k * NC;
                 const float4 a = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v);
                 const float4 b = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v + 1);
-                xr[k * 8 + 0] = a.x, xr[k * 8 + 1] = a.y, xr[k * 8 + 2] = a.z, xr[k * 8 + 3] = a.w;
-                xr[k * 8 + 4] = b.x, xr[k * 8 + 5] = b.y, xr[k * 8 + 6] = b.z, xr[k * 8 + 7] = b.w;
+                if (RND) {  // ggml-cpu.c:1832-1856: x is converted to the weight type
+                    vh[k * 4 + 0] = pack2<WT>(a.x, a.y), vh[k * 4 + 1] = pack2<WT>(a.z, a.w);
+                    vh[k * 4 + 2] = pack2<WT>(b.x, b.y), vh[k * 4 + 3] = pack2<WT>(b.z, b.w);
+                    continue;
+                }
+                vr[k * 8 + 0] = a.x, vr[k * 8 + 1] = a.y, vr[k * 8 + 2] = a.z, vr[k * 8 + 3] = a.w;
+                vr[k * 8 + 4] = b.x, vr[k * 8 + 5] = b.y, vr[k * 8 + 6] = b.z, vr[k * 8 + 7] = b.w;
                 if (rounding) {  // ggml-cpu.c:1832-1856: x is converted to the weight type
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        xr[k * 8 + e] = round_through<WT>(xr[k * 8 + e]);
+                        vr[k * 8 + e] = round_through<WT>(vr[k * 8 + e]);
                     }
                 }
             }
         }
-        for (int i = 0; i < n_wpu; ++i) {
-            if (i > 0) {
-                L3_STAMP_BEGIN(D_WPU);
-                load_wpu(i);
-            }
-            dot_deposit(xr, kseq++);
-            L3_STAMP_END();
+        if (warp == 0) {
+            LAYER_STAMP(8);
         }
-        if (n_wpu == 0) {
-            L3_STAMP_END();
+        while (n_issued < DEPTH - 1) {
+            issue(n_issued);
+            ++n_issued;
         }
-
-        // ---- gate/up rows of my share of the active-row list (the helper warp has fetched it meanwhile)
-        if (p.has_ffn) {
-            mbar_wait(listbar, 0);
-            const int b_end = ctl[2];
-            for (int i0 = 0; i0 < b_end; i0 += npg) {
-                const int n = min(npg, b_end - i0);
-                L3_STAMP_BEGIN(D_GU);
-#pragma unroll
-                for (int j = 0; j < RPI; ++j) {
-                    const int  jj = gated ? (j >> 1) : j;
-                    const bool ok = jj < n;
-                    const unsigned char * src = p.w_up;
-                    if (ok) {
-                        src = ((gated && (j & 1)) ? p.w_gate : p.w_up) + (size_t) list_row[i0 + jj] * row_bytes;
-                    }
-#pragma unroll
-                    for (int k = 0; k < VPT; ++k) {
-                        w[j][k] = (ok && vok[k]) ? ldg_stream_v4(src + toff[k]) : zero4;
-                    }
-                }
-                dot_deposit(xr, kseq++);
-                L3_STAMP_END();
+        for (int slot = 0, islot = DEPTH - 1;;) {
+            issue(islot);
+            cp_async_wait<DEPTH - 1>();  // the oldest item in flight has landed
+            if (!consume(slot)) {
+                break;
             }
+            slot  = (slot + 1 == DEPTH) ? 0 : slot + 1;
+            islot = (islot + 1 == DEPTH) ? 0 : islot + 1;
         }
-
-        // ---- Wpd rows: dense, known at entry; they need the predictor's hidden vector (gathered by the helper warps while the
-        // rows above streamed).  x is dead from here on: its registers hold my 8 (16) values of h1.
-        float hr[VPT * 8];
-        bool  h1_ready = false;
-        auto wpd_item = [&](int i) {
-            L3_STAMP_BEGIN(D_WPD);
-            const int row0 = pa + i * wpi;
-#pragma unroll
-            for (int j = 0; j < RPI; ++j) {
-                const int             rj  = row0 + j * p.RP;  // first Wpd row of virtual row j
-                const unsigned char * src = p.wpd + (size_t) rj * wrow_bytes;
-#pragma unroll
-                for (int k = 0; k < VPT; ++k) {
-                    w[j][k] = (pok[k] && rj + wrow[k] < pb) ? ldg_stream_v4(src + toff[k]) : zero4;
-                }
-            }
-            if (!h1_ready) {
-                h1_ready = true;
-                mbar_wait(h1bar, 0);
-#pragma unroll
-                for (int k = 0; k < VPT; ++k) {
-                    const int    hcol = (tid + k * NC) - wrow[k] * p.Vr;
-                    const float4 h0   = *reinterpret_cast<const float4 *>(h1_s + (pok[k] ? hcol : 0) * 8);
-                    const float4 h1v  = *reinterpret_cast<const float4 *>(h1_s + (pok[k] ? hcol : 0) * 8 + 4);
-                    hr[k * 8 + 0] = h0.x, hr[k * 8 + 1] = h0.y, hr[k * 8 + 2] = h0.z, hr[k * 8 + 3] = h0.w;
-                    hr[k * 8 + 4] = h1v.x, hr[k * 8 + 5] = h1v.y, hr[k * 8 + 6] = h1v.z, hr[k * 8 + 7] = h1v.w;
-                    if (p.pflags & SPIF_FLAG_CPU_ROUNDING) {
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            hr[k * 8 + e] = round_through<WT>(hr[k * 8 + e]);
-                        }
-                    }
-                }
-            }
-            dot_deposit(hr, kseq++);
-            L3_STAMP_END();
-        };
-        for (int i = 0; i < n_wpd1; ++i) {
-            wpd_item(i);
-        }
-
-        // ---- W_down^T rows of the non-zero hidden values (axpy-sparse.cu:53), ascending: a fixed FMA chain per element
-        if (p.has_ffn) {
-            mbar_wait(dnbar, 0);  // the epilogue warp has retired every gate/up item
-            const int n_pend = ctl[0];
-            for (int i0 = 0; i0 < n_pend; i0 += RPI) {
-                const int n = min(RPI, n_pend - i0);
-                L3_STAMP_BEGIN(D_DN);
-#pragma unroll
-                for (int j = 0; j < RPI; ++j) {
-                    const bool            ok  = j < n;
-                    const unsigned char * src = p.w_down + (size_t) (ok ? pend_row[i0 + j] : 0) * row_bytes;
-#pragma unroll
-                    for (int k = 0; k < VPT; ++k) {
-                        w[j][k] = (ok && vok[k]) ? ldg_stream_v4(src + toff[k]) : zero4;
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < RPI; ++j) {
-                    if (j < n) {  // uniform
-                        const float alpha = pend_alpha[i0 + j];
-#pragma unroll
-                        for (int k = 0; k < VPT; ++k) {
-                            float f[8];
-                            unpack8<WT>(w[j][k], f);
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                acc[k * 8 + e] = fmaf(f[e], alpha, acc[k * 8 + e]);
-                            }
-                        }
-                    }
-                }
-                L3_STAMP_END();
-            }
-            // my slice of this CTA's partial y; a helper thread publishes it (fence + counter) off this path
-            float * prt = p.partials + (size_t) c * p.n_embd;
-#pragma unroll
-            for (int k = 0; k < VPT; ++k) {
-                if (vok[k]) {
-                    float4 * o = reinterpret_cast<float4 *>(prt) + 2 * (tid + k * NC);
-                    __stcg(o, make_float4(acc[k * 8 + 0], acc[k * 8 + 1], acc[k * 8 + 2], acc[k * 8 + 3]));
-                    __stcg(o + 1, make_float4(acc[k * 8 + 4], acc[k * 8 + 5], acc[k * 8 + 6], acc[k * 8 + 7]));
-                }
-            }
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(flushbar);
-            }
-        }
-
-        // ---- the remaining Wpd rows cover the time until every CTA has published its partial y
-        for (int i = n_wpd1; i < n_wpd; ++i) {
-            wpd_item(i);
-        }
+        cp_async_wait<0>();
         if (warp == 0) {
             LAYER_STAMP(10);
         }
@@ -383,8 +478,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
         if (p.has_ffn) {
             layer_sum_partials<true>(p, tid, NC, 1, red, seq, 2 * NW);
         }
-#undef L3_STAMP_BEGIN
-#undef L3_STAMP_END
     } else if (warp == NW) {
         // ================================================== epilogue warp ==================================================
         for (int i = lane; i < rb - ra; i += 32) {
@@ -416,7 +509,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
                 if (n_gu == 0 && lane == 0) {
                     p.cta_stats[c * 2 + 0] = ctl[3];
                     p.cta_stats[c * 2 + 1] = 0;
-                    mbar_arrive(dnbar);
+                    st_release_cta_s32(ctl + 1, 1);
                     mbar_arrive(flushbar);
                 }
             }
@@ -424,7 +517,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
                 break;
             }
             mbar_wait_spin(&done[k % K], (unsigned) (k / K) & 1u);
-            const float * ps = part + (k % K) * 256;
+            const float * ps = part + (k % K) * 128;
             if (k < n_wpu + n_gu) {
                 // row sum = sum over (vector k', warp w) of the partial dots, in a fixed order: LPR lanes per row, then a tree
                 float s = 0.f;
@@ -471,19 +564,27 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
                         }
                         if (!(h == 0.0f)) {  // axpy-sparse.cu:53: rows with hid == 0 are never read
                             if (lane == 0) {
-                                pend_row[pend_tail]   = list_row[i];
-                                pend_alpha[pend_tail] = h;
+                                const unsigned long long a = (unsigned long long) (p.w_down + (size_t) list_row[i] * row_bytes);
+                                tab_d[pend_tail] = make_uint4((uint32_t) a, (uint32_t) (a >> 32), row_bytes, __float_as_uint(h));
                             }
                             ++pend_tail;
                             ++n_nonzero;
                         }
                     }
-                    if (k - n_wpu + 1 == n_gu && lane == 0) {  // the W_down^T list is final
-                        ctl[0]                 = pend_tail;
-                        p.cta_stats[c * 2 + 0] = ctl[3];
-                        p.cta_stats[c * 2 + 1] = n_nonzero;
-                        mbar_arrive(dnbar);     // release: the consumers' wait acquires pend_row / pend_alpha / ctl[0]
-                        mbar_arrive(flushbar);
+                    if (lane == 0) {
+                        if (k - n_wpu + 1 < n_gu) {
+                            st_release_cta_s32(ctl + 0, pend_tail);  // after the table rows
+                        } else {  // the W_down^T table is final: pad it to whole items
+                            const int                n_dn = (pend_tail + RPI - 1) / RPI;
+                            const unsigned long long a0   = (unsigned long long) p.w_down;  // a valid address, no bytes, alpha 0
+                            for (int q = pend_tail; q < n_dn * RPI; ++q) {
+                                tab_d[q] = make_uint4((uint32_t) a0, (uint32_t) (a0 >> 32), 0u, 0u);
+                            }
+                            p.cta_stats[c * 2 + 0] = ctl[3];
+                            p.cta_stats[c * 2 + 1] = n_nonzero;
+                            st_release_cta_s32(ctl + 1, n_dn * RPI + 1);
+                            mbar_arrive(flushbar);
+                        }
                     }
                 }
             } else {
@@ -600,10 +701,25 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer3_kernel(const __grid_const
                 list_neu[j]   = neu;
                 list_bu[j]    = p.b_up ? __ldg(p.b_up + neu) : 0.f;
                 list_bg[j]    = p.b_gate ? __ldg(p.b_gate + neu) : 0.f;
+                // the rows of this neuron in the gate/up table: gated (up, gate), else (up)
+                const unsigned long long au = (unsigned long long) (p.w_up + (size_t) row * row_bytes);
+                if (gated) {
+                    const unsigned long long ag = (unsigned long long) (p.w_gate + (size_t) row * row_bytes);
+                    tab_b[2 * j]     = make_uint4((uint32_t) au, (uint32_t) (au >> 32), row_bytes, 0u);
+                    tab_b[2 * j + 1] = make_uint4((uint32_t) ag, (uint32_t) (ag >> 32), row_bytes, 0u);
+                } else {
+                    tab_b[j] = make_uint4((uint32_t) au, (uint32_t) (au >> 32), row_bytes, 0u);
+                }
+            }
+            const int n_rows_b = gated ? 2 * b_end : b_end, n_gu_items = (n_rows_b + RPI - 1) / RPI;
+            const unsigned long long a0 = (unsigned long long) p.w_up;  // a valid address, no bytes
+            for (int q = n_rows_b + lane; q < n_gu_items * RPI; q += 32) {
+                tab_b[q] = make_uint4((uint32_t) a0, (uint32_t) (a0 >> 32), 0u, 0u);
             }
             __syncwarp();
             if (lane == 0) {
                 ctl[2] = b_end;
+                ctl[5] = n_gu_items;
                 ctl[3] = total_active;
                 mbar_arrive(listbar);  // release: test_wait / try_wait on the other side acquire the list
             }

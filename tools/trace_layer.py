@@ -71,7 +71,7 @@ def main():
     setter(None)
     # producer stamps: 0 pre-wait prefetch issued, 1 wait done, 2 list built, 3 first GU issued, 4 flush retired, 5 loop done, 6 list out
     # consumer stamps: 8 first item, 9 h1 loaded, 10 END seen, 11 partials complete, 12 y written
-    names = {7: "entry", 0: "prewait", 1: "wait", 14: "poll0", 2: "list", 8: "c.first", 13: "h1.sent", 9: "h1.got", 4: "flush", 5: "p.end", 10: "c.end", 6: "l.out", 11: "c.parts", 12: "c.y"}
+    names = {7: "entry", 0: "prewait", 1: "wait", 14: "poll0", 2: "list", 8: "c.first", 13: "h1.sent", 9: "h1.got", 4: "flush", 10: "c.end", 6: "l.out", 11: "c.parts", 3: "s.ld", 5: "s.l2", 12: "c.y"}
     prev_end = None
     for i, t in enumerate(traces):
         t = t.cpu().numpy().astype(np.float64)

@@ -258,15 +258,52 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
         if (t < 32) {
             LAYER_STAMP(5);
         }
+        // second level: the four quarters of a column sit in four adjacent lanes, combined as (q0 + q1) + (q2 + q3) by two
+        // shuffles -- no third pass through shared memory
         if (t < 64) {
-            const int j = t >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
+            const int c2 = t >> 2, j = t & 3, lo = j * G / 4, hi = (j + 1) * G / 4;
             float4    a = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int g = lo; g < hi; ++g) {
-                const float4 v = red[g * 16 + col];
+                const float4 v = red[g * 16 + c2];
                 a.x += v.x, a.y += v.y, a.z += v.z, a.w += v.w;
             }
-            red2[j * 16 + col] = a;
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                a.x += __shfl_xor_sync(0xffffffffu, a.x, o), a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+                a.z += __shfl_xor_sync(0xffffffffu, a.z, o), a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+            }
+            if (j == 0) {
+                const bool own = c2 < ncol;
+                if (own && p.b_down) {
+                    const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0 + c2);
+                    a.x += bb.x, a.y += bb.y, a.z += bb.z, a.w += bb.w;
+                }
+                a = layer_allreduce_f4(p.comm, seq, a, c0 + c2, own);
+                if (own) {
+                    reinterpret_cast<float4 *>(p.y)[c0 + c2] = a;
+                }
+            }
         }
+        if (c == 0 && (t >> 5) == (nthr > 64 ? 2 : 1) && p.stats_out) {
+            int nz = 0;
+            for (int q = lane; q < P; q += 32) {
+                nz += __ldcg(p.cta_stats + q * 2 + 1);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                nz += __shfl_xor_sync(0xffffffffu, nz, o);
+            }
+            if (lane == 0) {
+                p.stats_out[0] = __ldcg(p.cta_stats + 0);
+                p.stats_out[1] = nz;
+                p.stats_out[2] = 0;
+                p.stats_out[3] = 0;
+            }
+        }
+        if (t < 32) {
+            LAYER_STAMP(12);
+        }
+        return;
     } else {
         const int j = t >> 4, lo = j * G / 4, hi = (j + 1) * G / 4;
         red2        = scratch;
@@ -1038,6 +1075,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const __grid_consta
 
 #include "spif_layer_direct.cuh"
 #include "spif_layer_stream.cuh"
+#include "spif_layer_tma.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
 // float mask -> block lists (the form the layer kernel consumes).  One warp per block of rows, ballot + popc, ascending.
@@ -1145,6 +1183,37 @@ static int launch_layer3_t(const LayerParams & kp, int P, int threads, size_t sm
         return launch_layer3_t<WT, VPT, MAXT, RND, can_trace>(kp, P, threads, smem, device, stream);
     }
     auto kern = spif_layer3_kernel<WT, VPT, MAXT, TRACE, RND>;
+    static unsigned long long done = 0;  // per instantiation: bit per device
+    const unsigned long long  bit  = 1ull << (device & 63);
+    if (!(done & bit)) {
+        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
+        int per_sm = 0;
+        SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+        SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
+        done |= bit;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(P);
+    cfg.blockDim           = dim3(threads);
+    cfg.dynamicSmemBytes   = smem;
+    cfg.stream             = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs                                        = at;
+    cfg.numAttrs                                     = 1;
+    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
+    return 0;
+}
+
+template <typename WT, int VPT, int MAXT, bool RND, bool TRACE = false>
+static int launch_layer4_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
+    constexpr bool can_trace = VPT == 1 && !RND && std::is_same<WT, spif_f16>::value;
+    if (!TRACE && can_trace && kp.trace) {  // tools/trace_layer.py: per-item time stamps
+        return launch_layer4_t<WT, VPT, MAXT, RND, can_trace>(kp, P, threads, smem, device, stream);
+    }
+    auto kern = spif_layer4_kernel<WT, VPT, MAXT, TRACE, RND>;
     static unsigned long long done = 0;  // per instantiation: bit per device
     const unsigned long long  bit  = 1ull << (device & 63);
     if (!(done & bit)) {
@@ -1289,7 +1358,37 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
     }
     kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
-    static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 2; }();
+    static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 3; }();
+    if (k_impl == 3) {  // version 6: row tables + one producer lane + TMA bulk copies into a ring of 4-row slots (spif_layer_tma.cuh)
+        const int vpt4 = (V <= 640) ? 1 : 2;
+        kp.nw          = (V + 32 * vpt4 - 1) / (32 * vpt4);
+        SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);
+        const int threads4   = (kp.nw + 4) * 32;  // consumers + epilogue + 2 helpers + producer
+        const int slot_bytes = (4 / vpt4) * kp.row_bytes;
+        int       nslots     = 8;
+        Layer4Smem L4        = layer4_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P);
+        while (nslots > 2 && L4.total > (uint32_t) ctx.max_smem_optin) {
+            --nslots;
+            L4 = layer4_smem_layout(nslots, slot_bytes, kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P);
+        }
+        SPIF_REQUIRE(L4.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
+        // the final column-sliced sum reuses the ring as scratch: [(2 nw + 4) x 16] float4
+        SPIF_REQUIRE((size_t) nslots * slot_bytes >= (size_t) (kp.nw * 2 + 4) * 16 * 16, SPIF_E_SHAPE);
+        kp.nslots = nslots;
+        if (ffn && ffn->hidden_out) {
+            SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
+        }
+        const bool h16 = type == SPIF_TYPE_F16;
+        const bool rnd = (!ffn || (ffn->flags & SPIF_FLAG_CPU_ROUNDING)) && (!pv || (pv->flags & SPIF_FLAG_CPU_ROUNDING));
+#define SPIF_L4_GO(WT_, VPT_, MAXT_)                                                                                       \
+    (rnd ? launch_layer4_t<WT_, VPT_, MAXT_, true>(kp, P, threads4, L4.total, ctx.device, ctx.stream) :                    \
+           launch_layer4_t<WT_, VPT_, MAXT_, false>(kp, P, threads4, L4.total, ctx.device, ctx.stream))
+        if (vpt4 == 2) {
+            return h16 ? SPIF_L4_GO(spif_f16, 2, 640) : SPIF_L4_GO(spif_bf16, 2, 640);
+        }
+        return h16 ? SPIF_L4_GO(spif_f16, 1, 768) : SPIF_L4_GO(spif_bf16, 1, 768);
+#undef SPIF_L4_GO
+    }
     if (k_impl == 2) {  // version 5: static schedule of row batches, cp.async staging per thread (spif_layer_stream.cuh)
         // one 16-byte vector per thread up to 10 KB rows, two above: the staging of DEPTH items of 4 vectors per thread must fit
         const int vpt3 = (V <= 640) ? 1 : 2;

@@ -383,7 +383,7 @@ def run_ours(a):
     if world == 1:  # the ncu capture is of the single-GPU launch; at N > 1 the per-launch bytes differ, so no constant is quoted
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_top_kernel.json")))
-            if (tj.get("kernel", "").startswith("spif_layer_kernel")) == fused:
+            if (tj.get("kernel", "").startswith("spif_layer")) == fused:
                 traffic = tj.get("dram_bytes_per_launch")
         except Exception:
             pass

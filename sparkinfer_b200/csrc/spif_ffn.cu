@@ -195,6 +195,11 @@ static int launch_reduce(const FfnKParams & kp, const float * b_down, float * y,
     return 0;
 }
 
+int spif_launch_reduce_partials(const FfnKParams & kp, const float * b_down, float * y, int32_t * stats_out, int n_embd, int n_tok,
+                                int P, cudaStream_t stream, const spif_shard_comm * comm) {
+    return launch_reduce(kp, b_down, y, stats_out, n_embd, n_tok, P, stream, comm);
+}
+
 // workspace layout shared with spif_api.cu: [partials n_tok*P*n_embd f32][cta_stats n_tok*P*2 i32]
 // `row_bytes` / `nc` (consumer threads) / `variant` come from the weight format; `launch` instantiates the kernel.
 int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,

@@ -581,6 +581,10 @@ static int spif_ffn_launch_kernel(const FfnKParams & kp, dim3 grid, int threads,
     return 0;
 }
 
+// y = fixed-order sum of the per-CTA partials (+ b_down) [+ the shard exchange]: spif_reduce_partials_kernel (spif_ffn.cu)
+int spif_launch_reduce_partials(const FfnKParams & kp, const float * b_down, float * y, int32_t * stats_out, int n_embd, int n_tok,
+                                int P, cudaStream_t stream, const spif_shard_comm * comm);
+
 typedef int (*spif_ffn_launch_fn)(int type, int mode, int variant, const FfnKParams & kp, dim3 grid, int threads, size_t smem,
                                   cudaStream_t stream, int device);
 int spif_launch_ffn_common(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,

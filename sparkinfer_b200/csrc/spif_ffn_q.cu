@@ -17,24 +17,7 @@
 //     axpy is acc = fma(q, d * alpha, acc) in FP32 like axpyq-sparse.cu / ggml_axpy_avx_q8_0_alphaf32.
 // Activation quantiser: default = the CUDA reference's (d = amax/127, q = roundf(x/d), quantize.cu:19-31);
 // SPIF_FLAG_CPU_ROUNDING = the CPU backend's (id = 127/amax, round-half-even, arch/x86/quants.c:290-356).
-#include "spif_ffn_kernel.cuh"
-
-struct spif_q8_0 {};
-struct spif_q4_0 {};
-
-template <typename QT> struct QuantTraits;
-template <> struct QuantTraits<spif_q8_0> {
-    static constexpr int BLOCK_BYTES = 34;
-    static constexpr int PAIR_WORDS  = 17;
-};
-template <> struct QuantTraits<spif_q4_0> {
-    static constexpr int BLOCK_BYTES = 18;
-    static constexpr int PAIR_WORDS  = 9;
-};
-
-__device__ __forceinline__ float half_bits_to_float(unsigned h) {
-    return __half2float(__ushort_as_half((unsigned short) (h & 0xffffu)));
-}
+#include "spif_ffn_qwarp.cuh"
 
 template <typename QT> struct QuantCodec {
     using T                   = QuantTraits<QT>;
@@ -220,12 +203,156 @@ static int launch_quant(int type, int mode, int variant, const FfnKParams & kp, 
                                       launch_qm<QuantCodec<spif_q4_0>>(mode, kp, grid, threads, smem, stream, device);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// warp-per-neuron kernel (spif_ffn_qwarp.cuh): the default for every mode
+template <typename QT, int IPT, int MAXT>
+static int launch_qwarp_m(int mode, const FfnKParams & kp, dim3 grid, int threads, size_t smem, cudaStream_t stream, int device) {
+    auto go = [&](auto kern, unsigned long long & done) -> int {
+        const int rc0 = spif_set_max_smem_once(kern, smem, device, done);
+        if (rc0) {
+            return rc0;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim            = grid;
+        cfg.blockDim           = dim3(threads);
+        cfg.dynamicSmemBytes   = smem;
+        cfg.stream             = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs                                        = at;
+        cfg.numAttrs                                     = 1;
+        SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
+        return 0;
+    };
+    static unsigned long long d0 = 0, d1 = 0, d2 = 0;
+    switch (mode) {
+        case SPIF_MODE_FUSED:
+            return go(spif_ffn_qwarp_kernel<QT, SPIF_MODE_FUSED, IPT, MAXT>, d0);
+        case SPIF_MODE_GEMV:
+            return go(spif_ffn_qwarp_kernel<QT, SPIF_MODE_GEMV, IPT, MAXT>, d1);
+        default:
+            return go(spif_ffn_qwarp_kernel<QT, SPIF_MODE_AXPY, IPT, MAXT>, d2);
+    }
+}
+
+// returns SPIF_E_UNSUPPORTED when the shape does not qualify (the ring kernel handles it then)
+static int spif_launch_ffn_qwarp(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,
+                                 size_t ws_bytes, const spif_launch_ctx & ctx) {
+    const int nblk      = a.n_embd / 32;
+    const int row_bytes = nblk * (a.type == SPIF_TYPE_Q8_0 ? 34 : 18);
+    const int P         = ctx.sm_count;
+    SPIF_REQUIRE(P >= 1 && P <= 320, SPIF_E_UNSUPPORTED);  // spif_reduce_partials_kernel: 32 lanes x 10 partials
+    SPIF_REQUIRE(a.n_embd % 256 == 0 && a.n_embd <= 16384, SPIF_E_UNSUPPORTED);
+    SPIF_REQUIRE(a.neuron_idx != nullptr || a.m == a.n_ff, SPIF_E_SHAPE);
+    SPIF_REQUIRE(a.sparse_idx != nullptr, SPIF_E_NULL);
+    const int n_items = a.n_embd / 8;
+    int       threads = (n_items + 31) / 32 * 32;
+    threads           = threads < 256 ? 256 : (threads > 1024 ? 1024 : threads);
+    while (a.m > 4096 * (threads / 32) && threads < 1024) {  // activity bits kept in registers by build_my_list
+        threads += 32;
+    }
+    SPIF_REQUIRE(a.m <= 4096 * (threads / 32), SPIF_E_UNSUPPORTED);
+    const int ipt = (n_items + threads - 1) / threads;
+    SPIF_REQUIRE(ipt <= 2, SPIF_E_UNSUPPORTED);
+
+    FfnKParams kp = {};
+    kp.w_up       = (const unsigned char *) a.w_up;
+    kp.w_gate     = (const unsigned char *) a.w_gate;
+    kp.w_down     = (const unsigned char *) a.w_down_t;
+    kp.b_up       = a.b_up;
+    kp.b_gate     = a.b_gate;
+    kp.x          = a.x;
+    kp.mask       = a.sparse_idx;
+    kp.hid_in     = hid_in;
+    kp.neuron_idx = a.neuron_idx;
+    kp.n_embd     = a.n_embd;
+    kp.n_ff       = a.n_ff;
+    kp.m          = a.m;
+    kp.mask_len   = (a.flags & SPIF_FLAG_MASK_BY_ROW) ? a.m : a.n_ff;
+    kp.V          = a.n_embd / 8;
+    kp.row_bytes  = row_bytes;
+    kp.thr        = a.thr;
+    kp.arch       = a.arch;
+    kp.flags      = a.flags;
+    kp.dense_out  = (mode == SPIF_MODE_GEMV) ? dst_dense : a.hidden_out;
+    kp.trace      = g_spif_trace;
+    kp.magic      = (unsigned int) ((1ull << 32) / (unsigned) P) + 1u;
+    kp.zero_fill  = (mode == SPIF_MODE_GEMV && a.neuron_idx == nullptr && !(a.flags & SPIF_FLAG_MASK_BY_ROW)) ? 1 : 0;
+    kp.list_cap   = (a.m + P - 1) / P + 1;
+    kp.nc         = threads;
+    if (mode == SPIF_MODE_AXPY) {  // the axpy-only op reads its rows from the down pointer
+        kp.w_down = (const unsigned char *) a.w_down_t;
+    }
+
+    const bool gated         = (mode == SPIF_MODE_FUSED) && (a.arch != SPIF_ARCH_RELU_UP);
+    const int  rows_per_slot = (mode == SPIF_MODE_FUSED) ? (gated ? 3 : 2) : 1;
+    const int  slot_bytes    = rows_per_slot * row_bytes;
+    // slots: one per warp at most; half of the SM's shared memory when that still gives 12 slots (the next launch of a PDL
+    // chain can then become resident under this one's tail), else all of it
+    const int nwarp = threads / 32;
+    auto      fit   = [&](size_t budget) {
+        int ns = nwarp;
+        while (ns > 1 && qwarp_smem_layout(kp.list_cap, ns, a.n_embd, slot_bytes).total + 64 > budget) {
+            --ns;
+        }
+        return ns;
+    };
+    const size_t full_b = (size_t) ctx.max_smem_optin - 1024;
+    int          nslot  = fit(full_b / 2 - 1024);
+    if (nslot < 12 && nslot < nwarp) {
+        nslot = fit(full_b);
+    }
+    const QwarpSmem L = qwarp_smem_layout(kp.list_cap, nslot, a.n_embd, slot_bytes);
+    SPIF_REQUIRE(L.total + 64 <= full_b, SPIF_E_UNSUPPORTED);
+    kp.S              = nslot;
+    const size_t smem = L.total + 64;  // + readable pad behind the last slot (odd block counts read one block past a row)
+
+    const size_t part_bytes = sizeof(float) * (size_t) a.n_tok * P * a.n_embd;
+    const size_t stat_bytes = sizeof(int32_t) * (size_t) a.n_tok * P * 2;
+    if (mode != SPIF_MODE_GEMV) {
+        SPIF_REQUIRE(ws != nullptr && ((uintptr_t) ws & 255) == 0 && ws_bytes >= part_bytes + stat_bytes, SPIF_E_WORKSPACE);
+        kp.partials  = (float *) ws;
+        kp.cta_stats = (int32_t *) ((char *) ws + part_bytes);
+    }
+    if (mode == SPIF_MODE_GEMV && !kp.zero_fill) {
+        SPIF_CUDA_TRY(cudaMemsetAsync(dst_dense, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
+    }
+    if (mode == SPIF_MODE_FUSED && a.hidden_out) {
+        SPIF_CUDA_TRY(cudaMemsetAsync(a.hidden_out, 0, sizeof(float) * (size_t) a.n_ff * a.n_tok, ctx.stream));
+    }
+    const dim3 grid(P, a.n_tok);
+    int        rc;
+#define SPIF_QW_GO(QT_)                                                                                          \
+    (ipt == 2       ? launch_qwarp_m<QT_, 2, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :      \
+     threads <= 768 ? launch_qwarp_m<QT_, 1, 768>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :       \
+                      launch_qwarp_m<QT_, 1, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device))
+    rc = (a.type == SPIF_TYPE_Q8_0) ? SPIF_QW_GO(spif_q8_0) : SPIF_QW_GO(spif_q4_0);
+#undef SPIF_QW_GO
+    if (rc) {
+        return rc;
+    }
+    if (mode != SPIF_MODE_GEMV) {
+        return spif_launch_reduce_partials(kp, (mode == SPIF_MODE_FUSED) ? a.b_down : (const float *) nullptr,
+                                           (mode == SPIF_MODE_AXPY) ? dst_dense : a.y, a.stats_out, a.n_embd, a.n_tok, P,
+                                           ctx.stream, (mode == SPIF_MODE_FUSED) ? ctx.comm : nullptr);
+    }
+    return 0;
+}
+
 int spif_launch_ffn_q(const spif_ffn_args & a, int mode, const float * hid_in, float * dst_dense, void * ws,
                       size_t ws_bytes, const spif_launch_ctx & ctx) {
     SPIF_REQUIRE(a.type == SPIF_TYPE_Q8_0 || a.type == SPIF_TYPE_Q4_0, SPIF_E_TYPE);
     // rows are streamed with TMA bulk copies: 16-byte multiples <=> n_embd % 256 == 0 for both block sizes (the
     // reference asserts % 32, mmq-sparse.cu:177; every architecture it supports has n_embd % 256 == 0)
     SPIF_REQUIRE(a.n_embd > 0 && a.n_embd % 256 == 0, SPIF_E_SHAPE);
+    static const int k_ring = [] { const char * e = getenv("SPIF_Q_RING"); return e ? atoi(e) : 0; }();  // 1: round-1 ring kernel
+    if (!k_ring) {
+        const int rc = spif_launch_ffn_qwarp(a, mode, hid_in, dst_dense, ws, ws_bytes, ctx);
+        if (rc != SPIF_E_UNSUPPORTED) {
+            return rc;
+        }
+    }
     const int nblk      = a.n_embd / 32;
     const int row_bytes = nblk * (a.type == SPIF_TYPE_Q8_0 ? 34 : 18);
     const int npairs    = (nblk + 1) / 2;

@@ -149,3 +149,36 @@ def test_unary_ops_vs_reference_formulas():
             ref2 = ((x + tf) > 0).astype(np.float32)
         got2 = sp.shifted_step(dev(x), t).cpu().numpy()
         assert np.array_equal(got2, ref2)
+
+
+# ---- more active neurons per CTA than shared-memory slots: the quantised warp-per-neuron kernel (spif_ffn_qwarp.cuh) works in
+# rounds (gate/up prefetch of the next round, slot and barrier-phase reuse) -- 60 % activity gives ~33 neurons per CTA on 8 slots
+@pytest.mark.parametrize("arch", [ARCH_PROSPARSE, ARCH_RELU_UP])
+@pytest.mark.parametrize("wtype", [Q8_0, Q4_0])
+def test_quant_many_rounds(oracle, wtype, arch):
+    import sparkinfer_b200 as sp
+    n_embd, n_ff, n_tok = 512, 8192, 2
+    seed = synth.SEED0 + 77 + wtype + arch
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(wtype, w) for w in (Wu, Wg, Wd))
+    x = synth.activations(n_embd, n_tok, seed + 1)
+    p = synth.direct_mask(n_ff, n_tok, 0.60, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    gate = None if arch == ARCH_RELU_UP else dev(qg)
+    y_ref, _, _, hid_ref = oracle.sparse_ffn(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)
+    y, hid, stats = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff,
+                                  flags=sp.FLAG_CPU_ROUNDING | sp.FLAG_PER_TOKEN, want_hidden=True, want_stats=True, ws=ws)
+    act = ~(p < 0.5)
+    assert rel_err(y.cpu().numpy(), y_ref) < 2e-4
+    assert rel_err(hid.cpu().numpy() * act, hid_ref * act) < 2e-4
+    assert np.array_equal(stats.cpu().numpy()[:, 0], act.sum(axis=1))
+    assert np.array_equal(stats.cpu().numpy()[:, 1], np.count_nonzero(hid.cpu().numpy(), axis=1))
+    # the two single ops through the same kernel
+    ref_u = oracle.mul_mat_sparse(wtype, qu, x, p, n_embd, n_ff)
+    got_u = sp.mul_mat_sparse(dev(qu), wtype, dev(x), dev(p), flags=sp.FLAG_CPU_ROUNDING, ws=ws).cpu().numpy()
+    assert rel_err(got_u, ref_u) < 3e-5
+    hidv = ref_u.copy()
+    hidv[:, ::3] = 0.0
+    ref_y = oracle.axpy_sparse(wtype, qd, hidv, p, n_embd, n_ff)
+    got_y = sp.axpy_sparse(dev(qd), wtype, dev(hidv), dev(p), n_embd=n_embd, ws=ws).cpu().numpy()
+    assert rel_err(got_y, ref_y) < 3e-5

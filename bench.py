@@ -656,10 +656,19 @@ def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
         blk[:, :, :2] = d.view(torch.uint8).reshape(F, nb, 2)
         return blk.reshape(F, nb * 18).contiguous()
 
+    def q8_rows():  # block_q8_0 = {f16 d, int8 qs[32]} (the quant format the reference's sparse kernels ship: mmq-sparse.cu)
+        nb = E // 32
+        blk = torch.randint(0, 256, (F, nb, 34), dtype=torch.uint8, device=device, generator=gen)
+        d = torch.full((F, nb, 1), 0.02 / 64, dtype=torch.float16, device=device)
+        blk[:, :, :2] = d.view(torch.uint8).reshape(F, nb, 2)
+        return blk.reshape(F, nb * 34).contiguous()
+
     f16 = [(w.up, w.gate, w.down_t) for w in st.layers[:nl]]
     q4 = [(q4_rows(), q4_rows(), q4_rows()) for _ in range(nl)] if E % 512 == 0 else None
+    q8 = [(q8_rows(), q8_rows(), q8_rows()) for _ in range(nl)] if E % 512 == 0 else None
     for wname, wtype, rb, weights, Ts in (("f16", st.w_type, 2 * E, f16, batches),
-                                          ("q4_0", sp.GGML_TYPE_Q4_0, E // 32 * 18, q4, (1,) + tuple(batches))):
+                                          ("q4_0", sp.GGML_TYPE_Q4_0, E // 32 * 18, q4, (1,) + tuple(batches)),
+                                          ("q8_0", sp.GGML_TYPE_Q8_0, E // 32 * 34, q8, (1,) + tuple(batches))):
         if weights is None:
             continue
         for T in Ts:
@@ -670,8 +679,11 @@ def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
                      for w in st.layers[:nl]]
             stats = [torch.zeros((T, 4), dtype=torch.int32, device=device) for _ in range(nl)]
             leg = {"weights": wname, "n_tok": T, "layers_timed": nl}
-            for name, flags in ((("per_token", sp.FLAG_PER_TOKEN),) if T == 1 else
-                                (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN))):
+            # T == 1: "per_token" = every launch waits for its predecessor before it looks at its mask; "mask_stable" = the mask
+            # of layer l exists a whole layer early, as in the reference's look-ahead order (SPIF_FLAG_MASK_STABLE): the kernel
+            # scans it and requests its first rows under the previous launch's tail
+            for name, flags in ((("per_token", sp.FLAG_PER_TOKEN), ("mask_stable", sp.FLAG_PER_TOKEN | sp.FLAG_MASK_STABLE))
+                                if T == 1 else (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN))):
                 def run():
                     for l in range(nl):
                         u, g_, d_ = weights[l]

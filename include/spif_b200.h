@@ -262,6 +262,22 @@ int spif_reorder_rows(const void * src, void * dst, const int32_t * perm, int64_
 int spif_rebalance_plan(const float * dfr, int32_t * shard_of_group, int n_g, int n_shards, int max_swaps, float min_gain,
                         int32_t * plan, int * n_swaps);
 
+/* ---- model-split file (`-ms`): consumer and producer, host code ------------------------------------------------------
+ * The file the reference's cache manager loads (sparkinfer_cache_manager ctor, src/llama-sparkinfer.cpp:150-158, 257,
+ * 269-276): a GGUF v3 container with KV `ffn_group_size` (i32), `ffn_normalized_pattern` (f32[n_layer]) and one tensor
+ * `blk.N.ffn_reorder_perms` (I32 {n_ff}, new_row -> old_row) per layer.  spif_model_split_open parses it (unknown keys and
+ * tensors are skipped); _pattern feeds spif_cache_group_budget, _perm feeds spif_reorder_rows.  The reference has no
+ * producer for this file; spif_model_split_write emits one the unmodified reference loads (tests/test_model_split.py reads
+ * it back with the reference's gguf_init_from_file).  SPIF_E_SHAPE = malformed / truncated file or not a permutation.  */
+typedef struct spif_model_split spif_model_split;
+int  spif_model_split_open(const char * path_host, spif_model_split ** out);
+void spif_model_split_close(spif_model_split * ms);
+int  spif_model_split_info(const spif_model_split * ms, int32_t * group_size, int32_t * n_layer, int32_t * n_ff);
+int  spif_model_split_pattern(const spif_model_split * ms, float * pattern_out_host, int n_layer);
+int  spif_model_split_perm(const spif_model_split * ms, int layer, int32_t * perm_out_host, int n_ff);
+int  spif_model_split_write(const char * path_host, int group_size, const float * pattern_host, int n_layer,
+                            const int32_t * perms_host /* [n_layer][n_ff] */, int n_ff);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,12 @@ SYMBOLS = {
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
     "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),
     "spif_reorder_rows": (c_i, [c_vp, c_vp, c_vp, c_i64, c_i64]),
+    "spif_model_split_open": (c_i, [ctypes.c_char_p, ctypes.POINTER(c_vp)]),
+    "spif_model_split_close": (None, [c_vp]),
+    "spif_model_split_info": (c_i, [c_vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
+    "spif_model_split_pattern": (c_i, [c_vp, c_vp, c_i]),
+    "spif_model_split_perm": (c_i, [c_vp, c_i, c_vp, c_i]),
+    "spif_model_split_write": (c_i, [ctypes.c_char_p, c_i, c_vp, c_i, c_vp, c_i]),
 }
 
 _lib = None

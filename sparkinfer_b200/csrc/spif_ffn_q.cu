@@ -247,8 +247,15 @@ static int spif_launch_ffn_qwarp(const spif_ffn_args & a, int mode, const float 
     SPIF_REQUIRE(a.neuron_idx != nullptr || a.m == a.n_ff, SPIF_E_SHAPE);
     SPIF_REQUIRE(a.sparse_idx != nullptr, SPIF_E_NULL);
     const int n_items = a.n_embd / 8;
-    int       threads = (n_items + 31) / 32 * 32;
-    threads           = threads < 256 ? 256 : (threads > 1024 ? 1024 : threads);
+    // SPIF_QW_HALF=1 (default): half-size CTAs (two column items per thread) whenever that still leaves >= 8 warps, so that
+    // the next launch of a PDL chain fits on the SM beside this one (registers and shared memory) and scans its mask / requests
+    // its first rows under this launch's tail
+    static const int k_half = [] { const char * e = getenv("SPIF_QW_HALF"); return e ? atoi(e) : 1; }();
+    int threads = (n_items + 31) / 32 * 32;
+    if (k_half && threads >= 512) {
+        threads = (n_items / 2 + 31) / 32 * 32;
+    }
+    threads = threads < 256 ? 256 : (threads > 1024 ? 1024 : threads);
     while (a.m > 4096 * (threads / 32) && threads < 1024) {  // activity bits kept in registers by build_my_list
         threads += 32;
     }
@@ -324,7 +331,8 @@ static int spif_launch_ffn_qwarp(const spif_ffn_args & a, int mode, const float 
     const dim3 grid(P, a.n_tok);
     int        rc;
 #define SPIF_QW_GO(QT_)                                                                                          \
-    (ipt == 2       ? launch_qwarp_m<QT_, 2, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :      \
+    (ipt == 2 ? (threads <= 512 ? launch_qwarp_m<QT_, 2, 512>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :  \
+                                  launch_qwarp_m<QT_, 2, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device)) : \
      threads <= 768 ? launch_qwarp_m<QT_, 1, 768>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :       \
                       launch_qwarp_m<QT_, 1, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device))
     rc = (a.type == SPIF_TYPE_Q8_0) ? SPIF_QW_GO(spif_q8_0) : SPIF_QW_GO(spif_q4_0);

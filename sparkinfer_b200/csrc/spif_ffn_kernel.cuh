@@ -59,7 +59,10 @@ __device__ __forceinline__ unsigned long long gtime_ns() {
 // warp scan over per-lane totals instead of one per 32 rows: each warp owns a contiguous chunk, a lane reads the
 // chunk with coalesced 128-bit loads (float4 j of the lane = chunk + 32 j + lane) and packs its activity bits into
 // registers (4 bits per load).  ~200 instructions per warp at n_ff = 13824 instead of ~1500 for the ballot-per-row form.
-template <int MODE, typename C>
+// WIDE: all (up to 16) mask loads of a lane are issued before the first one is used -- one L2 round trip instead of one per
+// unrolled group of 8 plus one per load of the remainder loop (2.6 us -> ~1 us at n_ff = 13824 with 10 warps); costs 64
+// registers at this point of the kernel, so only kernels whose register budget is set elsewhere ask for it.
+template <int MODE, typename C, bool WIDE = false>
 __device__ __forceinline__ void build_my_list(const FfnKParams & p, const float * mask, const float * hid, float * dense,
                                               int * warp_cnt, int * list_row, int * list_neu, float * list_alpha,
                                               int * s_counts) {
@@ -88,6 +91,30 @@ __device__ __forceinline__ void build_my_list(const FfnKParams & p, const float 
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int jn = min(16, q4 - 16 * h);
+            if (WIDE) {
+                if (jn > 0) {
+                    float4 v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int f = base + (16 * h + j) * 32 + lane;
+                        v[j]        = (j < jn) ? __ldg(m4 + min(f, last)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int f  = base + (16 * h + j) * 32 + lane;
+                        unsigned  nb = (spif_is_active(v[j].x, p.thr) ? 1u : 0u) | (spif_is_active(v[j].y, p.thr) ? 2u : 0u) |
+                                      (spif_is_active(v[j].z, p.thr) ? 4u : 0u) | (spif_is_active(v[j].w, p.thr) ? 8u : 0u);
+                        if (MODE == SPIF_MODE_AXPY && j < jn) {
+                            const float4 a = __ldg(h4 + min(f, last));
+                            nb &= (alpha_of(a.x) == 0.0f ? 0u : 1u) | (alpha_of(a.y) == 0.0f ? 0u : 2u) |
+                                  (alpha_of(a.z) == 0.0f ? 0u : 4u) | (alpha_of(a.w) == 0.0f ? 0u : 8u);
+                        }
+                        nb = (j < jn && f <= last) ? nb : 0u;
+                        bits[h] |= (unsigned long long) nb << (4 * j);
+                    }
+                }
+                continue;
+            }
 #pragma unroll 8
             for (int j = 0; j < jn; ++j) {
                 const int    f  = base + (16 * h + j) * 32 + lane;

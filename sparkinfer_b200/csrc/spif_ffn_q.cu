@@ -331,7 +331,8 @@ static int spif_launch_ffn_qwarp(const spif_ffn_args & a, int mode, const float 
     const dim3 grid(P, a.n_tok);
     int        rc;
 #define SPIF_QW_GO(QT_)                                                                                          \
-    (ipt == 2 ? (threads <= 512 ? launch_qwarp_m<QT_, 2, 512>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :  \
+    (ipt == 2 ? (threads <= 320 ? launch_qwarp_m<QT_, 2, 320>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :  \
+                 threads <= 512 ? launch_qwarp_m<QT_, 2, 512>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :  \
                                   launch_qwarp_m<QT_, 2, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device)) : \
      threads <= 768 ? launch_qwarp_m<QT_, 1, 768>(mode, kp, grid, threads, smem, ctx.stream, ctx.device) :       \
                       launch_qwarp_m<QT_, 1, 1024>(mode, kp, grid, threads, smem, ctx.stream, ctx.device))

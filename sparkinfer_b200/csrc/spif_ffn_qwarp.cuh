@@ -70,7 +70,7 @@ static inline __host__ __device__ QwarpSmem qwarp_smem_layout(int list_cap, int 
 }
 
 template <typename QT, int MODE, int IPT, int MAXT>
-__global__ void __launch_bounds__(MAXT, 1) spif_ffn_qwarp_kernel(const FfnKParams p) {
+__global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_kernel(const FfnKParams p) {
     using T = QuantTraits<QT>;
     extern __shared__ __align__(128) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_qwarp_kernel(const FfnKParam
     const float * xg    = p.x + (size_t) tok * p.n_embd;
     const float * hid   = (MODE == SPIF_MODE_AXPY) ? p.hid_in + (size_t) tok * p.n_ff : nullptr;
     float *       dense = p.dense_out ? p.dense_out + (size_t) tok * p.n_ff : nullptr;
-    build_my_list<MODE, QwarpAlpha>(p, mask, hid, dense, warp_cnt, list_row, list_neu, list_alpha, s_counts);  // syncs the CTA
+    build_my_list<MODE, QwarpAlpha, true>(p, mask, hid, dense, warp_cnt, list_row, list_neu, list_alpha, s_counts);  // syncs the CTA
     const int n = s_counts[0];
     SPIF_STAMP(2);
 
@@ -143,36 +143,51 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_qwarp_kernel(const FfnKParam
     }
     pdl_launch_dependents();
 
-    // ---- x -> 8 bit per 32-block, once per CTA: 8 lanes per block, one float4 each (quantize.cu:19-31 / quants.c:290-356)
+    // ---- x -> 8 bit per 32-block, once per CTA: 8 lanes per block, one float4 each (quantize.cu:19-31 / quants.c:290-356).
+    // All of a thread's loads are issued first (XQ = 4 covers every launch shape: threads >= n_embd / 16): the first cut did a
+    // dependent L2 round trip per block group, 3 us of the layer's 10.
     if (MODE != SPIF_MODE_AXPY) {
-        const bool cpu = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
-        const int  wi  = lane & 7;
-        for (int b = (tid >> 3); b < nblk; b += (NT >> 3)) {
-            const float4 v = __ldg(reinterpret_cast<const float4 *>(xg + (size_t) b * 32) + wi);
-            float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+        constexpr int XQ  = 4;
+        const bool    cpu = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
+        const int     wi  = lane & 7, bstep = NT >> 3;
+        for (int b0 = (tid >> 3); b0 < nblk; b0 += XQ * bstep) {
+            float4 xv[XQ];
 #pragma unroll
-            for (int o = 1; o < 8; o <<= 1) {
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            }
-            const float d  = amax / 127.f;
-            const float id = (amax != 0.0f) ? 127.f / amax : 0.0f;
-            const float e4[4] = { v.x, v.y, v.z, v.w };
-            int         s = 0, w = 0;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int q = cpu ? __float2int_rn(e4[e] * id) : ((amax == 0.0f) ? 0 : (int) roundf(e4[e] / d));
-                s += q;
-                w |= (q & 0xff) << (8 * e);
+            for (int u = 0; u < XQ; ++u) {
+                const int b = b0 + u * bstep;
+                xv[u]       = (b < nblk) ? __ldg(reinterpret_cast<const float4 *>(xg + (size_t) b * 32) + wi) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
 #pragma unroll
-            for (int o = 1; o < 8; o <<= 1) {
-                s += __shfl_xor_sync(0xffffffffu, s, o);
-            }
-            const int pr = b >> 1, bb = b & 1;
-            reinterpret_cast<int *>(xq)[((size_t) (bb * 2 + (wi >> 2)) * np + pr) * 4 + (wi & 3)] = w;
-            if (wi == 0) {
-                reinterpret_cast<float *>(xd)[2 * pr + bb] = __half2float(__float2half_rn(d));
-                reinterpret_cast<int *>(xs)[2 * pr + bb]   = s;
+            for (int u = 0; u < XQ; ++u) {
+                const int    b = b0 + u * bstep;  // (b < nblk) is uniform over the 8 lanes of a block and over whole warps' shuffles
+                const float4 v = xv[u];
+                float amax = fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w)));
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                }
+                const float d  = amax / 127.f;
+                const float id = (amax != 0.0f) ? 127.f / amax : 0.0f;
+                const float e4[4] = { v.x, v.y, v.z, v.w };
+                int         sm = 0, w = 0;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int q = cpu ? __float2int_rn(e4[e] * id) : ((amax == 0.0f) ? 0 : (int) roundf(e4[e] / d));
+                    sm += q;
+                    w |= (q & 0xff) << (8 * e);
+                }
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    sm += __shfl_xor_sync(0xffffffffu, sm, o);
+                }
+                if (b < nblk) {
+                    const int pr = b >> 1, bb = b & 1;
+                    reinterpret_cast<int *>(xq)[((size_t) (bb * 2 + (wi >> 2)) * np + pr) * 4 + (wi & 3)] = w;
+                    if (wi == 0) {
+                        reinterpret_cast<float *>(xd)[2 * pr + bb] = __half2float(__float2half_rn(d));
+                        reinterpret_cast<int *>(xs)[2 * pr + bb]   = sm;
+                    }
+                }
             }
         }
         if ((nblk & 1) && tid < 8) {  // odd block count: the missing half of the last pair contributes nothing
@@ -308,6 +323,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_ffn_qwarp_kernel(const FfnKParam
             continue;
         }
         __syncthreads();
+        if (round == 0) {
+            SPIF_STAMP(7);
+        }
         // ---- phase B: every thread adds the landed W_down^T rows into its columns, in list order
         const int cnt = min(NSLOT, n - base);
         for (int s = 0; s < cnt; ++s) {

@@ -212,8 +212,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
         if (warp == 0) {
             LAYER_STAMP(8);
         }
-        const uint32_t ring_s = smem_u32(ring) + (uint32_t) tid * 16u;  // my first vector of slot 0, row 0
-        const uint32_t koff   = (uint32_t) NC * 16u;                    // my next vector (VPT == 2)
+        // my vector(s) of slot 0, row 0.  Threads beyond the end of a row (n_embd / 8 not a multiple of 32, e.g. 1376 or 4544)
+        // hold x == 0 / unsummed h1 lanes and re-read the row's LAST vector: bytes beyond the row belong to the next row, the next
+        // slot or stale shared memory, and a NaN bit pattern there times their zero made the whole dot NaN -- which the ReLU-type
+        // activations then turned into a silent hidden == 0 (seen as a flaky parity failure at 1376 x 2048 in round 2)
+        const uint32_t ring_s = smem_u32(ring) + min((uint32_t) tid * 16u, row_bytes - 16u);
+        const uint32_t koff   = min((uint32_t) (tid + NC) * 16u, row_bytes - 16u) - min((uint32_t) tid * 16u, row_bytes - 16u);  // my next vector (VPT == 2)
         bool           h1_ready = false;
         int            kseq = 0, qc = 0;
         uint32_t       slot_s = ring_s;

@@ -62,7 +62,11 @@ def test_lookahead_ffn_only(oracle, arch, wtype, n_embd, n_ff):
                                                    down_b=dev(b_down), flags=flags, out=y, hidden_out=hid, stats=stats),
                                 list_in=lst)
         y, hid, stats = y.cpu().numpy(), hid.cpu().numpy(), stats.cpu().numpy()
-        assert rel_err(y, y_ref[0]) < tol, (TYPE_NAMES[wtype], arch, flags, rel_err(y, y_ref[0]))
+        if not rel_err(y, y_ref[0]) < tol:  # diagnosis of a failure: is it the list, a hidden value or the sum over CTAs?
+            wrong_h = np.nonzero(np.abs(hid - hid_ref[0] * act[0]) > 1e-3 * np.abs(hid_ref).max())[0]
+            raise AssertionError((TYPE_NAMES[wtype], arch, flags, rel_err(y, y_ref[0]), "stats", stats.tolist(), "active",
+                                  int(act.sum()), "list ok", lst.rows() == np.nonzero(act[0])[0].tolist(), "hidden wrong at",
+                                  wrong_h[:8].tolist(), "columns off", int((np.abs(y - y_ref[0]) > tol * np.abs(y_ref).max()).sum())))
         assert rel_err(hid * act[0], hid_ref[0] * act[0]) < (2e-5 if flags else TOL[wtype])
         assert np.all(hid[~act[0]] == 0.0)
         assert stats[0] == act.sum()

@@ -278,6 +278,36 @@ int  spif_model_split_perm(const spif_model_split * ms, int layer, int32_t * per
 int  spif_model_split_write(const char * path_host, int group_size, const float * pattern_host, int n_layer,
                             const int32_t * perms_host /* [n_layer][n_ff] */, int n_ff);
 
+/* ---- online shard balancer: host-side state (plan -> exec -> anchor) ----------------------------------------------------
+ * Counterpart of the reference's per-layer cache state (cache_meta, group_maps, dfr_decay_pack: src/llama-sparkinfer.h,
+ * ggml/include/ggml-sparkinfer.hpp:16-24) and of the plan / exec / anchor split of ggml_sparkinfer_reload
+ * (ggml/src/ggml-cuda/ggml-cuda.cu:2499-2606, lambda adaptation ggml-sparkinfer.hpp:143-175), re-targeted to GPU shards:
+ * every rank holds an identical spif_balancer (the plan depends on all-gathered scores only, so no coordinator is needed).
+ *   create   slot s of shard r initially holds the s-th smallest group id with shard_of_group[layer][g] == r;
+ *   plan     slot_scores_host = the all-gathered decayed firing rates [n_shards][n_layer][n_slot] (spif_dfr_update output of
+ *            every shard).  Per layer: spif_rebalance_plan, then the moves THIS rank executes, ordered by (round, layer) --
+ *            both ends of a move see the same order.  The new tables are pending; lambda adapts: raised (x (1 + step)) when the
+ *            balance the previous plan promised did not hold (mean imbalance now > promised x (1 + drift_tol)), else lowered,
+ *            clamped to [0.05, 0.95].  SPIF_E_WORKSPACE: moves_cap too small, *n_moves = entries needed, nothing pending;
+ *   exec     the caller moves, per move, the g rows of up / gate / down^T / predictor-down (+ bias, + score) of `slot`
+ *            to `peer` and receives the peer's into the same slot (device work: NVLink send/recv or peer copies);
+ *   commit   (anchor) the pending tables become current; abort drops them.                                              */
+typedef struct spif_balancer spif_balancer;
+typedef struct spif_move {
+    int32_t layer, round;         /* swap `round` of `layer` */
+    int32_t slot, peer;           /* my slot whose group leaves / arrives; the other shard */
+    int32_t group_out, group_in;  /* group ids (for logging / checks) */
+} spif_move;
+int  spif_balancer_create(int n_layer, int n_g, int n_shards, int rank, const int32_t * shard_of_group_host /* [n_layer][n_g] */,
+                          float lambda0, float lambda_step, float drift_tol, spif_balancer ** out);
+void spif_balancer_destroy(spif_balancer * b);
+int  spif_balancer_slots(const spif_balancer * b, int layer, int32_t * slots_out_host /* [n_shards][n_slot] -> group id */);
+int  spif_balancer_state(const spif_balancer * b, float * lambda, int64_t * swaps_done, int * has_pending);
+int  spif_balancer_plan(spif_balancer * b, const float * slot_scores_host, int max_swaps, float min_gain, spif_move * moves_out,
+                        int moves_cap, int * n_moves, float * imbalance_before, float * imbalance_after, int * n_swaps_total);
+int  spif_balancer_commit(spif_balancer * b);
+int  spif_balancer_abort(spif_balancer * b);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,14 @@ SYMBOLS = {
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
     "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),
     "spif_reorder_rows": (c_i, [c_vp, c_vp, c_vp, c_i64, c_i64]),
+    "spif_balancer_create": (c_i, [c_i, c_i, c_i, c_i, c_vp, c_f, c_f, c_f, ctypes.POINTER(c_vp)]),
+    "spif_balancer_destroy": (None, [c_vp]),
+    "spif_balancer_slots": (c_i, [c_vp, c_i, c_vp]),
+    "spif_balancer_state": (c_i, [c_vp, ctypes.POINTER(c_f), ctypes.POINTER(c_i64), ctypes.POINTER(c_i)]),
+    "spif_balancer_plan": (c_i, [c_vp, c_vp, c_i, c_f, c_vp, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_f), ctypes.POINTER(c_f),
+                                 ctypes.POINTER(c_i)]),
+    "spif_balancer_commit": (c_i, [c_vp]),
+    "spif_balancer_abort": (c_i, [c_vp]),
     "spif_model_split_open": (c_i, [ctypes.c_char_p, ctypes.POINTER(c_vp)]),
     "spif_model_split_close": (None, [c_vp]),
     "spif_model_split_info": (c_i, [c_vp, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),

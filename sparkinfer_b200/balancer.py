@@ -10,15 +10,18 @@ addresses never change, captured CUDA graphs stay valid.
 
 Division of labour:
   observe()    one spif_dfr_update launch per layer on this rank's masks  (CUDA, C-ABI)
-  scores()     all_gather of the per-slot scores -> global score per group (torch.distributed)
-  rebalance()  spif_rebalance_plan per layer (host code in the library, identical on every rank) + the row exchange
+  slot_scores  all_gather of the per-slot scores (torch.distributed)
+  rebalance()  spif_balancer_plan (host C++ in the library: slot tables, per-layer spif_rebalance_plan, adaptive decay, the
+               moves of this rank) -> the row exchange (NCCL send/recv) -> spif_balancer_commit (the anchor)
 The plan only depends on gathered data, so every rank derives the same one without a coordinator.
 """
+import ctypes
+
 import numpy as np
 import torch
 import torch.distributed as dist
 
-from . import placement
+from . import _lib, placement
 
 
 def _row_bytes(t, rows):
@@ -27,8 +30,16 @@ def _row_bytes(t, rows):
     return n // rows
 
 
+class Move(ctypes.Structure):
+    """struct spif_move (include/spif_b200.h)"""
+    _fields_ = [("layer", ctypes.c_int32), ("round", ctypes.c_int32), ("slot", ctypes.c_int32), ("peer", ctypes.c_int32),
+                ("group_out", ctypes.c_int32), ("group_in", ctypes.c_int32)]
+
+
 class ShardBalancer:
-    """keeps slot -> group maps of every layer and shard, the decayed firing rates, and moves groups between shards"""
+    """Executor around the library's spif_balancer (host C++: slot tables of every layer and shard, swap plans, adaptive decay,
+    pending / committed state).  This class owns only the device side: the decayed firing rates (one spif_dfr_update launch per
+    layer), the all-gather of the scores, and the row exchange of the planned moves over NCCL send/recv."""
 
     LAYER_CHUNK = 16
 
@@ -36,27 +47,51 @@ class ShardBalancer:
         """layers: this rank's LayerWeights (m rows each); shard_of_group: per layer int array [n_g] (same on all ranks).
         Slot s of shard r initially holds the s-th smallest group id placed on r (placement.shard_rows order)."""
         self.layers, self.rank, self.world, self.group = layers, rank, world, group
-        self.g, self.lam = g, lam
-        # adaptive decay (ggml-sparkinfer.hpp:169-173: lambda *= 1 +- SPIF_DX_DFR_DECAY/1000, clamped to [0.05, 0.95], raised
-        # when the compute had to wait for reloads, lowered otherwise).  Re-targeted: raised when the balance the last plan
-        # promised did not hold until this round (the scores were too jumpy and the swaps were wasted), lowered otherwise.
-        self.lam_step, self.drift_tol = lam_step, drift_tol
-        self._promised = None
+        self.g = g
         self.L = len(layers)
         self.n_slot = layers[0].m // g
-        self.slots = []  # per layer: int32 [world, n_slot] = group id held by each slot of each shard
-        for sog in shard_of_group:
-            sog = np.asarray(sog)
-            tab = np.stack([np.nonzero(sog == r)[0] for r in range(world)]).astype(np.int32)
-            assert tab.shape == (world, self.n_slot), "equal group count per shard"
-            self.slots.append(tab)
+        self.n_g = self.n_slot * world
+        sog = np.ascontiguousarray(np.stack([np.asarray(s) for s in shard_of_group]), dtype=np.int32)
+        assert sog.shape == (self.L, self.n_g), "equal group count per shard"
+        self._lib = _lib.load()
+        self._h = ctypes.c_void_p()
+        _lib.check(self._lib.spif_balancer_create(self.L, self.n_g, world, rank, sog.ctypes.data, float(lam), float(lam_step),
+                                                  float(drift_tol), ctypes.byref(self._h)), "spif_balancer_create")
         dev = layers[0].up.device
         self.dfr = torch.zeros((self.L, self.n_slot), dtype=torch.float32, device=dev)  # per local slot
         self.tokens_seen = 0
-        self.swaps_done = 0
         self.bytes_moved = 0
 
-    # -- bookkeeping --------------------------------------------------------------------------------------------
+    def __del__(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.spif_balancer_destroy(self._h)
+            self._h = None
+
+    # -- bookkeeping (state lives in the library) ----------------------------------------------------------------------
+    @property
+    def slots(self):
+        """per layer int32 [world, n_slot]: the group id held by each slot of each shard (committed state)"""
+        out = []
+        for l in range(self.L):
+            tab = np.empty((self.world, self.n_slot), dtype=np.int32)
+            _lib.check(self._lib.spif_balancer_slots(self._h, l, tab.ctypes.data), "spif_balancer_slots")
+            out.append(tab)
+        return out
+
+    def _state(self):
+        lam, swaps, pend = ctypes.c_float(0), ctypes.c_int64(0), ctypes.c_int(0)
+        _lib.check(self._lib.spif_balancer_state(self._h, ctypes.byref(lam), ctypes.byref(swaps), ctypes.byref(pend)),
+                   "spif_balancer_state")
+        return lam.value, swaps.value, pend.value
+
+    @property
+    def lam(self):
+        return self._state()[0]
+
+    @property
+    def swaps_done(self):
+        return self._state()[1]
+
     def shard_of_group(self, l):
         tab = self.slots[l]
         sog = np.empty(tab.size, dtype=np.int32)
@@ -71,24 +106,28 @@ class ShardBalancer:
     def observe(self, masks):
         """masks: [L, n_tok, m] activation probabilities of this rank's rows (FfnStack.p).  One launch per layer."""
         from . import ops
+        lam = self.lam
         for l in range(self.L):
-            ops.dfr_update(masks[l], self.dfr[l], self.g, self.lam)
+            ops.dfr_update(masks[l], self.dfr[l], self.g, lam)
         self.tokens_seen += int(masks.shape[1])
         return self.L
 
-    def scores(self):
-        """-> per layer float64 [n_g]: the score of every group, assembled from every shard's slots"""
+    def slot_scores(self):
+        """-> float32 [world, L, n_slot]: every shard's per-slot scores (all-gathered)"""
         if self.world > 1:
             parts = [torch.empty_like(self.dfr) for _ in range(self.world)]
             dist.all_gather(parts, self.dfr, group=self.group)
-            allv = torch.stack(parts).cpu().numpy()  # [world, L, n_slot]
-        else:
-            allv = self.dfr.cpu().numpy()[None]
-        out = []
+            return np.ascontiguousarray(torch.stack(parts).cpu().numpy(), dtype=np.float32)
+        return np.ascontiguousarray(self.dfr.cpu().numpy()[None], dtype=np.float32)
+
+    def scores(self, allv=None):
+        """-> per layer float64 [n_g]: the score of every group, assembled from every shard's slots"""
+        allv = self.slot_scores() if allv is None else allv
+        out, slots = [], self.slots
         for l in range(self.L):
-            d = np.zeros(self.slots[l].size, dtype=np.float64)
+            d = np.zeros(self.n_g, dtype=np.float64)
             for r in range(self.world):
-                d[self.slots[l][r]] = allv[r, l]
+                d[slots[l][r]] = allv[r, l]
             out.append(d)
         return out
 
@@ -122,58 +161,46 @@ class ShardBalancer:
             o += n
         self.dfr[l, slot:slot + 1].view(torch.uint8).reshape(-1).copy_(buf[o:o + 4])
 
-    def apply(self, plans):
-        """plans: per layer list of (group_a, group_b, hot_shard, cold_shard) from placement.rebalance_plan.
-        Swap k of every layer forms one round (a group may move again in a later swap of the same layer, so the
-        swaps of one layer are ordered; different layers are independent and share the round's send/recv batch)."""
-        n_round = max((len(p) for p in plans), default=0)
-        moved = 0
-        # one send/recv batch = swap k of LAYER_CHUNK consecutive layers (bounds the ops per NCCL group and the staging memory;
-        # the chunking is by layer index, so both ends of every pair cut their op lists at the same places)
-        work = [(k, c) for k in range(n_round) for c in range(0, self.L, self.LAYER_CHUNK)]
-        for k, c0 in work:
+    def apply(self, moves):
+        """moves: this rank's spif_move list, sorted by (round, layer) by the library.  One send/recv batch = the moves of one
+        round within LAYER_CHUNK consecutive layers (bounds the ops per NCCL group and the staging memory; the chunking is by
+        (round, layer), so both ends of every pair cut their op lists at the same places)."""
+        moved, i = 0, 0
+        while i < len(moves):
+            k, c0 = moves[i].round, moves[i].layer // self.LAYER_CHUNK
             ops_, post = [], []
-            for l in range(c0, min(c0 + self.LAYER_CHUNK, self.L)):
-                plan = plans[l]
-                if k >= len(plan):
-                    continue
-                a, b, hot, cold = plan[k]
-                tab = self.slots[l]
-                sa = int(np.nonzero(tab[hot] == a)[0][0])
-                sb = int(np.nonzero(tab[cold] == b)[0][0])
-                if self.rank in (hot, cold):
-                    mine, peer = (sa, cold) if self.rank == hot else (sb, hot)
-                    out = self._pack(l, mine)
-                    inc = torch.empty_like(out)
-                    ops_.append(dist.P2POp(dist.isend, out, peer, group=self.group))
-                    ops_.append(dist.P2POp(dist.irecv, inc, peer, group=self.group))
-                    post.append((l, mine, inc, out))
-                    moved += out.numel()
-                tab[hot, sa], tab[cold, sb] = b, a
-                self.swaps_done += 1
-            if ops_:
-                for r in dist.batch_isend_irecv(ops_):
-                    r.wait()
-                for l, slot, inc, _keep in post:
-                    self._unpack(l, slot, inc)
+            while i < len(moves) and moves[i].round == k and moves[i].layer // self.LAYER_CHUNK == c0:
+                mv = moves[i]
+                out = self._pack(mv.layer, mv.slot)
+                inc = torch.empty_like(out)
+                ops_.append(dist.P2POp(dist.isend, out, mv.peer, group=self.group))
+                ops_.append(dist.P2POp(dist.irecv, inc, mv.peer, group=self.group))
+                post.append((mv.layer, mv.slot, inc, out))
+                moved += out.numel()
+                i += 1
+            for r in dist.batch_isend_irecv(ops_):
+                r.wait()
+            for l, slot, inc, _keep in post:
+                self._unpack(l, slot, inc)
         self.bytes_moved += moved
         return moved
 
     def rebalance(self, max_swaps=8, min_gain=0.0):
-        """gather scores, plan per layer, execute.  -> dict(imbalance_before, imbalance_after (planned), swaps, bytes)"""
-        sc = self.scores()
-        before = self.imbalance(sc)
-        if self.lam_step > 0.0 and self._promised is not None:
-            drifted = float(np.mean(before)) > self._promised * (1.0 + self.drift_tol)
-            self.lam = float(np.clip(self.lam * (1.0 + (self.lam_step if drifted else -self.lam_step)), 0.05, 0.95))
-        from . import ops
-        plans = []
-        for l in range(self.L):  # planner = host code inside the library (spif_rebalance_plan); placement.py mirrors it
-            plan, _ = ops.rebalance_plan(sc[l], self.shard_of_group(l), self.world, max_swaps, min_gain)
-            plans.append(plan)
-        moved = self.apply(plans) if self.world > 1 else 0
-        after = [placement.imbalance(sc[l], self.shard_of_group(l), self.world) for l in range(self.L)]
-        self._promised = float(np.mean(after))
-        return {"lambda": self.lam,
-                "imbalance_before": float(np.mean(before)), "imbalance_after": float(np.mean(after)),
-                "swaps": int(sum(len(p) for p in plans)), "bytes_sent_this_rank": int(moved)}
+        """gather scores -> spif_balancer_plan (plans of every layer, adaptive decay, pending tables) -> row exchange ->
+        spif_balancer_commit.  -> dict(lambda, imbalance_before, imbalance_after (planned), swaps, bytes)"""
+        allv = self.slot_scores()
+        cap = max(1, 2 * int(max_swaps) * self.L)
+        moves = (Move * cap)()
+        n, tot = ctypes.c_int(0), ctypes.c_int(0)
+        before, after = ctypes.c_float(0), ctypes.c_float(0)
+        _lib.check(self._lib.spif_balancer_plan(self._h, allv.ctypes.data, int(max_swaps), float(min_gain), moves, cap,
+                                                ctypes.byref(n), ctypes.byref(before), ctypes.byref(after), ctypes.byref(tot)),
+                   "spif_balancer_plan")
+        try:
+            moved = self.apply([moves[i] for i in range(n.value)]) if self.world > 1 else 0
+        except Exception:
+            self._lib.spif_balancer_abort(self._h)
+            raise
+        _lib.check(self._lib.spif_balancer_commit(self._h), "spif_balancer_commit")
+        return {"lambda": self.lam, "imbalance_before": float(before.value), "imbalance_after": float(after.value),
+                "swaps": int(tot.value), "bytes_sent_this_rank": int(moved)}

@@ -172,7 +172,20 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
                 int         sm = 0, w = 0;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const int q = cpu ? __float2int_rn(e4[e] * id) : ((amax == 0.0f) ? 0 : (int) roundf(e4[e] / d));
+                    // default = the CUDA reference's roundf(x / d) (quantize.cu:29).  x * id is within 1.1e-5 of x / d for
+                    // |x / d| <= 127, so the two round alike unless x * id is that close to a half-integer: only then divide
+                    // (the IEEE division was a third of the x stage's instructions).  Bit-identical to roundf(x / d).
+                    int q;
+                    if (cpu) {
+                        q = __float2int_rn(e4[e] * id);
+                    } else {
+                        const float t = e4[e] * id;
+                        float       r = roundf(t);
+                        if (fabsf(fabsf(t - truncf(t)) - 0.5f) < 1e-4f) {
+                            r = roundf(e4[e] / d);
+                        }
+                        q = (int) r;  // amax == 0: id == 0 -> t == 0 -> q == 0
+                    }
                     sm += q;
                     w |= (q & 0xff) << (8 * e);
                 }

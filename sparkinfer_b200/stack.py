@@ -44,7 +44,7 @@ class FfnStack:
         if group is not None and exchange == "peer":
             try:
                 comm = ops.ShardComm(n_tok * n_embd + r, group, device)
-            except Exception as e:  # symmetric memory not available here: every rank must take the same decision
+            except RuntimeError as e:  # symmetric memory not available here: every rank must take the same decision
                 comm = None
                 print(f"[sparkinfer_b200] peer exchange unavailable ({type(e).__name__}: {e}); using ncclAllReduce", flush=True)
             ok = torch.tensor([1 if comm is not None else 0], device=device)

@@ -290,3 +290,97 @@ def test_c_abi_cache_budget_and_reorder():
     assert np.array_equal(out, bias[perm])
     perm[3] = n                                                                            # out of range -> error, no write
     assert L.spif_reorder_rows(src.ctypes.data, dst.ctypes.data, perm.ctypes.data, n, rb) != 0
+
+
+def test_balancer_state_machine_c_abi():
+    """spif_balancer (host C++): plan -> pending, commit / abort, the moves of both ends of every swap mirror each other, the
+    tables stay a partition, lambda follows ggml-sparkinfer.hpp:169-173 re-targeted (promise held -> lower, drifted -> raise)"""
+    import ctypes
+    from sparkinfer_b200 import _lib, placement
+    from sparkinfer_b200.balancer import Move
+    L = _lib.load()
+    n_layer, n_g, world = 3, 24, 4
+    n_slot = n_g // world
+    rng = np.random.default_rng(12)
+    sog = np.stack([np.arange(n_g) // n_slot for _ in range(n_layer)]).astype(np.int32)       # contiguous = unbalanced
+    hot = [np.sort(rng.random(n_g))[::-1].astype(np.float32) for _ in range(n_layer)]           # hottest groups on shard 0
+
+    def make(rank):
+        h = ctypes.c_void_p()
+        assert L.spif_balancer_create(n_layer, n_g, world, rank, sog.ctypes.data, 0.9, 0.05, 0.02, ctypes.byref(h)) == 0
+        return h
+
+    def slots(h):
+        out = []
+        for l in range(n_layer):
+            t = np.empty((world, n_slot), np.int32)
+            assert L.spif_balancer_slots(h, l, t.ctypes.data) == 0
+            out.append(t)
+        return out
+
+    def slot_scores(tabs, hotness):
+        s = np.empty((world, n_layer, n_slot), np.float32)
+        for l in range(n_layer):
+            for r in range(world):
+                s[r, l] = hotness[l][tabs[l][r]]
+        return s
+
+    def plan(h, scores, max_swaps, cap=256):
+        mv = (Move * cap)()
+        n, tot, b, a = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_float(0), ctypes.c_float(0)
+        rc = L.spif_balancer_plan(h, scores.ctypes.data, max_swaps, 0.0, mv, cap, ctypes.byref(n), ctypes.byref(b), ctypes.byref(a),
+                                  ctypes.byref(tot))
+        return rc, [mv[i] for i in range(min(n.value, cap))], n.value, b.value, a.value, tot.value
+
+    hs = [make(r) for r in range(world)]
+    bad = sog.copy()
+    bad[0, 0] = 1                                                                               # unequal split is rejected
+    h_bad = ctypes.c_void_p()
+    assert L.spif_balancer_create(n_layer, n_g, world, 0, bad.ctypes.data, 0.9, 0.05, 0.02, ctypes.byref(h_bad)) != 0
+    sc = slot_scores(slots(hs[0]), hot)
+    rc, _, need, _, _, _ = plan(hs[0], sc, 5, cap=1)
+    assert rc == -4 and need > 1                                                                # SPIF_E_WORKSPACE, nothing pending
+    res = [plan(h, sc, 5) for h in hs]
+    assert all(r[0] == 0 for r in res)
+    before, after, total = res[0][3], res[0][4], res[0][5]
+    assert after < before and total > 0 and all((r[3], r[4], r[5]) == (before, after, total) for r in res)
+    ref_before = np.mean([placement.imbalance(hot[l].astype(np.float64), sog[l], world) for l in range(n_layer)])
+    assert abs(before - ref_before) < 1e-5
+    # every swap appears once on each of its two ranks, mirrored, at the same (round, layer); ordering is (round, layer)
+    seen = {}
+    for rank, r in enumerate(res):
+        keys = [(m.round, m.layer) for m in r[1]]
+        assert keys == sorted(keys)
+        for m in r[1]:
+            seen.setdefault((m.round, m.layer), []).append((rank, m.peer, m.group_out, m.group_in))
+    assert sum(len(v) for v in seen.values()) == 2 * total
+    for v in seen.values():
+        (r0, p0, o0, i0), (r1, p1, o1, i1) = v
+        assert (r0, p0, o0, i0) == (p1, r1, i1, o1)
+    # pending until commit; a second plan before commit / abort is refused
+    assert all(np.array_equal(a, b) for a, b in zip(slots(hs[0]), [sog[l].reshape(world, n_slot) * 0 + np.arange(n_g).reshape(world, n_slot) for l in range(n_layer)]))
+    assert plan(hs[0], sc, 5)[0] != 0
+    assert L.spif_balancer_abort(hs[0]) == 0 and L.spif_balancer_commit(hs[0]) != 0
+    assert plan(hs[0], sc, 5)[0] == 0                                                           # (lambda: promise held -> lowered)
+    for h in hs:
+        assert L.spif_balancer_commit(h) == 0
+    tabs = slots(hs[1])
+    for l in range(n_layer):
+        assert sorted(tabs[l].reshape(-1).tolist()) == list(range(n_g))
+        # the committed tables realise the planned balance
+    got_after = np.mean([placement.imbalance(hot[l].astype(np.float64), np.argsort(tabs[l].reshape(-1)) // n_slot, world)
+                         for l in range(n_layer)])
+    assert abs(got_after - after) < 1e-5
+    assert all(np.array_equal(a, b) for a, b in zip(slots(hs[0]), slots(hs[3])))
+    lam = ctypes.c_float(0)
+    assert L.spif_balancer_state(hs[1], ctypes.byref(lam), None, None) == 0 and abs(lam.value - 0.9) < 1e-7   # first plan: no history
+    # the promise holds -> lambda lowered; then the hotness flips -> drifted -> raised
+    rc = plan(hs[1], slot_scores(slots(hs[1]), hot), 5)
+    assert rc[0] == 0 and L.spif_balancer_commit(hs[1]) == 0
+    assert L.spif_balancer_state(hs[1], ctypes.byref(lam), None, None) == 0 and abs(lam.value - 0.9 * 0.95) < 1e-6
+    flipped = [h_[::-1].copy() for h_ in hot]
+    rc = plan(hs[1], slot_scores(slots(hs[1]), flipped), 5)
+    assert rc[0] == 0 and L.spif_balancer_state(hs[1], ctypes.byref(lam), None, None) == 0
+    assert abs(lam.value - 0.9 * 0.95 * 1.05) < 1e-6
+    for h in hs:
+        L.spif_balancer_destroy(h)

@@ -74,6 +74,7 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the reference-CUDA-kernels leg (oracle/_ref/libspif_refcuda.so)")
     ap.add_argument("--no-scale-70b", action="store_true", help="N > 1: skip the relullama-70b scaling leg")
+    ap.add_argument("--no-other-configs", action="store_true", help="N = 1: skip the prosparse-7b / llama3-8b-topk quick legs")
     ap.add_argument("--activations", default="f32", choices=["f32", "weight"],
                     help="f32: x / hidden values stay F32 (flags 0); weight: rounded to the weight type like the reference CPU "
                          "ops, ggml-cpu.c:1832-1856 (SPIF_FLAG_CPU_ROUNDING): exact f16 x f16 products, F32 accumulation")
@@ -380,7 +381,7 @@ def run_ours(a):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "B200_PROFILING.md fallback 6650"
     traffic = None
-    if world == 1:  # the ncu capture is of the single-GPU launch; at N > 1 the per-launch bytes differ, so no constant is quoted
+    if world == 1 and a.workload == "prosparse-13b" and a.rho == 0.10 and a.rank == 1024:  # the ncu capture is of exactly this launch
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_top_kernel.json")))
             if (tj.get("kernel", "").startswith("spif_layer")) == fused:
@@ -398,6 +399,13 @@ def run_ours(a):
             sys.stderr.flush()
             os._exit(0)
 
+    # N = 1: the other single-GPU configurations of BASELINE.json (configs[0] architecture and configs[3]) as quick legs, so
+    # that the driver's default run records them too (same schedule, same timing rules, parity on 2 layers each)
+    other_configs = []
+    if world == 1 and not a.no_other_configs and a.workload == "prosparse-13b":
+        for name in ("prosparse-7b", "llama3-8b-topk"):
+            torch.cuda.empty_cache()
+            other_configs.append(quick_leg(a, name, rank, world, device, barrier))
     scale_70b = None
     if world > 1 and not a.no_scale_70b and a.workload == "prosparse-13b":
         # the north-star's scaling target (BASELINE.json configs[4]): ReluLLaMA-70B neuron-sharded over the same ranks
@@ -422,7 +430,7 @@ def run_ours(a):
         n_launch = L + 1
         bytes_launch = (ffn_bytes + pred_bytes) / n_launch
         us_launch = ms_step0 * 1e3 / n_launch
-        kname = "spif_layer_kernel<f16> (sparse FFN of layer l + predictor of layer l+1 + list + sum over CTAs%s): one spif_sparse_ffn_lookahead call" % (
+        kname = "spif_layer4_kernel<f16> (sparse FFN of layer l + predictor of layer l+1 + list + sum over CTAs%s): one spif_sparse_ffn_lookahead call" % (
             " + shard exchange" if world > 1 else "")
     else:
         bytes_launch, us_launch = ffn_bytes / L, ms_ffn * 1e3 / L
@@ -467,6 +475,8 @@ def run_ours(a):
     }
     if scale_70b is not None:
         out["scale_70b"] = scale_70b
+    if other_configs:
+        out["other_configs"] = other_configs
     if world == 1 and not a.no_gpu_baseline:
         out["gpu_baseline"] = gpu_baseline(a, st, wl, x_pool[0], device)
     if world == 1 and not a.no_batched:
@@ -550,7 +560,8 @@ def quick_leg(a, workload, rank, world, device, barrier):
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=device)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item()) / steps
     parity = parity_check(a2, st, wl, x_pool[0], g, step_stats, rank, world, device, n_layers=2) if not a.no_parity else None
     ffn_bytes = float(((2 * A_all[0] + Z_all[0]) * 2 * E).sum())

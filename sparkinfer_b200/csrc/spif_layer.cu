@@ -222,11 +222,20 @@ __device__ __noinline__ float4 layer_allreduce_f4(const spif_comm_dev & c, uint3
 
 template <bool WIDE>
 __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t, int nthr, int bar_id, float4 * scratch,
-                                                   uint32_t seq, int G) {
+                                                   uint32_t seq, int G, unsigned target = 0) {
     const int P = gridDim.x, c = blockIdx.x, lane = t & 31;
+    // b_down of my column: requested before the wait below instead of on the path between the sum and the store of y
+    float4 bb_pre = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (WIDE && t < 64 && (t & 3) == 0 && p.b_down) {
+        const int n4p = p.n_embd >> 2, c0p = share(c, n4p, P), c1p = share(c + 1, n4p, P);
+        if ((t >> 2) < c1p - c0p) {
+            bb_pre = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0p + (t >> 2));
+        }
+    }
     if (t == 0) {  // every CTA has published its partial y
         unsigned spins = 0;
-        while (ld_u32_acquire_gpu(p.comm.seq + 3) < (unsigned) P) {
+        const unsigned want = target ? target : (unsigned) P;  // publications expected (one per CTA, or one per warp of every CTA)
+        while (ld_u32_acquire_gpu(p.comm.seq + 3) < want) {
             if (++spins > SPIF_COMM_SPIN_LIMIT) {
                 atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
                 break;
@@ -275,8 +284,7 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
             if (j == 0) {
                 const bool own = c2 < ncol;
                 if (own && p.b_down) {
-                    const float4 bb = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0 + c2);
-                    a.x += bb.x, a.y += bb.y, a.z += bb.z, a.w += bb.w;
+                    a.x += bb_pre.x, a.y += bb_pre.y, a.z += bb_pre.z, a.w += bb_pre.w;
                 }
                 a = layer_allreduce_f4(p.comm, seq, a, c0 + c2, own);
                 if (own) {

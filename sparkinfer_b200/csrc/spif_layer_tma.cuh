@@ -14,6 +14,15 @@
 
 #define SPIF_L4_K 16 /* depth of the partial-dot ring (reduce items between the consumer warps and the epilogue warp) */
 
+// extra clock64 stamps of the traced instantiation: [500] epilogue sees the last gate/up item complete, [501] epilogue has
+// published the final W_down^T table, [502] producer first sees it, [504] helper: every warp has stored its partial y
+#define CLK_STAMP(idx)                                                                              \
+    do {                                                                                            \
+        if (TRACE && p.trace && lane == 0) {                                                        \
+            p.trace[(size_t) blockIdx.x * 512 + (idx)] = (unsigned long long) clock64();            \
+        }                                                                                           \
+    } while (0)
+
 struct Layer4Smem {
     uint32_t ring, full, empty, sdesc, done, part, ctl, list_row, list_neu, list_bu, list_bg, tab_a, tab_b, tab_c, tab_d, bpu_s,
         bpd_s, lout_s, h1_s, blk_pre, total;
@@ -128,6 +137,11 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
 
     const bool gated    = (p.arch != SPIF_ARCH_RELU_UP);
     const bool rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
+    // experiment switches (SPIF_LAYER_DEBUG): bit 1 = consumer warps finish every gate/up and W_down^T item in lockstep (no
+    // warp runs ahead into filler Wpd items while a slower warp still holds up the hidden values); bit 2 = every warp publishes
+    // its own slice of the partial y (fence + counter) instead of one helper thread after a CTA-wide hand-off
+    const bool lockstep = (p.dbg & 2) != 0;
+    const bool pub_warp = (p.dbg & 4) != 0;
     const int  world    = p.comm.world;
     const int  h1_off   = p.n_embd;  // h1 words live behind the y words of a slot
     uint32_t   seq      = 0;
@@ -281,6 +295,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                     if (lane == 0) {
                         mbar_arrive(&empty[s]);  // my rows are in registers / consumed: the slot can be refilled
                     }
+                    if (lockstep) {
+                        named_bar_sync(2, NC);
+                    }
                 } else {
                     if (ty == T_DOTH && !h1_ready) {
                         // the hidden vector of the predictor, gathered by the helper warps while the rows above streamed
@@ -337,6 +354,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                         mbar_arrive(&done[ks]);
                     }
                     ++kseq;
+                    if (lockstep && d.w == 2) {  // name 2 = gate/up rows
+                        named_bar_sync(2, NC);
+                    }
                 }
             } else {  // T_FLUSH
                 // my slice of this CTA's partial y; a helper thread publishes it (fence + counter) off this path
@@ -351,7 +371,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 }
                 __syncwarp();
                 if (lane == 0) {
-                    mbar_arrive(flushbar);
+                    if (pub_warp) {
+                        __threadfence();
+                        atomicAdd(p.comm.seq + 3, 1u);
+                    } else {
+                        mbar_arrive(flushbar);
+                    }
                     mbar_arrive(&empty[s]);
                 }
             }
@@ -370,7 +395,8 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
         // ---- y[columns of this CTA] = sum over all CTAs of their partial y, fixed order (+ b_down) [+ sum over the shards].
         // Its scratch is the ring: every consumer warp is past the loop when the first barrier inside releases.
         if (p.has_ffn) {
-            layer_sum_partials<true>(p, tid, NC, 1, reinterpret_cast<float4 *>(ring), seq, 2 * NW);
+            layer_sum_partials<true>(p, tid, NC, 1, reinterpret_cast<float4 *>(ring), seq, 2 * NW,
+                                     pub_warp ? (unsigned) (P * (NW + 1)) : 0u);
         }
     } else if (warp == NW) {
         // ================================================== epilogue warp ==================================================
@@ -404,20 +430,34 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                     p.cta_stats[c * 2 + 0] = ctl[3];
                     p.cta_stats[c * 2 + 1] = 0;
                     st_release_cta_s32(ctl + 1, 1);
-                    mbar_arrive(flushbar);
+                    if (pub_warp) {
+                        __threadfence();
+                        atomicAdd(p.comm.seq + 3, 1u);
+                    } else {
+                        mbar_arrive(flushbar);
+                    }
                 }
             }
             if (k >= total) {
                 break;
             }
             mbar_wait_spin(&done[k % K], (unsigned) (k / K) & 1u);
+            if (have_list && k == n_wpu + n_gu - 1) {
+                CLK_STAMP(500);
+            }
             const float * ps = part + (k % K) * 128;
             if (k < n_wpu + n_gu) {
                 // row sum = sum over (vector k', warp w) of the partial dots, in a fixed order: LPR lanes per row, then a tree
                 float s = 0.f;
-                for (int e = esub; e < VPT * NW; e += LPR) {
-                    const int kk = e / NW, ww = e - kk * NW;
-                    s += ps[(erow * VPT + kk) * 32 + ww];
+                if (VPT == 1) {
+                    for (int e = esub; e < NW; e += LPR) {
+                        s += ps[erow * 32 + e];
+                    }
+                } else {
+                    for (int e = esub; e < VPT * NW; e += LPR) {
+                        const int kk = e / NW, ww = e - kk * NW;
+                        s += ps[(erow * VPT + kk) * 32 + ww];
+                    }
                 }
 #pragma unroll
                 for (int o = LPR / 2; o > 0; o >>= 1) {
@@ -474,10 +514,16 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                             for (int q = pend_tail; q < n_dn * RPI; ++q) {
                                 tab_d[q] = make_uint4((uint32_t) a0, (uint32_t) (a0 >> 32), 0u, 0u);
                             }
+                            st_release_cta_s32(ctl + 1, n_dn * RPI + 1);  // first: the producer is waiting for exactly this
+                            CLK_STAMP(501);
                             p.cta_stats[c * 2 + 0] = ctl[3];
                             p.cta_stats[c * 2 + 1] = n_nonzero;
-                            st_release_cta_s32(ctl + 1, n_dn * RPI + 1);
-                            mbar_arrive(flushbar);
+                            if (pub_warp) {
+                                __threadfence();
+                                atomicAdd(p.comm.seq + 3, 1u);
+                            } else {
+                                mbar_arrive(flushbar);
+                            }
                         }
                     }
                 }
@@ -554,6 +600,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
             bool     flushed = !p.has_ffn;
             uint32_t a_ptr = tabA_s, b_ptr = tabB_s, c_ptr = tabC_s;
             int      s = 0, q = 0, qi = 0, b_done = 0;
+            bool     seen_final = false;
             unsigned eph = 0;  // parity of empty[s] to wait for once the ring has wrapped
             // 1: an item was issued, 0: nothing can be issued right now, -1: END was issued
             auto put = [&](bool prewait) -> int {
@@ -571,6 +618,10 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                     if (!flushed && (b_left >= 0 || b_done > 0)) {
                         const int final_rows = ld_acquire_cta_s32(ctl + 1);  // > 0: all gate/up items retired; rows incl. padding + 1
                         const int rows       = final_rows > 0 ? final_rows - 1 : ld_acquire_cta_s32(ctl + 0);
+                        if (TRACE && final_rows > 0 && !seen_final) {
+                            seen_final = true;
+                            CLK_STAMP(502);
+                        }
                         if ((d_next + 1) * RPI <= rows) {
                             ty = T_AXPY, name = 3, pt = tabD_s + (uint32_t) d_next * (RPI * 16u);
                             ++d_next;
@@ -656,8 +707,8 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 if (rc < 0) {
                     break;
                 }
-                if (rc == 0) {
-                    __nanosleep(40);
+                if (rc == 0 && (flushed || b_left != 0)) {
+                    __nanosleep(40);  // (no sleep while only the last hidden values are missing: the W_down^T rows are the critical path)
                 }
             }
         }
@@ -817,8 +868,11 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 LAYER_STAMP(9);
             }
         }
-        if (p.has_ffn && ht == 0) {
+        if (p.has_ffn && ht == 0 && !pub_warp) {
             mbar_wait(flushbar, 0);  // every consumer warp has stored its slice of the partial y, the epilogue warp the counts
+            if (TRACE && p.trace) {
+                p.trace[(size_t) blockIdx.x * 512 + 504] = (unsigned long long) clock64();
+            }
             __threadfence();
             atomicAdd(p.comm.seq + 3, 1u);
             LAYER_STAMP(4);

@@ -101,6 +101,8 @@ def main():
                     iss, lnd, ret = [(row[16 + 4 * q + j] - row[15]) / 1965.0 if row[16 + 4 * q + j] > 0 else float("nan") for j in (1, 2, 3)]
                     items.append(f"{names_t.get(ty, ty)}:{iss:.1f}/{lnd:.1f}/{ret:.1f}")
                 print(f"   cta {cta} items (issued/landed/retired, us since CTA entry at 1965 MHz): " + " ".join(items))
+                ex = {500: "epi.lastGU", 501: "epi.final", 502: "prod.final", 504: "help.flushbar"}
+                print(f"   cta {cta} extra: " + " ".join(f"{nm}={(row[k] - row[15]) / 1965.0:.2f}" for k, nm in ex.items() if row[k] > 0))
 
 
 if __name__ == "__main__":

@@ -222,7 +222,7 @@ __device__ __noinline__ float4 layer_allreduce_f4(const spif_comm_dev & c, uint3
 
 template <bool WIDE>
 __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t, int nthr, int bar_id, float4 * scratch,
-                                                   uint32_t seq, int G, unsigned target = 0) {
+                                                   uint32_t seq, int G) {
     const int P = gridDim.x, c = blockIdx.x, lane = t & 31;
     // b_down of my column: requested before the wait below instead of on the path between the sum and the store of y
     float4 bb_pre = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -234,8 +234,7 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
     }
     if (t == 0) {  // every CTA has published its partial y
         unsigned spins = 0;
-        const unsigned want = target ? target : (unsigned) P;  // publications expected (one per CTA, or one per warp of every CTA)
-        while (ld_u32_acquire_gpu(p.comm.seq + 3) < want) {
+        while (ld_u32_acquire_gpu(p.comm.seq + 3) < (unsigned) P) {
             if (++spins > SPIF_COMM_SPIN_LIMIT) {
                 atomicOr(p.comm.seq + 2, SPIF_COMM_ERR_TIMEOUT);
                 break;

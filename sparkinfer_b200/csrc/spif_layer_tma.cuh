@@ -137,11 +137,9 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
 
     const bool gated    = (p.arch != SPIF_ARCH_RELU_UP);
     const bool rounding = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
-    // experiment switches (SPIF_LAYER_DEBUG): bit 1 = consumer warps finish every gate/up and W_down^T item in lockstep (no
-    // warp runs ahead into filler Wpd items while a slower warp still holds up the hidden values); bit 2 = every warp publishes
-    // its own slice of the partial y (fence + counter) instead of one helper thread after a CTA-wide hand-off
-    const bool lockstep = (p.dbg & 2) != 0;
-    const bool pub_warp = (p.dbg & 4) != 0;
+    // (rejected experiments, profiles/r2_layer_experiments.txt: consumer warps in step per gate/up and W_down^T item +0.6 us;
+    // every warp publishing its own slice of the partial y with its own fence +0.4 us -- a __threadfence under this load costs
+    // ~1.1 us wherever it stands, so one per CTA it stays)
     const int  world    = p.comm.world;
     const int  h1_off   = p.n_embd;  // h1 words live behind the y words of a slot
     uint32_t   seq      = 0;
@@ -295,9 +293,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                     if (lane == 0) {
                         mbar_arrive(&empty[s]);  // my rows are in registers / consumed: the slot can be refilled
                     }
-                    if (lockstep) {
-                        named_bar_sync(2, NC);
-                    }
                 } else {
                     if (ty == T_DOTH && !h1_ready) {
                         // the hidden vector of the predictor, gathered by the helper warps while the rows above streamed
@@ -354,9 +349,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                         mbar_arrive(&done[ks]);
                     }
                     ++kseq;
-                    if (lockstep && d.w == 2) {  // name 2 = gate/up rows
-                        named_bar_sync(2, NC);
-                    }
                 }
             } else {  // T_FLUSH
                 // my slice of this CTA's partial y; a helper thread publishes it (fence + counter) off this path
@@ -371,12 +363,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 }
                 __syncwarp();
                 if (lane == 0) {
-                    if (pub_warp) {
-                        __threadfence();
-                        atomicAdd(p.comm.seq + 3, 1u);
-                    } else {
-                        mbar_arrive(flushbar);
-                    }
+                    mbar_arrive(flushbar);
                     mbar_arrive(&empty[s]);
                 }
             }
@@ -395,8 +382,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
         // ---- y[columns of this CTA] = sum over all CTAs of their partial y, fixed order (+ b_down) [+ sum over the shards].
         // Its scratch is the ring: every consumer warp is past the loop when the first barrier inside releases.
         if (p.has_ffn) {
-            layer_sum_partials<true>(p, tid, NC, 1, reinterpret_cast<float4 *>(ring), seq, 2 * NW,
-                                     pub_warp ? (unsigned) (P * (NW + 1)) : 0u);
+            layer_sum_partials<true>(p, tid, NC, 1, reinterpret_cast<float4 *>(ring), seq, 2 * NW);
         }
     } else if (warp == NW) {
         // ================================================== epilogue warp ==================================================
@@ -430,12 +416,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                     p.cta_stats[c * 2 + 0] = ctl[3];
                     p.cta_stats[c * 2 + 1] = 0;
                     st_release_cta_s32(ctl + 1, 1);
-                    if (pub_warp) {
-                        __threadfence();
-                        atomicAdd(p.comm.seq + 3, 1u);
-                    } else {
-                        mbar_arrive(flushbar);
-                    }
+                    mbar_arrive(flushbar);
                 }
             }
             if (k >= total) {
@@ -518,12 +499,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                             CLK_STAMP(501);
                             p.cta_stats[c * 2 + 0] = ctl[3];
                             p.cta_stats[c * 2 + 1] = n_nonzero;
-                            if (pub_warp) {
-                                __threadfence();
-                                atomicAdd(p.comm.seq + 3, 1u);
-                            } else {
-                                mbar_arrive(flushbar);
-                            }
+                            mbar_arrive(flushbar);
                         }
                     }
                 }
@@ -868,7 +844,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 LAYER_STAMP(9);
             }
         }
-        if (p.has_ffn && ht == 0 && !pub_warp) {
+        if (p.has_ffn && ht == 0) {
             mbar_wait(flushbar, 0);  // every consumer warp has stored its slice of the partial y, the epilogue warp the counts
             if (TRACE && p.trace) {
                 p.trace[(size_t) blockIdx.x * 512 + 504] = (unsigned long long) clock64();

@@ -693,8 +693,10 @@ def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
             # T == 1: "per_token" = every launch waits for its predecessor before it looks at its mask; "mask_stable" = the mask
             # of layer l exists a whole layer early, as in the reference's look-ahead order (SPIF_FLAG_MASK_STABLE): the kernel
             # scans it and requests its first rows under the previous launch's tail
+            # (quantised weights at <= 12 tokens: spif_sparse_ffn itself picks the per-token kernel, there is no union leg)
             for name, flags in ((("per_token", sp.FLAG_PER_TOKEN), ("mask_stable", sp.FLAG_PER_TOKEN | sp.FLAG_MASK_STABLE))
-                                if T == 1 else (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN))):
+                                if T == 1 else (("per_token", sp.FLAG_PER_TOKEN),) if (wname != "f16" and T <= 12) else
+                                (("union_gemm", 0), ("per_token", sp.FLAG_PER_TOKEN))):
                 def run():
                     for l in range(nl):
                         u, g_, d_ = weights[l]

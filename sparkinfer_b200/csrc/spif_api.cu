@@ -271,7 +271,11 @@ static int sparse_ffn_impl(const spif_ffn_args * args, const spif_shard_comm * c
     if (rc) {
         return rc;
     }
-    if (a.n_tok >= 2 && !(a.flags & SPIF_FLAG_PER_TOKEN)) {
+    // quantised weights at small batches: the warp-per-neuron kernel with one CTA row per token re-streams a row per token that
+    // needs it, but at <= 12 tokens that is still less time than dequantising the union of the rows into F16 operand tiles
+    // (13B Q4_0, T = 8: 51 us against 92 us; T = 32: 194 against 124 -- profiles/r2_bench_n1_default.json `batched`)
+    const bool quant_small = !is_float_type(a.type) && a.n_tok <= 12;
+    if (a.n_tok >= 2 && !(a.flags & SPIF_FLAG_PER_TOKEN) && !quant_small) {
         // batched / prefill: union of the per-token masks -> gathered GEMM on tensor cores, each row read once
         rc = spif_launch_ffn_batch(a, ws, ws_bytes, ctx);
         if (rc == 0 && comm) {

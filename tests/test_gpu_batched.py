@@ -113,9 +113,10 @@ def test_batched_quant_sparse_ffn(oracle, arch, wtype, n_embd, n_ff, n_tok, rho)
     act = ~(p < 0.5)
     assert rel_err(y, y64) < 2e-2, (wtype, arch, rel_err(y, y64))
     assert rel_err(y, y_ref) < 2e-2, (wtype, arch, rel_err(y, y_ref))
-    assert rel_err(y, y64) <= rel_err(y_ref, y64) + 1e-3      # F16 activations are no worse than the 8-bit ones
     assert np.array_equal(stats[:, 0], act.sum(axis=1))
-    assert np.all(stats[:, 2] == int(act.any(axis=0).sum()))
+    if n_tok > 12:  # the union GEMM (<= 12 tokens of quantised weights take the per-token warp-per-neuron kernel: 8-bit x)
+        assert rel_err(y, y64) <= rel_err(y_ref, y64) + 1e-3  # F16 activations are no worse than the 8-bit ones
+        assert np.all(stats[:, 2] == int(act.any(axis=0).sum()))
     y2 = sp.sparse_ffn(arch, wtype, dev(qu), gate, dev(qd), dev(x), dev(p), n_ff, ws=ws)
     assert np.array_equal(y, y2.cpu().numpy())
 

@@ -39,17 +39,17 @@ def test_topk_mask_bit_exact(oracle, n_ff, n_tok, k):
         assert int(got[t].sum()) == min(max(k, 0), n_ff)
 
 
-@pytest.mark.skipif(os.environ.get("SPIF_EXPERIMENTAL") != "1",
-                    reason="cluster top-k kernel is experimental (off by default): SPIF_EXPERIMENTAL=1 to run")
+@pytest.mark.parametrize("variant", ["1", "0"])
 @pytest.mark.parametrize("n_ff,n_tok,k", [(14336, 1, 1434), (14336, 4, 2867), (1000, 3, 1), (1000, 2, 999), (4096, 1, 0),
                                           (4096, 1, 4096), (16384, 2, 5000), (8191, 3, 4000)])
-def test_topk_mask_cluster_variant(oracle, n_ff, n_tok, k):
-    """the 8-CTA cluster radix select (SPIF_TOPK_CLUSTER=1) against the oracle, ties included"""
+def test_topk_mask_cluster_variant(oracle, n_ff, n_tok, k, variant):
+    """the 8-CTA cluster radix select (default, SPIF_TOPK_CLUSTER=1) and the single-CTA kernels (=0) against the oracle,
+    ties included"""
     import sparkinfer_b200 as sp
     rng = np.random.default_rng(synth.SEED0 + 3 * n_ff + k)
     score = rng.normal(0, 1, (n_tok, n_ff)).astype(np.float32)
     score[:, ::3] = np.round(score[:, ::3] * 4) / 4
-    os.environ["SPIF_TOPK_CLUSTER"] = "1"
+    os.environ["SPIF_TOPK_CLUSTER"] = variant
     try:
         got = sp.topk_mask(dev(score), k).cpu().numpy()
     finally:

@@ -1080,8 +1080,6 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const __grid_consta
     }
 }
 
-#include "spif_layer_direct.cuh"
-#include "spif_layer_stream.cuh"
 #include "spif_layer_tma.cuh"
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -1142,64 +1140,6 @@ static int launch_layer_t(const LayerParams & kp, int P, int threads, size_t sme
     int per_sm = 0;
     SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
     SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim            = dim3(P);
-    cfg.blockDim           = dim3(threads);
-    cfg.dynamicSmemBytes   = smem;
-    cfg.stream             = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs                                        = at;
-    cfg.numAttrs                                     = 1;
-    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
-    return 0;
-}
-
-template <typename WT, int VPT, int RPS, int MAXT>
-static int launch_layer2_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
-    auto kern = spif_layer2_kernel<WT, VPT, RPS, MAXT>;
-    static unsigned long long done = 0;  // per instantiation: bit per device
-    const unsigned long long  bit  = 1ull << (device & 63);
-    if (!(done & bit)) {
-        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        done |= bit;
-    }
-    // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
-    int per_sm = 0;
-    SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-    SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim            = dim3(P);
-    cfg.blockDim           = dim3(threads);
-    cfg.dynamicSmemBytes   = smem;
-    cfg.stream             = stream;
-    cudaLaunchAttribute at[1];
-    at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs                                        = at;
-    cfg.numAttrs                                     = 1;
-    SPIF_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, kp));
-    return 0;
-}
-
-template <typename WT, int VPT, int MAXT, bool RND, bool TRACE = false>
-static int launch_layer3_t(const LayerParams & kp, int P, int threads, size_t smem, int device, cudaStream_t stream) {
-    constexpr bool can_trace = VPT == 1 && !RND && std::is_same<WT, spif_f16>::value;
-    if (!TRACE && can_trace && kp.trace) {  // tools/trace_layer.py: per-item time stamps
-        return launch_layer3_t<WT, VPT, MAXT, RND, can_trace>(kp, P, threads, smem, device, stream);
-    }
-    auto kern = spif_layer3_kernel<WT, VPT, MAXT, TRACE, RND>;
-    static unsigned long long done = 0;  // per instantiation: bit per device
-    const unsigned long long  bit  = 1ull << (device & 63);
-    if (!(done & bit)) {
-        SPIF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        // every CTA waits for words written by every other CTA: the whole grid must be resident (one CTA per SM)
-        int per_sm = 0;
-        SPIF_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
-        SPIF_REQUIRE(per_sm >= 1, SPIF_E_UNSUPPORTED);
-        done |= bit;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim            = dim3(P);
     cfg.blockDim           = dim3(threads);
@@ -1365,8 +1305,10 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         kp.Vr = 32, kp.RP = 1, kp.WR = 1, kp.r = 256;
     }
     kp.lin_nblk          = P;  // lists on a device are always built with one block per SM
+    // SPIF_LAYER_IMPL=0 selects the first version (issuer thread + per-slot descriptors, below): kept as the A/B reference of
+    // profiles/r2_bench_n1_layer_tmaring.json; the register-direct and cp.async versions in between live in the git history only
     static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 3; }();
-    if (k_impl == 3) {  // version 6: row tables + one producer lane + TMA bulk copies into a ring of 4-row slots (spif_layer_tma.cuh)
+    if (k_impl != 0) {  // version 6: row tables + a producer warp + TMA bulk copies into a ring of 4-row slots (spif_layer_tma.cuh)
         const int vpt4 = (V <= 640) ? 1 : 2;
         kp.nw          = (V + 32 * vpt4 - 1) / (32 * vpt4);
         SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);
@@ -1395,49 +1337,6 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
         }
         return h16 ? SPIF_L4_GO(spif_f16, 1, 768) : SPIF_L4_GO(spif_bf16, 1, 768);
 #undef SPIF_L4_GO
-    }
-    if (k_impl == 2) {  // version 5: static schedule of row batches, cp.async staging per thread (spif_layer_stream.cuh)
-        // one 16-byte vector per thread up to 10 KB rows, two above: the staging of DEPTH items of 4 vectors per thread must fit
-        const int vpt3 = (V <= 640) ? 1 : 2;
-        kp.nw          = (V + 32 * vpt3 - 1) / (32 * vpt3);
-        SPIF_REQUIRE(kp.nw >= 2, SPIF_E_UNSUPPORTED);
-        const int        threads3 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
-        const Layer3Smem L3       = layer3_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw);
-        SPIF_REQUIRE(L3.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
-        if (ffn && ffn->hidden_out) {
-            SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
-        }
-        const bool h16 = type == SPIF_TYPE_F16;
-        // x, the hidden values and the predictor's hidden vector all rounded to the weight type (the reference CPU arithmetic):
-        // exact products by one instruction per element (fhfma2)
-        const bool rnd = (!ffn || (ffn->flags & SPIF_FLAG_CPU_ROUNDING)) && (!pv || (pv->flags & SPIF_FLAG_CPU_ROUNDING));
-#define SPIF_L3_GO(WT_, VPT_, MAXT_)                                                                                       \
-    (rnd ? launch_layer3_t<WT_, VPT_, MAXT_, true>(kp, P, threads3, L3.total, ctx.device, ctx.stream) :                    \
-           launch_layer3_t<WT_, VPT_, MAXT_, false>(kp, P, threads3, L3.total, ctx.device, ctx.stream))
-        if (vpt3 == 2) {
-            return h16 ? SPIF_L3_GO(spif_f16, 2, 640) : SPIF_L3_GO(spif_bf16, 2, 640);
-        }
-        return h16 ? SPIF_L3_GO(spif_f16, 1, 736) : SPIF_L3_GO(spif_bf16, 1, 736);
-#undef SPIF_L3_GO
-    }
-    if (k_impl == 1) {  // version 4: warp-autonomous register-direct streaming (spif_layer_direct.cuh)
-        const int        threads2 = (kp.nw + 3) * 32;  // consumers + epilogue + 2 helpers
-        const Layer2Smem L2       = layer2_smem_layout(kp.cap_ffn, kp.cap_pd, kp.cap_pu, pv ? pv->r : 0, P, kp.nw, 4);
-        SPIF_REQUIRE(L2.total <= (uint32_t) ctx.max_smem_optin, SPIF_E_SHAPE);
-        if (ffn && ffn->hidden_out) {
-            SPIF_CUDA_TRY(cudaMemsetAsync(ffn->hidden_out, 0, sizeof(float) * (size_t) ffn->n_ff, ctx.stream));
-        }
-        const bool h16 = type == SPIF_TYPE_F16;
-        if (vpt == 2) {
-            return h16 ? launch_layer2_t<spif_f16, 2, 2, 640>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
-                         launch_layer2_t<spif_bf16, 2, 2, 640>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
-        }
-        if (threads2 <= 736) {
-            return h16 ? launch_layer2_t<spif_f16, 1, 4, 736>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
-                         launch_layer2_t<spif_bf16, 1, 4, 736>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
-        }
-        return h16 ? launch_layer2_t<spif_f16, 1, 4, 1024>(kp, P, threads2, L2.total, ctx.device, ctx.stream) :
-                     launch_layer2_t<spif_bf16, 1, 4, 1024>(kp, P, threads2, L2.total, ctx.device, ctx.stream);
     }
     const int rps        = (vpt == 1 && kp.row_bytes <= 12288) ? 4 : 2;  // weight rows per ring slot
     const int slot_bytes = rps * kp.row_bytes;

@@ -1,5 +1,5 @@
 // spif_layer_tma.cuh -- the look-ahead layer kernel, version 6: row tables + ONE producer lane + the TMA unit.
-// Included by spif_layer.cu after spif_layer_stream.cuh (shares the row tables, fhfma2, the epilogue / helper roles).
+// Included by spif_layer.cu (shares LayerParams, the packed shuffle trees, layer_sum_partials and the launch code).
 //
 // Version 5 (spif_layer_stream.cuh) proved the schedule -- tables of rows in shared memory, a non-blocking priority pick, the
 // partial y complete right after the last gate/up item -- but its consumers issued their own loads: a table lookup, 64-bit
@@ -11,6 +11,54 @@
 // as soon as their 16-byte slices are in registers.  A consumer's item is: wait, 4 LDS.128, 32 FHFMA (or 64 convert + FFMA),
 // one packed shuffle tree, 4 floats into the partial ring, two barrier arrivals.
 #pragma once
+
+__device__ __forceinline__ int ld_acquire_cta_s32(const int * p) {
+    int v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_cta_s32(int * p, int v) {
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+
+// ---- exact f16 x f16 (bf16 x bf16) products accumulated in F32 by ONE instruction per element (fma.rn.f32.f16 -> FHFMA):
+// with SPIF_FLAG_CPU_ROUNDING x / the hidden values are values of the weight type (ggml-cpu.c:1832-1856), so the 8
+// conversions per 16 bytes of weights disappear and the results are bit-identical to convert + FFMA (both round once).
+template <typename WT> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<spif_f16>(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+template <> __device__ __forceinline__ uint32_t pack2<spif_bf16>(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+template <typename WT> __device__ __forceinline__ void fhfma2(float & s0, float & s1, uint32_t w, uint32_t x);
+template <> __device__ __forceinline__ void fhfma2<spif_f16>(float & s0, float & s1, uint32_t w, uint32_t x) {
+    asm("{\n\t.reg .b16 a0, a1, b0, b1;\n\tmov.b32 {a0, a1}, %2;\n\tmov.b32 {b0, b1}, %3;\n\t"
+        "fma.rn.f32.f16 %0, a0, b0, %0;\n\tfma.rn.f32.f16 %1, a1, b1, %1;\n\t}"
+        : "+f"(s0), "+f"(s1) : "r"(w), "r"(x));
+}
+template <> __device__ __forceinline__ void fhfma2<spif_bf16>(float & s0, float & s1, uint32_t w, uint32_t x) {
+    asm("{\n\t.reg .b16 a0, a1, b0, b1;\n\tmov.b32 {a0, a1}, %2;\n\tmov.b32 {b0, b1}, %3;\n\t"
+        "fma.rn.f32.bf16 %0, a0, b0, %0;\n\tfma.rn.f32.bf16 %1, a1, b1, %1;\n\t}"
+        : "+f"(s0), "+f"(s1) : "r"(w), "r"(x));
+}
+// same order of additions as dot8: even elements in one chain, odd elements in the other
+template <typename WT> __device__ __forceinline__ float dot8h(const uint4 & wv, const uint32_t * xh) {
+    float s0 = 0.f, s1 = 0.f;
+    fhfma2<WT>(s0, s1, wv.x, xh[0]);
+    fhfma2<WT>(s0, s1, wv.y, xh[1]);
+    fhfma2<WT>(s0, s1, wv.z, xh[2]);
+    fhfma2<WT>(s0, s1, wv.w, xh[3]);
+    return s0 + s1;
+}
+
+// A row of the schedule: {global address lo, hi, valid bytes of the row (0: no row), alpha of a W_down^T row}.  Tables in shared
+// memory, one per source: Wpu rows and Wpd "virtual rows" (RP adjacent Wpd rows = row_bytes) are filled at kernel entry, the
+// gate/up table by the helper warp that fetches the active-row list, the W_down^T table by the epilogue warp as it retires
+// the hidden values.  Every table is padded with empty rows to whole items.
+enum { T_DOT = 0, T_DOTH = 1, T_AXPY = 2, T_FLUSH = 3, T_NONE = 4, T_END = 5 };
 
 #define SPIF_L4_K 16 /* depth of the partial-dot ring (reduce items between the consumer warps and the epilogue warp) */
 

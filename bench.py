@@ -727,6 +727,25 @@ def batched_legs(a, st, wl, device, batches=(8, 32), n_layers=8, reps=20):
                 else:
                     rows = float((2 * sn[:, :, 0] + sn[:, :, 1]).sum(axis=1).mean())
                 leg[name] = {"us_per_layer": us, "ffn_tok_s": T / (us * st.L) * 1e6, "algorithmic_GBps": rows * rb / us / 1e3}
+            if wname == "q8_0" and T == 1 and not a.no_gpu_baseline:
+                # the quant format the reference's sparse CUDA kernels ship (mmq-sparse.cu + quantize.cu, axpyq-sparse.cu, compiled
+                # unmodified for sm_100): the same Q8_0 rows, masks and x through them, CUDA graph, no predictor
+                import oracle_lib
+                if oracle_lib.RefCuda.available():
+                    rc = oracle_lib.RefCuda()
+                    ly = st.layers[:nl]
+                    xr = x.expand(nl, E).contiguous()
+                    yr = torch.zeros((nl, E), dtype=torch.float32, device=device)
+                    pr = torch.stack([mk[0] for mk in masks]).contiguous()
+                    us_g, _ = rc.stack(st.arch, sp.GGML_TYPE_Q8_0, F16, [w[0] for w in weights], [w[1] for w in weights],
+                                       [w[2] for w in weights], [w.pred_up for w in ly], [w.pred_down for w in ly],
+                                       [w.pred_down_b for w in ly], xr, yr, pr, E, F, st.r, with_pred=False, warmup=2, iters=10)
+                    torch.cuda.synchronize()
+                    run()
+                    torch.cuda.synchronize()
+                    err = float(((yr[nl - 1] - y[0]).abs().max() / y[0].abs().max().clamp_min(1e-30)).item())
+                    leg["reference_cuda_kernels"] = {"us_per_layer": us_g / nl, "max_rel_err_vs_ours_last_layer": err,
+                                                     "what": "mmq-sparse.cu / axpyq-sparse.cu / quantize.cu, unmodified, sm_100"}
             res.append(leg)
     return res
 
@@ -770,7 +789,8 @@ def cpu_stack_tok_s(a, wl, iters, warmup):
         raise RuntimeError("CPU stack timing failed")
     tok_s = 1e6 / (us * wl_L / nl)
     sample = (f"{nl} of {wl_L} layers (predictor + sparse FFN, look-ahead order), median of {iters} steps after {warmup} "
-              f"warm-up, {cores} threads, scaled x{wl_L / nl:g} to the full stack")
+              f"warm-up, {cores} threads, scaled x{wl_L / nl:g} to the full stack"
+              + ("; reference built -march=x86-64-v3 (AVX2, no AVX-512) so that the binary travels" if kind == "reference" else ""))
     return tok_s, kind, cores, sample
 
 

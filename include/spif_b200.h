@@ -18,6 +18,13 @@
  *   - every function returns 0 on success, a negative SPIF_E* code for argument errors, or a positive cudaError_t.
  *     The glue turns non-zero into GGML_ABORT (the reference aborts on the same conditions).
  * There is NO CPU fallback: without a CUDA device every compute entry point returns an error.
+ *
+ * Environment: the library reads a handful of SPIF_* variables, once per process, as EXPERIMENT switches between kernel
+ * variants that all compute the same results (SPIF_LAYER_IMPL, SPIF_LAYER_L2_HINT, SPIF_Q_RING, SPIF_QW_HALF, SPIF_DIRECT,
+ * SPIF_DIRECT_SMALL, SPIF_RED_FIRST, SPIF_FFN_CTAS, SPIF_PDL_LATE, SPIF_DG_WARPS, SPIF_DG_VL, SPIF_DG_ASYNC, SPIF_CTAS_PER_SM,
+ * SPIF_STAGES, SPIF_SMEM_SPLIT, SPIF_GU_PCT, SPIF_DSLOTS, SPIF_TOPK_CLUSTER) and two debug switches that do NOT
+ * (SPIF_LAYER_DEBUG, SPIF_BATCH_DEBUG: timing floors with the arithmetic or the loads skipped).  Defaults are the measured
+ * best; DESIGN.md section 4 lists meaning and default of each.  None is needed in production.
  */
 #ifndef SPIF_B200_H
 #define SPIF_B200_H

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SPIF_B200_ABI_VERSION 2
+#define SPIF_B200_ABI_VERSION 3
 
 typedef struct CUstream_st * spif_stream_t; /* == cudaStream_t */
 
@@ -231,10 +231,26 @@ typedef struct spif_pred_args {
     float * sparse_idx_out; /* nullable {m} */
     float * logits_out;     /* nullable {m} */
 } spif_pred_args;
+/* Optional fusion of what stands either side of the sparse FFN in the reference's layer graph (src/models/llama.cpp:98-101,
+ * 144): build_norm(ffn_inp, ffn_norm, LLM_NORM_RMS) before it -- x_n = (x * (1 / sqrtf(mean(x^2) + eps))) * w,
+ * the arithmetic of ggml_compute_forward_rms_norm_f32 (ggml-cpu/ops.cpp:3730-3779: double sum, float mean) followed by
+ * ggml_mul -- and ggml_add(cur, ffn_inp) after it.  With norm_w the kernel normalises ffn->x / pred->x (the RAW ffn_inp)
+ * itself: the FFN of layer l and the look-ahead predictor of layer l + 1 both read the normalised vector, as in the reference;
+ * with residual, y = (ffn + b_down) + residual.  Replaces three graph nodes (RMS_NORM, MUL, ADD) and their launches. */
+typedef struct spif_layer_io {
+    const float * norm_w;    /* nullable {n_embd}: ffn_norm weight */
+    float         norm_eps;  /* f_norm_rms_eps */
+    int32_t       reserved;
+    const float * residual;  /* nullable {n_embd}: ffn_inp; may alias x */
+} spif_layer_io;
 size_t spif_active_list_bytes(int m);
 int spif_mask_to_list(const float * sparse_idx, int m, float thr, void * list_out, spif_stream_t stream);
 int spif_sparse_ffn_lookahead(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
                               const spif_shard_comm * comm, void * ws, size_t ws_bytes, spif_stream_t stream);
+/* the same with the layer's RMSNorm / residual add fused in (io may be NULL = spif_sparse_ffn_lookahead) */
+int spif_sparse_ffn_lookahead_ex(const spif_ffn_args * ffn, const spif_pred_args * pred, const spif_layer_io * io,
+                                 const void * list_in, void * list_out, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
+                                 spif_stream_t stream);
 
 /* ---- balancer helpers (build_dfr, src/llama-graph.cpp:910-930; binbcast.cu:26-42; sumcols.cu; argsort.cu) ---------
  * One fused kernel: per group of `g` consecutive neurons, delta = #(active, token) pairs, then

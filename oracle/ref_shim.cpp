@@ -190,6 +190,22 @@ int spif_ref_axpy_sparse(int wtype, const void * wt, const float * hid, const fl
     return 0;
 }
 
+// build_norm(x, w, LLM_NORM_RMS) = ggml_mul(ggml_rms_norm(x, eps), w)  (src/llama-graph.cpp build_norm; src/models/llama.cpp:98-101)
+// and, with add != NULL, the residual ggml_add(y, add) of :144 applied to y_in instead of the FFN output: out2 = y_in + add.
+int spif_ref_rms_norm_mul(const float * x, const float * w, float eps, int n_embd, int n_tok, float * out, int n_threads) {
+    shim_ctx      s(scratch_bytes(n_embd, 0, 0, n_tok));
+    ggml_tensor * X = s.leaf2(GGML_TYPE_F32, n_embd, n_tok, x);
+    ggml_tensor * W = s.leaf1(GGML_TYPE_F32, n_embd, w);
+    ggml_tensor * R = ggml_mul(s.ctx, ggml_rms_norm(s.ctx, X, eps), W);
+    ggml_cgraph * gf = ggml_new_graph(s.ctx);
+    ggml_build_forward_expand(gf, R);
+    if (run(s, gf, n_threads)) {
+        return 1;
+    }
+    memcpy(out, R->data, sizeof(float) * (size_t) n_embd * n_tok);
+    return 0;
+}
+
 // build_predictor (src/llama-graph.cpp:865-894): sigmoid(Wpd . relu(Wpu . x + bpu) + bpd). Biases nullable.
 int spif_ref_predictor(int ptype, const void * wpu, const float * bpu, const void * wpd, const float * bpd,
                        const float * x, float * sparse_idx_out, int n_embd, int r, int n_ff, int n_tok,

@@ -30,6 +30,11 @@ class PredArgs(ctypes.Structure):
     ]
 
 
+class LayerIo(ctypes.Structure):
+    """struct spif_layer_io (include/spif_b200.h)"""
+    _fields_ = [("norm_w", c_vp), ("norm_eps", ctypes.c_float), ("reserved", ctypes.c_int32), ("residual", c_vp)]
+
+
 class ShardCommStruct(ctypes.Structure):
     """struct spif_shard_comm (include/spif_b200.h)"""
     _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("cap_floats", ctypes.c_int32),
@@ -60,6 +65,8 @@ SYMBOLS = {
     "spif_mask_to_list": (c_i, [c_vp, c_i, c_f, c_vp, c_vp]),
     "spif_sparse_ffn_lookahead": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(PredArgs), c_vp, c_vp,
                                         ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
+    "spif_sparse_ffn_lookahead_ex": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(PredArgs), ctypes.POINTER(LayerIo), c_vp, c_vp,
+                                           ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
     "spif_initial_placement": (c_i, [c_vp, c_i, c_i, c_vp]),
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
     "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),

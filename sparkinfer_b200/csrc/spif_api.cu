@@ -12,7 +12,7 @@ size_t spif_batch_workspace_bytes(int n_embd, int n_ff, int n_tok);
 int    spif_launch_shard_allreduce(float * y, int64_t n, const spif_shard_comm * comm, cudaStream_t stream);
 size_t spif_active_list_bytes_impl(int m);
 int    spif_launch_mask_to_list(const float * mask, int m, float thr, void * list, const spif_launch_ctx & ctx);
-int    spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+int    spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const spif_layer_io * io, const void * list_in, void * list_out,
                          const spif_shard_comm * comm, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx);
 
 static int make_ctx(spif_launch_ctx & ctx, spif_stream_t stream) {
@@ -343,7 +343,18 @@ int spif_sparse_ffn_lookahead(const spif_ffn_args * ffn, const spif_pred_args * 
     if (rc) {
         return rc;
     }
-    return spif_launch_layer(ffn, pred, list_in, list_out, comm, ws, ws_bytes, ctx);
+    return spif_launch_layer(ffn, pred, nullptr, list_in, list_out, comm, ws, ws_bytes, ctx);
+}
+
+int spif_sparse_ffn_lookahead_ex(const spif_ffn_args * ffn, const spif_pred_args * pred, const spif_layer_io * io,
+                                 const void * list_in, void * list_out, const spif_shard_comm * comm, void * ws, size_t ws_bytes,
+                                 spif_stream_t stream) {
+    spif_launch_ctx ctx;
+    int             rc = make_ctx(ctx, stream);
+    if (rc) {
+        return rc;
+    }
+    return spif_launch_layer(ffn, pred, io, list_in, list_out, comm, ws, ws_bytes, ctx);
 }
 
 int spif_dfr_update(const float * sparse_idx, int n_ff, int n_tok, int g, float thr, float lambda, int ema,

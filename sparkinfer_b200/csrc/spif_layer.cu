@@ -53,6 +53,9 @@ struct LayerParams {
     int32_t *             stats_out;   // nullable [4]
     const int32_t *       lin_cnt;     // active-row list of this layer: counts per block
     const int32_t *       lin_rows;    //   rows, block b at offset floor(b * m / nblk)
+    const float *         norm_w;      // nullable [n_embd]: RMSNorm weight, x is normalised in the kernel (spif_layer_io)
+    const float *         residual;    // nullable [n_embd]: added to y after b_down
+    float                 norm_eps;
     float *               partials;    // [P][n_embd]
     int32_t *             cta_stats;   // [P][2]
     // ---- predictor of the next layer (has_pred)
@@ -225,11 +228,16 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
                                                    uint32_t seq, int G) {
     const int P = gridDim.x, c = blockIdx.x, lane = t & 31;
     // b_down of my column: requested before the wait below instead of on the path between the sum and the store of y
-    float4 bb_pre = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (WIDE && t < 64 && (t & 3) == 0 && p.b_down) {
+    float4 bb_pre = make_float4(0.f, 0.f, 0.f, 0.f), res_pre = bb_pre;
+    if (WIDE && t < 64 && (t & 3) == 0 && (p.b_down || p.residual)) {
         const int n4p = p.n_embd >> 2, c0p = share(c, n4p, P), c1p = share(c + 1, n4p, P);
         if ((t >> 2) < c1p - c0p) {
-            bb_pre = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0p + (t >> 2));
+            if (p.b_down) {
+                bb_pre = __ldg(reinterpret_cast<const float4 *>(p.b_down) + c0p + (t >> 2));
+            }
+            if (p.residual) {  // ggml_add(cur, ffn_inp), src/models/llama.cpp:144 (plain load: may be this launch's own x)
+                res_pre = reinterpret_cast<const float4 *>(p.residual)[c0p + (t >> 2)];
+            }
         }
     }
     if (t == 0) {  // every CTA has published its partial y
@@ -286,6 +294,9 @@ __device__ __forceinline__ void layer_sum_partials(const LayerParams & p, int t,
                     a.x += bb_pre.x, a.y += bb_pre.y, a.z += bb_pre.z, a.w += bb_pre.w;
                 }
                 a = layer_allreduce_f4(p.comm, seq, a, c0 + c2, own);
+                if (own && p.residual) {  // after the sum over the shards: added once
+                    a.x += res_pre.x, a.y += res_pre.y, a.z += res_pre.z, a.w += res_pre.w;
+                }
                 if (own) {
                     reinterpret_cast<float4 *>(p.y)[c0 + c2] = a;
                 }
@@ -1185,7 +1196,7 @@ static int launch_layer4_t(const LayerParams & kp, int P, int threads, size_t sm
     return 0;
 }
 
-int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const void * list_in, void * list_out,
+int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, const spif_layer_io * io, const void * list_in, void * list_out,
                       const spif_shard_comm * comm, void * ws, size_t ws_bytes, const spif_launch_ctx & ctx) {
     SPIF_REQUIRE(ffn != nullptr || pred != nullptr, SPIF_E_NULL);
     SPIF_REQUIRE(comm != nullptr, SPIF_E_NULL);
@@ -1308,6 +1319,15 @@ int spif_launch_layer(const spif_ffn_args * ffn, const spif_pred_args * pred, co
     // SPIF_LAYER_IMPL=0 selects the first version (issuer thread + per-slot descriptors, below): kept as the A/B reference of
     // profiles/r2_bench_n1_layer_tmaring.json; the register-direct and cp.async versions in between live in the git history only
     static const int k_impl = [] { const char * e = getenv("SPIF_LAYER_IMPL"); return e ? atoi(e) : 3; }();
+    if (io && (io->norm_w || io->residual)) {
+        SPIF_REQUIRE(k_impl != 0, SPIF_E_UNSUPPORTED);
+        SPIF_REQUIRE(((uintptr_t) io->norm_w & 15) == 0 && ((uintptr_t) io->residual & 15) == 0, SPIF_E_SHAPE);
+        SPIF_REQUIRE(!io->norm_w || io->norm_eps >= 0.0f, SPIF_E_SHAPE);
+        SPIF_REQUIRE(!io->residual || ffn, SPIF_E_NULL);
+        kp.norm_w   = io->norm_w;
+        kp.norm_eps = io->norm_eps;
+        kp.residual = io->residual;
+    }
     if (k_impl != 0) {  // version 6: row tables + a producer warp + TMA bulk copies into a ring of 4-row slots (spif_layer_tma.cuh)
         const int vpt4 = (V <= 640) ? 1 : 2;
         kp.nw          = (V + 32 * vpt4 - 1) / (32 * vpt4);

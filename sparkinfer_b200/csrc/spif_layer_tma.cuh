@@ -73,7 +73,7 @@ enum { T_DOT = 0, T_DOTH = 1, T_AXPY = 2, T_FLUSH = 3, T_NONE = 4, T_END = 5 };
 
 struct Layer4Smem {
     uint32_t ring, full, empty, sdesc, done, part, ctl, list_row, list_neu, list_bu, list_bg, tab_a, tab_b, tab_c, tab_d, bpu_s,
-        bpd_s, lout_s, h1_s, blk_pre, total;
+        bpd_s, lout_s, h1_s, blk_pre, nsum, total;
 };
 
 __host__ __device__ static inline Layer4Smem layer4_smem_layout(int nslots, int slot_bytes, int cap_ffn, int cap_pd, int cap_pu,
@@ -106,8 +106,28 @@ __host__ __device__ static inline Layer4Smem layer4_smem_layout(int nslots, int 
     L.lout_s   = take(4u * cap_pd, 4);
     L.h1_s     = take(4u * r, 16);
     L.blk_pre  = take(4u * (nblk + 1), 4);
+    L.nsum     = take(8u * 32, 8);  // per consumer warp: sum of squares of its slice of x (fused RMSNorm)
     L.total    = (o + 127) / 128 * 128;
     return L;
+}
+
+// 1 / sqrtf(mean(x^2) + eps) from every consumer thread's double partial sum of squares (out of line: its doubles and the
+// barrier must not touch the register allocation of the streaming loop)
+__device__ __noinline__ float layer_rms_scale(double ss, double * nsum, int warp, int lane, int NW, int NC, int n_embd, float eps) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    }
+    if (lane == 0) {
+        nsum[warp] = ss;
+    }
+    named_bar_sync(2, NC);
+    double tot = 0.0;
+    for (int w = 0; w < NW; ++w) {
+        tot += nsum[w];
+    }
+    const float mean = (float) (tot / (double) n_embd);
+    return __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
 }
 
 // Warp roles: [0, NW) consumers, NW = epilogue, NW + 1 .. NW + 2 = helpers (row list, h1 gather, partial-y publication),
@@ -156,6 +176,7 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
     int *      lout_s     = reinterpret_cast<int *>(smem + L.lout_s);
     float *    h1_s       = reinterpret_cast<float *>(smem + L.h1_s);
     int *      blk_pre    = reinterpret_cast<int *>(smem + L.blk_pre);
+    double *   nsum       = reinterpret_cast<double *>(smem + L.nsum);
 
     if (tid == 0) {
         LAYER_STAMP(7);
@@ -254,18 +275,44 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                 const int    v = tid + k * NC;
                 const float4 a = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v);
                 const float4 b = __ldg(reinterpret_cast<const float4 *>(p.x) + 2 * v + 1);
-                if (RND) {  // ggml-cpu.c:1832-1856: x is converted to the weight type
-                    vh[k * 4 + 0] = pack2<WT>(a.x, a.y), vh[k * 4 + 1] = pack2<WT>(a.z, a.w);
-                    vh[k * 4 + 2] = pack2<WT>(b.x, b.y), vh[k * 4 + 3] = pack2<WT>(b.z, b.w);
-                    continue;
-                }
                 vr[k * 8 + 0] = a.x, vr[k * 8 + 1] = a.y, vr[k * 8 + 2] = a.z, vr[k * 8 + 3] = a.w;
                 vr[k * 8 + 4] = b.x, vr[k * 8 + 5] = b.y, vr[k * 8 + 6] = b.z, vr[k * 8 + 7] = b.w;
-                if (rounding) {
+            }
+        }
+        if (p.norm_w) {
+            // build_norm(ffn_inp, ffn_norm, LLM_NORM_RMS) fused (spif_layer_io): the arithmetic of
+            // ggml_compute_forward_rms_norm_f32 (ops.cpp:3756-3775) + ggml_mul -- squares rounded to F32, summed in double,
+            // mean and scale in F32, y = (x * scale) * w with two roundings.  Every CTA normalises the whole vector itself (its
+            // consumer threads hold all of x): one shuffle tree in double + one named barrier among the consumer warps.
+            double ss = 0.0;
+#pragma unroll
+            for (int e = 0; e < VPT * 8; ++e) {
+                ss += (double) __fmul_rn(vr[e], vr[e]);  // threads beyond the row hold zeros
+            }
+            const float scale = layer_rms_scale(ss, nsum, warp, lane, NW, NC, p.n_embd, p.norm_eps);
+#pragma unroll
+            for (int k = 0; k < VPT; ++k) {
+                if (toff[k] < row_bytes) {
+                    const int    v = tid + k * NC;
+                    const float4 a = __ldg(reinterpret_cast<const float4 *>(p.norm_w) + 2 * v);
+                    const float4 b = __ldg(reinterpret_cast<const float4 *>(p.norm_w) + 2 * v + 1);
+                    const float  wv[8] = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        vr[k * 8 + e] = round_through<WT>(vr[k * 8 + e]);
+                        vr[k * 8 + e] = __fmul_rn(__fmul_rn(vr[k * 8 + e], scale), wv[e]);
                     }
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < VPT; ++k) {
+            if (RND) {  // ggml-cpu.c:1832-1856: x is converted to the weight type
+                vh[k * 4 + 0] = pack2<WT>(vr[k * 8 + 0], vr[k * 8 + 1]), vh[k * 4 + 1] = pack2<WT>(vr[k * 8 + 2], vr[k * 8 + 3]);
+                vh[k * 4 + 2] = pack2<WT>(vr[k * 8 + 4], vr[k * 8 + 5]), vh[k * 4 + 3] = pack2<WT>(vr[k * 8 + 6], vr[k * 8 + 7]);
+            } else if (rounding) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    vr[k * 8 + e] = round_through<WT>(vr[k * 8 + e]);
                 }
             }
         }

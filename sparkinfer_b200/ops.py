@@ -18,7 +18,7 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import FfnArgs, PredArgs, ShardCommStruct, check
+from ._lib import FfnArgs, LayerIo, PredArgs, ShardCommStruct, check
 
 GGML_TYPE_F32, GGML_TYPE_F16, GGML_TYPE_Q4_0, GGML_TYPE_Q8_0, GGML_TYPE_BF16 = 0, 1, 2, 8, 30
 ARCH_PROSPARSE, ARCH_RELU_GATED, ARCH_RELU_UP, ARCH_SILU_GATED = 0, 1, 2, 3
@@ -246,11 +246,12 @@ def mask_to_list(sparse_idx, thr=SPARSE_THRESHOLD, out=None):
     return out
 
 
-def sparse_ffn_lookahead(comm, ws, ffn=None, pred=None, list_in=None, list_out=None):
+def sparse_ffn_lookahead(comm, ws, ffn=None, pred=None, list_in=None, list_out=None, io=None):
     """spif_sparse_ffn_lookahead: the sparse FFN of one layer (ffn: dict of sparse_ffn's arguments arch, w_type, up, gate,
     down_t, cur, n_ff, [neuron_idx, up_b, gate_b, down_b, flags, out, hidden_out, stats]) + the look-ahead predictor of
     the next (pred: dict pred_up, pred_up_b, pred_down, pred_down_b, cur, p_type, r, m, [flags, thr, out, logits_out]) in
-    one launch; list_in / list_out are ActiveList objects."""
+    one launch; list_in / list_out are ActiveList objects.  io: dict(norm_w, norm_eps, residual) = the layer's RMSNorm before
+    and residual add after, fused (spif_sparse_ffn_lookahead_ex); `cur` is then the RAW ffn_inp."""
     L = _lib.load()
     fa = pa = None
     if ffn is not None:
@@ -270,6 +271,14 @@ def sparse_ffn_lookahead(comm, ws, ffn=None, pred=None, list_in=None, list_out=N
                       thr=pred.get("thr", SPARSE_THRESHOLD), wpu=_p(pred["pred_up"]), bpu=_p(pred.get("pred_up_b")),
                       wpd=_p(pred["pred_down"]), bpd=_p(pred.get("pred_down_b")), x=_p(cur),
                       sparse_idx_out=_p(pred.get("out")), logits_out=_p(pred.get("logits_out")))
+    if io is not None:
+        lio = LayerIo(norm_w=_p(io.get("norm_w")), norm_eps=float(io.get("norm_eps", 0.0)), reserved=0, residual=_p(io.get("residual")))
+        check(L.spif_sparse_ffn_lookahead_ex(ctypes.byref(fa) if fa is not None else None,
+                                             ctypes.byref(pa) if pa is not None else None, ctypes.byref(lio),
+                                             _p(list_in.buf) if list_in is not None else None,
+                                             _p(list_out.buf) if list_out is not None else None, ctypes.byref(comm.c), ws.ptr,
+                                             ws.nbytes, _stream()), "spif_sparse_ffn_lookahead_ex")
+        return
     check(L.spif_sparse_ffn_lookahead(ctypes.byref(fa) if fa is not None else None, ctypes.byref(pa) if pa is not None else None,
                                       _p(list_in.buf) if list_in is not None else None,
                                       _p(list_out.buf) if list_out is not None else None, ctypes.byref(comm.c), ws.ptr,

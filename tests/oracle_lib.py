@@ -176,9 +176,22 @@ class Ref:
         self._pred = L.fn("predictor", c_i, [c_i, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i, c_i, c_i, c_i, c_i])
         self._ffn = L.fn("sparse_ffn", c_i, [c_i, c_i] + [c_vp] * 12 + [c_i, c_i, c_i, c_i])
         self._stack = L.fn("ffn_stack_time", c_d, [c_i, c_i, c_i, c_i] + [c_vp] * 8 + [c_i] * 7)
+        try:
+            self._rms = L.fn("rms_norm_mul", c_i, [c_vp, c_vp, ctypes.c_float, c_i, c_i, c_vp, c_i])
+        except AttributeError:  # an oracle/_ref built before round 2's f2 row
+            self._rms = None
 
     def describe(self):
         return self._describe().decode()
+
+    def rms_norm_mul(self, x, w, eps, n_threads=1):
+        """the reference's build_norm(x, w, LLM_NORM_RMS): ggml_rms_norm + ggml_mul on its CPU backend"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        n_tok, n_embd = x.shape
+        out = np.empty_like(x)
+        assert self._rms(x.ctypes.data, w.ctypes.data, float(eps), n_embd, n_tok, out.ctypes.data, n_threads) == 0
+        return out
 
     def row_size(self, t, n):
         return self._row_size(t, n)
@@ -293,3 +306,22 @@ def stack_time(lib, arch, wtype, ptype, w_up, w_gate, w_down, wpu, wpd, bpd, x, 
     us = lib._stack(arch, wtype, ptype, nl, keep[0], keep[1], keep[2], keep[3], keep[4], keep[5], _ptr(x), _ptr(y),
                     n_embd, n_ff, r, n_tok, n_threads, warmup, iters)
     return us, y
+
+
+def rms_norm_mul(x, w, eps):
+    """numpy restatement of build_norm(x, w, LLM_NORM_RMS) as the reference CPU backend computes it
+    (ggml_compute_forward_rms_norm_f32, ggml-cpu/ops.cpp:3730-3779, then ggml_mul): squares rounded to F32 and summed
+    sequentially in double, mean and scale in F32, y = (x * scale) * w with a rounding after each product.
+    Pinned bit-exact against oracle/_ref in tests/test_oracle_golden.py."""
+    x = np.asarray(x, dtype=np.float32)
+    w = np.asarray(w, dtype=np.float32)
+    out = np.empty_like(x)
+    for t in range(x.shape[0]):
+        sq = (x[t] * x[t]).astype(np.float32)
+        total = 0.0
+        for v in sq.astype(np.float64):  # sequential double sum (the order matters only in the last bit of the double)
+            total += v
+        mean = np.float32(total / x.shape[1])
+        scale = np.float32(1.0) / np.sqrt(np.float32(mean + np.float32(eps)), dtype=np.float32)
+        out[t] = ((x[t] * np.float32(scale)).astype(np.float32) * w).astype(np.float32)
+    return out

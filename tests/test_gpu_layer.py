@@ -218,3 +218,59 @@ def test_lookahead_rejects(oracle):
         sp.sparse_ffn_lookahead(comm, ws, pred=dict(pred_up=z, pred_down=z, cur=x, p_type=F16, r=128, m=1024))
     with pytest.raises(SpifError):  # nothing to do
         sp.sparse_ffn_lookahead(comm, ws)
+
+
+@pytest.mark.parametrize("flags_name", ["f32", "cpu_rounding"])
+@pytest.mark.parametrize("n_embd,r,n_ff", [(512, 256, 1024), (1376, 256, 2048), (5120, 1024, 13824)])
+def test_lookahead_fused_rmsnorm_and_residual(oracle, n_embd, r, n_ff, flags_name):
+    """SURVEY 8f2 (src/models/llama.cpp:98-101,144): build_norm(ffn_inp, ffn_norm, RMS) before and ggml_add(cur, ffn_inp) after
+    the sparse FFN, fused into the layer kernel (spif_sparse_ffn_lookahead_ex).  Oracle = the reference's rms_norm + mul
+    arithmetic (oracle_lib.rms_norm_mul, pinned bit-exact against oracle/_ref) -> oracle predictor / sparse FFN -> + residual."""
+    import oracle_lib
+    import sparkinfer_b200 as sp
+    seed = synth.SEED0 + 7 * n_embd + n_ff + r
+    rng = np.random.default_rng(seed)
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(F16, w) for w in (Wu, Wg, Wd))
+    wpu, wpd, bpd = synth.predictor_weights(n_embd, r, n_ff, 0.1, seed + 3)
+    qpu, qpd = oracle.quantize(F16, wpu), oracle.quantize(F16, wpd)
+    x = (synth.activations(n_embd, 1, seed + 1) * 3.0).astype(np.float32)          # raw ffn_inp, not unit variance
+    w_norm = rng.normal(1.0, 0.2, n_embd).astype(np.float32)
+    eps = 1e-5
+    b_down = rng.normal(0, 0.1, n_embd).astype(np.float32)
+    p = synth.direct_mask(n_ff, 1, 0.10, seed + 2)
+    x_n = oracle_lib.rms_norm_mul(x, w_norm, eps)
+    y_ffn = oracle.sparse_ffn(ARCH_PROSPARSE, F16, qu, qg, qd, x_n, p, n_embd, n_ff, b_down=b_down)[0]
+    y_ref = (y_ffn[0] + x[0]).astype(np.float32)
+    p_ref, z_ref = oracle.predictor(F16, qpu, None, qpd, bpd, x_n, n_embd, r, n_ff)
+    flags = sp.FLAG_CPU_ROUNDING if flags_name == "cpu_rounding" else 0
+    comm = sp.ShardComm(n_embd + r)
+    ws = sp.Workspace(n_embd, n_ff, 1)
+    dx = dev(x[0])
+    y = torch.full((n_embd,), float("nan"), device="cuda")
+    z_gpu = torch.empty((n_ff,), device="cuda")
+    p_gpu = torch.empty((n_ff,), device="cuda")
+    lst_out = sp.ActiveList(n_ff)
+    sp.sparse_ffn_lookahead(comm, ws,
+                            ffn=dict(arch=ARCH_PROSPARSE, w_type=F16, up=dev(qu), gate=dev(qg), down_t=dev(qd), cur=dx, n_ff=n_ff,
+                                     down_b=dev(b_down), flags=flags, out=y),
+                            pred=dict(pred_up=dev(qpu), pred_down=dev(qpd), pred_down_b=dev(bpd), cur=dx, p_type=F16, r=r, m=n_ff,
+                                      flags=sp.FLAG_CPU_ROUNDING, out=p_gpu, logits_out=z_gpu),
+                            list_in=sp.mask_to_list(dev(p[0])), list_out=lst_out,
+                            io=dict(norm_w=dev(w_norm), norm_eps=eps, residual=dx))
+    y, z_gpu, p_gpu = y.cpu().numpy(), z_gpu.cpu().numpy(), p_gpu.cpu().numpy()
+    tol = TOL_CPU_ROUNDING[F16] if flags else TOL[F16]
+    assert rel_err(y - x[0], y_ffn[0]) < tol, rel_err(y - x[0], y_ffn[0])      # the FFN part alone (the residual dominates y)
+    assert rel_err(y, y_ref) < tol
+    if flags:  # (the predictor follows the FFN's rounding mode: one codec per launch)
+        assert np.abs(z_gpu - z_ref[0]).max() < 1e-4 * max(1.0, np.abs(z_ref).max())
+        flips = (p_gpu < 0.5) != (p_ref[0] < 0.5)
+        assert np.all(np.abs(z_ref[0][flips]) < 1e-4)
+    assert lst_out.rows() == np.nonzero(~(p_gpu < 0.5))[0].tolist()
+    assert comm.status() == 0
+    # without io the same call must still treat `cur` as the already-normalised input
+    y2 = torch.empty((n_embd,), device="cuda")
+    sp.sparse_ffn_lookahead(comm, ws, ffn=dict(arch=ARCH_PROSPARSE, w_type=F16, up=dev(qu), gate=dev(qg), down_t=dev(qd),
+                                               cur=dev(x_n[0]), n_ff=n_ff, down_b=dev(b_down), flags=flags, out=y2),
+                            list_in=sp.mask_to_list(dev(p[0])))
+    assert rel_err(y2.cpu().numpy(), y_ffn[0]) < tol

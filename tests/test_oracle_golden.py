@@ -178,3 +178,18 @@ def test_f64_restatement_close(oracle):
         y = oracle.sparse_ffn(ARCH_PROSPARSE, t, qu, qg, qd, x, p, E, F)[0]
         y64, _ = oracle.sparse_ffn_f64(ARCH_PROSPARSE, t, qu, qg, qd, x, p, E, F)
         assert rel_err(y, y64) < tol
+
+
+def test_rms_norm_restatement_matches_reference():
+    """the numpy restatement of build_norm(LLM_NORM_RMS) (rms_norm + mul) is bit-exact against the reference's CPU ops"""
+    import oracle_lib
+    if not oracle_lib.Ref.available():
+        pytest.skip("oracle/_ref not built")
+    ref = oracle_lib.Ref()
+    if ref._rms is None:
+        pytest.skip("oracle/_ref predates spif_ref_rms_norm_mul: rebuild it")
+    rng = np.random.default_rng(41)
+    for n_embd, n_tok, eps in ((512, 3, 1e-5), (5120, 2, 1e-6), (1376, 1, 1e-5), (8192, 1, 0.0)):
+        x = (rng.normal(0, 1, (n_tok, n_embd)) * rng.choice([0.01, 1.0, 30.0])).astype(np.float32)
+        w = rng.normal(1, 0.2, n_embd).astype(np.float32)
+        assert np.array_equal(oracle_lib.rms_norm_mul(x, w, eps), ref.rms_norm_mul(x, w, eps)), (n_embd, n_tok)

@@ -62,6 +62,9 @@ def parse_args():
     ap.add_argument("--balance-rounds", type=int, default=0,
                     help="N > 1: rounds of the online shard balancer (observe masks, plan, swap groups) before the timed region")
     ap.add_argument("--balance-tokens", type=int, default=32, help="decode steps observed per balancer round")
+    ap.add_argument("--balance-async", action="store_true",
+                    help="balancer rounds move the rows on a side stream while decoding continues (rebalance_begin / _finish); "
+                         "reports tok/s during the exchange")
     ap.add_argument("--balance-swaps", type=int, default=64, help="max group swaps per layer per balancer round")
     ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
@@ -321,7 +324,7 @@ def run_ours(a):
         n_before = max(50, a.steps // 10)
         ms_before = timed(step_resident, n_before, 5) / n_before
         log('balancer: before-leg timed')
-        rounds, t_obs, t_move, tok = [], 0.0, 0.0, 0
+        rounds, t_obs, t_move, tok, ms_during = [], 0.0, 0.0, 0, []
         for rd in range(a.balance_rounds):
             t0 = time.perf_counter()
             for _ in range(a.balance_tokens):
@@ -331,13 +334,27 @@ def run_ours(a):
             torch.cuda.synchronize()
             t1 = time.perf_counter()
             log(f'balancer round {rd}: observed')
-            r = bal.rebalance(max_swaps=a.balance_swaps)
+            if a.balance_async:
+                # plan -> exec on a side stream while the decode graph keeps replaying -> anchor at a step boundary
+                bal.rebalance_begin(max_swaps=a.balance_swaps)
+                n_during = max(20, a.balance_tokens)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()                       # no barrier, no device-wide synchronize: the side stream keeps moving rows
+                for i in range(n_during):
+                    step_resident(tok + i)
+                e1.record()
+                e1.synchronize()
+                ms_during.append(e0.elapsed_time(e1) / n_during)
+                r = bal.rebalance_finish()
+            else:
+                r = bal.rebalance(max_swaps=a.balance_swaps)
             log(f'balancer round {rd}: moved {r["swaps"]} swaps')
             barrier()
             t2 = time.perf_counter()
             t_obs, t_move = t_obs + (t1 - t0), t_move + (t2 - t1)
             rounds.append({"swaps": r["swaps"], "lambda": r["lambda"], "dfr_imbalance_before": r["imbalance_before"],
-                           "dfr_imbalance_planned": r["imbalance_after"]})
+                           "dfr_imbalance_planned": r["imbalance_after"], "exchange_ms": r.get("exchange_ms"),
+                           "tok_s_during_exchange": (1e3 / ms_during[-1]) if (a.balance_async and ms_during) else None})
         measure_activity()
         act2 = shard_activity()
         balance.update({"active_rows_imbalance_before": balance["active_rows_imbalance"],

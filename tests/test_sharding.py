@@ -157,7 +157,21 @@ def _balancer_worker(rank, world, port, q):
         for l in range(L):                                    # hotness changes completely: the promise cannot hold
             bal.dfr[l] = torch.from_numpy(np.sort(hots[(l + 1) % L])[::-1][rank::world].copy().astype(np.float32))
         bal.rebalance(max_swaps=6)
-        q.put((rank, ok, res, again["imbalance_before"], [s.tolist() for s in bal.slots], lam_calm, bal.lam))
+        lam_drift = bal.lam
+        # the asynchronous form (plan -> staged exchange -> anchor): tables pending until finish, rows follow the tables
+        for l in range(L):
+            bal.dfr[l] = torch.from_numpy(hots[(l + 2) % L][bal.local_groups(l)].astype(np.float32))
+        before_tabs = [s.copy() for s in bal.slots]
+        info = bal.rebalance_begin(max_swaps=6)
+        ok &= all(np.array_equal(a, b) for a, b in zip(before_tabs, bal.slots))       # not committed yet
+        bal.rebalance_finish()
+        ok &= info["swaps"] > 0 and not all(np.array_equal(a, b) for a, b in zip(before_tabs, bal.slots))
+        for l in range(L):
+            mine = bal.local_groups(l)
+            got = layers[l].up.view(torch.float16).reshape(m, E).double().numpy()
+            want = (np.repeat(mine, g)[:, None] * 8 + 0 + 1000 * l) * np.ones((1, E))
+            ok &= bool(np.array_equal(got, want.astype(np.float16).astype(np.float64)))
+        q.put((rank, ok, res, again["imbalance_before"], [s.tolist() for s in bal.slots], lam_calm, lam_drift))
     finally:
         dist.destroy_process_group()
 

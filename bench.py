@@ -63,8 +63,8 @@ def parse_args():
                     help="N > 1: rounds of the online shard balancer (observe masks, plan, swap groups) before the timed region")
     ap.add_argument("--balance-tokens", type=int, default=32, help="decode steps observed per balancer round")
     ap.add_argument("--balance-async", action="store_true",
-                    help="balancer rounds move the rows on a side stream while decoding continues (rebalance_begin / _finish); "
-                         "reports tok/s during the exchange")
+                    help="balancer rounds move the rows in windows between decode steps (rebalance_begin / _step / _finish) "
+                         "instead of all at once; reports tok/s during the exchange")
     ap.add_argument("--balance-swaps", type=int, default=64, help="max group swaps per layer per balancer round")
     ap.add_argument("--no-batched", action="store_true", help="skip the batch 8/32 legs (BASELINE.json configs[2] shape)")
     ap.add_argument("--seed", type=int, default=0x5BA7C0DE)
@@ -335,13 +335,15 @@ def run_ours(a):
             t1 = time.perf_counter()
             log(f'balancer round {rd}: observed')
             if a.balance_async:
-                # plan -> exec on a side stream while the decode graph keeps replaying -> anchor at a step boundary
+                # plan -> one window of the exchange after every decode step -> anchor
                 bal.rebalance_begin(max_swaps=a.balance_swaps)
-                n_during = max(20, a.balance_tokens)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()                       # no barrier, no device-wide synchronize: the side stream keeps moving rows
-                for i in range(n_during):
-                    step_resident(tok + i)
+                e0.record()
+                n_during, left = 0, 1
+                while left > 0:
+                    step_resident(tok + n_during)
+                    left = bal.rebalance_step()
+                    n_during += 1
                 e1.record()
                 e1.synchronize()
                 ms_during.append(e0.elapsed_time(e1) / n_during)
@@ -353,8 +355,9 @@ def run_ours(a):
             t2 = time.perf_counter()
             t_obs, t_move = t_obs + (t1 - t0), t_move + (t2 - t1)
             rounds.append({"swaps": r["swaps"], "lambda": r["lambda"], "dfr_imbalance_before": r["imbalance_before"],
-                           "dfr_imbalance_planned": r["imbalance_after"], "exchange_ms": r.get("exchange_ms"),
-                           "tok_s_during_exchange": (1e3 / ms_during[-1]) if (a.balance_async and ms_during) else None})
+                           "dfr_imbalance_planned": r["imbalance_after"],
+                           "tok_s_during_exchange": (1e3 / ms_during[-1]) if (a.balance_async and ms_during) else None,
+                           "steps_during_exchange": n_during if a.balance_async else None})
         measure_activity()
         act2 = shard_activity()
         balance.update({"active_rows_imbalance_before": balance["active_rows_imbalance"],

@@ -30,14 +30,6 @@ def _row_bytes(t, rows):
     return n // rows
 
 
-class _NullCtx:
-    def __enter__(self):
-        return self
-
-    def __exit__(self, *a):
-        return False
-
-
 class Move(ctypes.Structure):
     """struct spif_move (include/spif_b200.h)"""
     _fields_ = [("layer", ctypes.c_int32), ("round", ctypes.c_int32), ("slot", ctypes.c_int32), ("peer", ctypes.c_int32),
@@ -169,11 +161,14 @@ class ShardBalancer:
             o += n
         self.dfr[l, slot:slot + 1].view(torch.uint8).reshape(-1).copy_(buf[o:o + 4])
 
-    # -- asynchronous form: plan -> exec on a side stream while decoding continues -> anchor at a step boundary --------
+    # -- windowed form: plan -> exec in small windows between decode steps -> anchor ------------------------------------
+    # (The first cut ran the whole exchange on a side stream next to the decode graphs: NCCL's send/recv kernels then sit on
+    # SMs waiting for the peer while the persistent layer kernel needs one CTA on EVERY SM -- rounds with many moves stalled
+    # for seconds, profiles/r2_balancer_async.txt.  Windows in stream order between two steps cannot interlock.)
     def rebalance_begin(self, max_swaps=8, min_gain=0.0):
-        """plan (spif_balancer_plan) and START the row exchange on a side stream: outgoing groups are packed from the live
-        slots (decoding only reads them), incoming groups land in staging buffers.  The caller keeps decoding on its stream and
-        calls rebalance_finish() at a step boundary (the reference's plan -> exec windows -> anchor, ggml-cuda.cu:2499-2606)."""
+        """plan (spif_balancer_plan); nothing moves yet.  Then call rebalance_step() after every decode step until it returns
+        0, and rebalance_finish().  The reference's plan -> exec windows (SPIF_RELOAD_WINDOW_SIZE) -> anchor,
+        ggml-cuda.cu:2499-2606."""
         assert getattr(self, "_staged", None) is None, "finish the previous round first"
         allv = self.slot_scores()
         cap = max(1, 2 * int(max_swaps) * self.L)
@@ -183,56 +178,56 @@ class ShardBalancer:
         _lib.check(self._lib.spif_balancer_plan(self._h, allv.ctypes.data, int(max_swaps), float(min_gain), moves, cap,
                                                 ctypes.byref(n), ctypes.byref(before), ctypes.byref(after), ctypes.byref(tot)),
                    "spif_balancer_plan")
-        moves = [moves[i] for i in range(n.value)]
-        if not hasattr(self, "_side"):
-            self._side = torch.cuda.Stream(device=self.dfr.device) if self.dfr.is_cuda else None
-        staged, moved, i = {}, 0, 0   # (layer, slot) -> the group that will live there after the anchor
-        main = torch.cuda.current_stream() if self._side is not None else None
-        ctx = torch.cuda.stream(self._side) if self._side is not None else _NullCtx()
-        if self._side is not None:
-            self._side.wait_stream(main)
-            self._t0 = torch.cuda.Event(enable_timing=True)
-            self._t0.record(self._side)
-        with ctx:
-            while self.world > 1 and i < len(moves):
-                k, c0 = moves[i].round, moves[i].layer // self.LAYER_CHUNK
-                ops_, batch = [], []
-                while i < len(moves) and moves[i].round == k and moves[i].layer // self.LAYER_CHUNK == c0:
-                    mv = moves[i]
-                    key = (mv.layer, mv.slot)
-                    out = staged[key] if key in staged else self._pack(mv.layer, mv.slot)  # a group that arrived in an earlier round
-                    inc = torch.empty_like(out)
-                    ops_.append(dist.P2POp(dist.isend, out, mv.peer, group=self.group))
-                    ops_.append(dist.P2POp(dist.irecv, inc, mv.peer, group=self.group))
-                    batch.append((key, inc, out))
-                    moved += out.numel()
-                    i += 1
-                for r in dist.batch_isend_irecv(ops_):
-                    r.wait()  # stream-level: the side stream waits, the host and the decode stream do not
-                for key, inc, _keep in batch:
-                    staged[key] = inc
-            if self._side is not None:
-                self._t1 = torch.cuda.Event(enable_timing=True)
-                self._t1.record(self._side)
-        self._staged = staged
-        self.bytes_moved += moved
+        self._moves, self._next = [moves[i] for i in range(n.value)], 0
+        self._staged = {}   # (layer, slot) -> the group that will live there after the anchor
+        # windows are cut by (round, layer chunk) -- a global rule, so that both ends of every move agree -- and every rank
+        # walks ALL windows, also the ones in which it has nothing to move
+        self._windows = [(k, c) for k in range(int(max_swaps)) for c in range(0, self.L, self.LAYER_CHUNK)]
+        self._w = 0
         self._info = {"imbalance_before": float(before.value), "imbalance_after": float(after.value), "swaps": int(tot.value),
-                      "bytes_sent_this_rank": int(moved)}
+                      "bytes_sent_this_rank": 0}
         return dict(self._info)
 
-    def rebalance_finish(self):
-        """the anchor: the caller's stream waits for the staged groups, copies them into their slots (device-to-device, in
-        stream order between two decode steps) and the library's pending tables become current."""
+    def rebalance_step(self):
+        """one window of the exchange on the CURRENT stream (call it between two decode steps): outgoing groups are packed from
+        the live slots, incoming groups land in staging buffers.  -> windows left"""
         assert getattr(self, "_staged", None) is not None
-        if self._side is not None:
-            torch.cuda.current_stream().wait_event(self._t1)
+        # exactly ONE window per call, empty or not: with more than two shards every rank must be in the same window after the
+        # same decode step (a rank that ran ahead would wait in a receive for a peer whose next decode step waits for it)
+        if self._w < len(self._windows):
+            k, c0 = self._windows[self._w]
+            self._w += 1
+            ops_, batch = [], []
+            while (self._next < len(self._moves) and self._moves[self._next].round == k
+                   and c0 <= self._moves[self._next].layer < c0 + self.LAYER_CHUNK):
+                mv = self._moves[self._next]
+                self._next += 1
+                key = (mv.layer, mv.slot)
+                out = self._staged[key] if key in self._staged else self._pack(mv.layer, mv.slot)  # arrived in an earlier round
+                inc = torch.empty_like(out)
+                ops_.append(dist.P2POp(dist.isend, out, mv.peer, group=self.group))
+                ops_.append(dist.P2POp(dist.irecv, inc, mv.peer, group=self.group))
+                batch.append((key, inc, out))
+                self._info["bytes_sent_this_rank"] += out.numel()
+            if ops_ and self.world > 1:
+                for r in dist.batch_isend_irecv(ops_):
+                    r.wait()  # stream-level for NCCL: the next decode step is ordered behind the window, the host is not blocked
+                for key, inc, _keep in batch:
+                    self._staged[key] = inc
+        return len(self._windows) - self._w
+
+    def rebalance_finish(self):
+        """the anchor: remaining windows, then the staged groups are copied into their slots (device-to-device, in stream order
+        between two decode steps) and the library's pending tables become current."""
+        assert getattr(self, "_staged", None) is not None
+        while self.rebalance_step() > 0:
+            pass
+        assert self._next == len(self._moves)
         for (l, slot), inc in self._staged.items():
             self._unpack(l, slot, inc)
         _lib.check(self._lib.spif_balancer_commit(self._h), "spif_balancer_commit")
+        self.bytes_moved += self._info["bytes_sent_this_rank"]
         info = dict(self._info, **{"lambda": self.lam})
-        if self._side is not None:
-            torch.cuda.current_stream().synchronize()
-            info["exchange_ms"] = float(self._t0.elapsed_time(self._t1))
         self._staged = None
         return info
 

@@ -61,14 +61,35 @@ const ggml_cuda_device_info & ggml_cuda_info() {
     }();
     return info;
 }
+// a caching pool like the reference's ggml_cuda_pool_leg (ggml-cuda.cu): freed buffers are kept and handed out again, so the
+// Q8_0 path's scratch (quantised activations, mmq-sparse.cu:339) is allocated in the eager warm-up and only REUSED while the
+// stream is being captured into a CUDA graph
 struct refcuda_pool : public ggml_cuda_pool {
+    std::vector<std::pair<void *, size_t>> cache;
     void * alloc(size_t size, size_t * actual_size) override {
+        int best = -1;
+        for (int i = 0; i < (int) cache.size(); ++i) {
+            if (cache[i].second >= size && (best < 0 || cache[i].second < cache[best].second)) {
+                best = i;
+            }
+        }
+        if (best >= 0) {
+            void * p     = cache[best].first;
+            *actual_size = cache[best].second;
+            cache.erase(cache.begin() + best);
+            return p;
+        }
         void * p = nullptr;
         CUDA_CHECK(cudaMalloc(&p, size));
         *actual_size = size;
         return p;
     }
-    void free(void * ptr, size_t) override { cudaFree(ptr); }
+    void free(void * ptr, size_t size) override { cache.emplace_back(ptr, size); }
+    ~refcuda_pool() {
+        for (auto & c : cache) {
+            cudaFree(c.first);
+        }
+    }
 };
 std::unique_ptr<ggml_cuda_pool> ggml_backend_cuda_context::new_pool_for_device(int, int) {
     return std::unique_ptr<ggml_cuda_pool>(new refcuda_pool());

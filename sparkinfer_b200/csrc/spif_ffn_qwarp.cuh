@@ -107,6 +107,23 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
         pdl_wait_prior_grid();
     }
     SPIF_STAMP(1);
+    // this thread's part of x (8 lanes per 32-block, one float4 each; XQ = 4 covers every launch shape: threads >= n_embd / 16).
+    // Without MASK_STABLE x is already valid here: request it BEFORE the mask scan, whose L2 round trips then cover its latency.
+    constexpr int XQ = 4;
+    float4        xv[XQ];
+    auto load_x = [&]() {
+        const int wi = lane & 7, bstep = NT >> 3;
+#pragma unroll
+        for (int u = 0; u < XQ; ++u) {
+            const int b = (tid >> 3) + u * bstep;
+            xv[u]       = (MODE != SPIF_MODE_AXPY && b < nblk) ?
+                              __ldg(reinterpret_cast<const float4 *>(p.x + (size_t) blockIdx.y * p.n_embd + (size_t) b * 32) + wi) :
+                              make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    if (!early) {
+        load_x();
+    }
     const float * mask  = p.mask + (size_t) tok * p.mask_len;
     const float * xg    = p.x + (size_t) tok * p.n_embd;
     const float * hid   = (MODE == SPIF_MODE_AXPY) ? p.hid_in + (size_t) tok * p.n_ff : nullptr;
@@ -140,6 +157,7 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
     }
     if (early) {
         pdl_wait_prior_grid();  // x, y and the partials workspace belong to the previous kernels until here
+        load_x();
     }
     pdl_launch_dependents();
 
@@ -147,16 +165,10 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
     // All of a thread's loads are issued first (XQ = 4 covers every launch shape: threads >= n_embd / 16): the first cut did a
     // dependent L2 round trip per block group, 3 us of the layer's 10.
     if (MODE != SPIF_MODE_AXPY) {
-        constexpr int XQ  = 4;
         const bool    cpu = (p.flags & SPIF_FLAG_CPU_ROUNDING) != 0;
         const int     wi  = lane & 7, bstep = NT >> 3;
-        for (int b0 = (tid >> 3); b0 < nblk; b0 += XQ * bstep) {
-            float4 xv[XQ];
-#pragma unroll
-            for (int u = 0; u < XQ; ++u) {
-                const int b = b0 + u * bstep;
-                xv[u]       = (b < nblk) ? __ldg(reinterpret_cast<const float4 *>(xg + (size_t) b * 32) + wi) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+        {
+            const int b0 = tid >> 3;
 #pragma unroll
             for (int u = 0; u < XQ; ++u) {
                 const int    b = b0 + u * bstep;  // (b < nblk) is uniform over the 8 lanes of a block and over whole warps' shuffles
@@ -172,19 +184,19 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
                 int         sm = 0, w = 0;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    // default = the CUDA reference's roundf(x / d) (quantize.cu:29).  x * id is within 1.1e-5 of x / d for
-                    // |x / d| <= 127, so the two round alike unless x * id is that close to a half-integer: only then divide
-                    // (the IEEE division was a third of the x stage's instructions).  Bit-identical to roundf(x / d).
+                    // default = the CUDA reference's roundf(x / d) (quantize.cu:29).  t = x * id is within 1.1e-5 of x / d for
+                    // |x / d| <= 127, and round-to-nearest-even of t equals roundf(x / d) unless t is that close to a half-integer
+                    // (where ties-away and a last-bit difference matter): only then divide and roundf.  Bit-identical to
+                    // roundf(x / d); the IEEE division + roundf for every element was a third of the x stage.
                     int q;
                     if (cpu) {
                         q = __float2int_rn(e4[e] * id);
                     } else {
                         const float t = e4[e] * id;
-                        float       r = roundf(t);
-                        if (fabsf(fabsf(t - truncf(t)) - 0.5f) < 1e-4f) {
-                            r = roundf(e4[e] / d);
+                        q             = __float2int_rn(t);  // amax == 0: id == 0 -> t == 0 -> q == 0
+                        if (fabsf(t - (float) q) > 0.5f - 1e-4f) {
+                            q = (int) roundf(e4[e] / d);
                         }
-                        q = (int) r;  // amax == 0: id == 0 -> t == 0 -> q == 0
                     }
                     sm += q;
                     w |= (q & 0xff) << (8 * e);
@@ -238,6 +250,11 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
                 const unsigned char * up = slot_ptr(warp);
                 const unsigned char * gt = up + p.row_bytes;
                 mbar_wait_spin(bars + 2 * warp, par);
+#ifdef SPIF_QW_TRACE_LANDED
+                if (round == 0 && warp == 0) {
+                    SPIF_STAMP(5);
+                }
+#endif
                 float su = 0.f, sg = 0.f;
                 for (int pr = lane; pr < np; pr += 32) {
                     const uint4  q0 = xq[pr], q1 = xq[np + pr], q2 = xq[2 * np + pr], q3 = xq[3 * np + pr];
@@ -407,7 +424,9 @@ __global__ void __launch_bounds__(MAXT, (MAXT <= 320 ? 2 : 1)) spif_ffn_qwarp_ke
             st[1]        = n_nonzero;
         }
     }
+#ifndef SPIF_QW_TRACE_LANDED
     SPIF_STAMP(5);
+#endif
     if (p.trace && tid == 0 && blockIdx.y == 0) {
         p.trace[(size_t) blockIdx.x * 8 + 6] = (unsigned long long) n;
     }

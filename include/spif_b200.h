@@ -83,6 +83,7 @@ enum spif_error {
     SPIF_E_WORKSPACE   = -4, /* ws too small / misaligned */
     SPIF_E_UNSUPPORTED = -5,
     SPIF_E_NO_DEVICE   = -6,
+    SPIF_E_STATIC_LIMIT = -7, /* spif_sparse_ffn_noalloc: the shape needs more scratch than the library's static array holds */
 };
 
 int          spif_abi_version(void);
@@ -331,6 +332,21 @@ int  spif_balancer_plan(spif_balancer * b, const float * slot_scores_host, int m
                         int moves_cap, int * n_moves, float * imbalance_before, float * imbalance_after, int * n_swaps_total);
 int  spif_balancer_commit(spif_balancer * b);
 int  spif_balancer_abort(spif_balancer * b);
+
+/* ---- allocation-free single-token layer (NO counterpart in the reference) ----
+ * spif_sparse_ffn for callers that can neither call cudaMalloc nor own a workspace (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid allocation): the scratch is a file-scope static __device__ array inside the library,
+ * SPIF_NOALLOC_WS_BYTES (12 MiB) on every GPU that loads the library, held until the process exits.  The call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine); inputs and outputs are still the caller's (args as for
+ * spif_sparse_ffn, n_tok == 1 only -- otherwise SPIF_E_UNSUPPORTED).  A shape whose spif_workspace_size(n_embd, n_ff, 1)
+ * exceeds the array returns SPIF_E_STATIC_LIMIT (every BASELINE.json architecture fits: ReluLLaMA-70B needs 10.2 MiB).
+ * ALL calls on a device share the one array, which keeps the previous call's contents (nothing in it has to start at zero:
+ * every CTA writes its partial row and counters before they are summed).  Calls on one stream are ordered and safe; calls
+ * that OVERLAP on the GPU (other streams, concurrent host threads on one device) RACE on it -- use spif_sparse_ffn with
+ * separate workspaces there.  Results are bit-identical to spif_sparse_ffn on the same inputs. */
+#define SPIF_NOALLOC_WS_BYTES (12u << 20)
+size_t spif_noalloc_max_bytes(void);
+int    spif_sparse_ffn_noalloc(const spif_ffn_args * args, spif_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -67,6 +67,8 @@ SYMBOLS = {
                                         ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
     "spif_sparse_ffn_lookahead_ex": (c_i, [ctypes.POINTER(FfnArgs), ctypes.POINTER(PredArgs), ctypes.POINTER(LayerIo), c_vp, c_vp,
                                            ctypes.POINTER(ShardCommStruct), c_vp, c_sz, c_vp]),
+    "spif_noalloc_max_bytes": (c_sz, []),
+    "spif_sparse_ffn_noalloc": (c_i, [ctypes.POINTER(FfnArgs), c_vp]),
     "spif_initial_placement": (c_i, [c_vp, c_i, c_i, c_vp]),
     "spif_rebalance_plan": (c_i, [c_vp, c_vp, c_i, c_i, c_i, c_f, c_vp, ctypes.POINTER(c_i)]),
     "spif_cache_group_budget": (c_i, [c_i64, c_i64, c_i, c_vp, c_i, c_i, c_vp]),

@@ -71,6 +71,8 @@ const char * spif_error_string(int code) {
             return "configuration not supported";
         case SPIF_E_NO_DEVICE:
             return "no CUDA device";
+        case SPIF_E_STATIC_LIMIT:
+            return "shape needs more scratch than the library's static array (SPIF_NOALLOC_WS_BYTES): use spif_sparse_ffn with a workspace";
         default:
             return code > 0 ? cudaGetErrorString((cudaError_t) code) : "unknown spif error";
     }

@@ -132,6 +132,38 @@ class FfnStack:
         self.launches_per_step = n
         return n
 
+    def step_overlap(self):
+        """the reference's data edges with the one overlap they allow: predictor(l+1) reads x_l, which in a real decode exists
+        only after FFN(l-1) (its y feeds the attention block that produces x_l), so predictor(l+1) starts after FFN(l-1) and
+        runs BESIDE FFN(l) on a second stream; FFN(l) waits for predictor(l).  Unlike step_two_streams the predictor chain cannot
+        run ahead of the FFN chain.  Used where the single-launch layer kernel does not apply (quantised FFN weights)."""
+        main = torch.cuda.current_stream()
+        side = self._side
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            n = self.predict(0, 0)
+            ev_p = torch.cuda.Event()
+            ev_p.record(side)
+        ev_f_prev = None
+        for l in range(self.L):
+            ev_next = None
+            if l + 1 < self.L:
+                if ev_f_prev is not None:
+                    side.wait_event(ev_f_prev)
+                with torch.cuda.stream(side):
+                    n += self.predict(l + 1, l)
+                    ev_next = torch.cuda.Event()
+                    ev_next.record(side)
+            main.wait_event(ev_p)
+            n += self.ffn(l, False, mask_stable=self.early_mask, exchange=True)  # full edge from predictor l
+            self.allreduce(l)
+            ev_f_prev = torch.cuda.Event()
+            ev_f_prev.record(main)
+            ev_p = ev_next
+        main.wait_stream(side)
+        self.launches_per_step = n
+        return n
+
     # -- look-ahead layer kernel: FFN(l) + predictor(l+1) in ONE launch (spif_sparse_ffn_lookahead) ------------------
     def fused_supported(self):
         return (self.n_tok == 1 and self.comm is not None and self.w_type == self.p_type and self.r % 256 == 0

@@ -139,7 +139,8 @@ int spif_predictor(int ptype, const void * wpu, const float * bpu, const void * 
  * n_tok == 1: one persistent kernel (+ fixed-order partial sum).  2 <= n_tok <= 32 with F16/BF16 weights and
  * n_embd % 512 == 0: the union of the per-token masks becomes a gathered GEMM on the tensor cores (tcgen05, accumulators
  * in tensor memory) -- every union row is read once instead of once per token as in mm-sparse.cu:107-210; x and the
- * hidden values are rounded to the weight float type there (the reference CPU backend's semantics).  Q8_0 / Q4_0 take the
+ * hidden values are rounded to the weight float type there (the reference CPU backend's semantics; F16 hidden values beyond
+ * +-65504 saturate instead of becoming inf -- the reference CUDA kernels keep them in F32 and stay finite).  Q8_0 / Q4_0 take the
  * same union GEMM (rows dequantised into F16 tiles) from 13 tokens on; up to 12 tokens, other shapes and
  * SPIF_FLAG_PER_TOKEN use the per-(row, token) schedule (quantised: one CTA row per token, 8-bit activations like mmq-sparse.cu).  stats_out[t] = {active, non-zero hidden} per token; the
  * union path also reports {.., .., union rows, union rows with a non-zero hidden value}.

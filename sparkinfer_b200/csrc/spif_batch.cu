@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(BATCH_NP(QT) + 32, 1) spif_batch_gateup_kernel
                                 p.hidden_out[(size_t) t * p.n_ff + s_neu[buf + r]] = h;
                             }
                         }
-                        const uint16_t hb = f32_to_wt_bits<WT>(h);
+                        const uint16_t hb = f32_to_wt_bits<WT>(saturate_to_wt<WT>(h));
                         const bool     nz = (hb & 0x7fffu) != 0;
                         if (lane < 16 && t < TP) {
                             p.hh[(size_t) t * p.m_pad + slot0 + r] = hb;

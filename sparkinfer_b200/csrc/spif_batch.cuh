@@ -117,6 +117,12 @@ template <> __device__ __forceinline__ uint16_t f32_to_wt_bits<spif_f16>(float v
 template <> __device__ __forceinline__ uint16_t f32_to_wt_bits<spif_bf16>(float v) {
     return __bfloat16_as_ushort(__float2bfloat16_rn(v));
 }
+// hidden values of the union GEMM travel in the weight float type: F16 would turn |h| > 65504 into inf (and y into inf / NaN)
+// where the reference CUDA kernels, which keep hidden in F32 (axpy-sparse.cu:44), stay finite -> saturate; NaN stays NaN
+template <typename WT> __device__ __forceinline__ float saturate_to_wt(float v) { return v; }
+template <> __device__ __forceinline__ float saturate_to_wt<spif_f16>(float v) {
+    return (v != v) ? v : fminf(fmaxf(v, -65504.0f), 65504.0f);
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Q8_0 / Q4_0 block PAIRS (64 consecutive weights) -> 64 F16 values = 8 x 16-byte operand chunks.

@@ -141,3 +141,23 @@ def test_shard_exchange_single_rank_self_exchange(oracle):
             assert torch.equal(y0, y1)
         y2 = sp.shard_allreduce(y0.clone(), comm)
         assert torch.equal(y0, y2)
+
+
+def test_batched_f16_hidden_saturates_instead_of_inf(oracle):
+    """union GEMM, F16: hidden values beyond the F16 range must saturate at +-65504, not turn y into inf / NaN (the
+    reference CUDA kernels keep hidden in F32, axpy-sparse.cu:44).  Expected y from the kernel's own F32 hidden_out."""
+    import sparkinfer_b200 as sp
+    n_embd, n_ff, n_tok = 512, 1024, 4
+    seed = synth.SEED0 + 991
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (oracle.quantize(F16, w) for w in (Wu * 40, Wg * 40, Wd))   # big gate / up values: |h| reaches 1e5 and more
+    x = (synth.activations(n_embd, n_tok, seed + 1) * 20).astype(np.float32)
+    p = synth.direct_mask(n_ff, n_tok, 0.2, seed + 2)
+    ws = sp.Workspace(n_embd, n_ff, n_tok)
+    y, hid = sp.sparse_ffn(ARCH_PROSPARSE, F16, dev(qu), dev(qg), dev(qd), dev(x), dev(p), n_ff, want_hidden=True, ws=ws)
+    y, hid = y.cpu().numpy(), hid.cpu().numpy()
+    assert np.abs(hid).max() > 65504.0, "the case must overflow F16"
+    assert np.all(np.isfinite(y))
+    h16 = np.clip(hid, -65504.0, 65504.0).astype(np.float16).astype(np.float64)
+    want = h16 @ Wd.astype(np.float16).astype(np.float64)
+    assert rel_err(y, want.astype(np.float32)) < 2e-3

@@ -1,0 +1,176 @@
+// glue_harness.cu -- TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// Runs glue/ggml_cuda_spif.cu -- the binding a SparkInfer maintainer adds to ggml-cuda -- for real: on the reference's OWN
+// structures (ggml_context, ggml_tensor, ggml_cgraph, ggml_backend_cuda_context with its pool), on a graph built with the
+// reference's OWN constructors in the order build_sparse_ffn emits it (src/llama-graph.cpp:969-971, 979-981, 1063-1098),
+// next to the reference's OWN CUDA kernels on the same graph.  Three passes over one layer, n_tok == 1, gpu_only:
+//   A  reference kernels node by node (dispatch as ggml-cuda.cu:2463-2497,2802-2807; kernels from libspif_refcuda.so)
+//   B  the same node loop with the sparse ops routed to spif_glue_mul_mat_sparse / _axpy_sparse / _fatrelu
+//   C  the node loop with the fusion hook: spif_glue_try_fuse_sparse_ffn(ctx, cgraph, 0) -- one spif_sparse_ffn call
+// Built by oracle/Makefile into _ref/libspif_gluetest.so (links libspif_refcuda.so, libspif_ref.so, libspif_b200.so);
+// driven by tests/test_glue.py (-m gpu).  The full llama-cli run needs the whole reference build and a
+// model file and is not attempted; this is the op-level drop-in check on real hardware.
+#include "common.cuh"
+#include "ggml.h"
+#include "mm-sparse.cuh"
+#include "axpy-sparse.cuh"
+#include "unary.cuh"
+#include "binbcast.cuh"
+
+#include <cstring>
+#include <vector>
+
+// glue/ggml_cuda_spif.cu
+void spif_glue_mul_mat_sparse(ggml_backend_cuda_context & ctx, const ggml_tensor * src0, const ggml_tensor * src1, ggml_tensor * dst);
+void spif_glue_axpy_sparse(ggml_backend_cuda_context & ctx, const ggml_tensor * src0, const ggml_tensor * src1, ggml_tensor * dst);
+void spif_glue_fatrelu(ggml_backend_cuda_context & ctx, ggml_tensor * dst);
+int  spif_glue_try_fuse_sparse_ffn(ggml_backend_cuda_context & ctx, ggml_cgraph * cgraph, int i);
+
+namespace {
+
+ggml_tensor * leaf(ggml_context * c, ggml_type type, int64_t ne0, int64_t ne1, const void * dev_ptr) {
+    ggml_tensor * t = ggml_new_tensor_2d(c, type, ne0, ne1);
+    t->data         = const_cast<void *>(dev_ptr);
+    return t;
+}
+
+// one node through the reference's kernels (n_tok == 1: the arguments ggml_cuda_op_mul_mat would forward on one device)
+void ref_node(ggml_backend_cuda_context & ctx, ggml_tensor * n) {
+    cudaStream_t st = ctx.stream();
+    switch (n->op) {
+        case GGML_OP_MUL_MAT_SPARSE:
+            ggml_cuda_op_mul_mat_sparse(ctx, n->src[0], n->src[1], n, (const char *) n->src[0]->data, (const float *) n->src[1]->data,
+                                        nullptr, (float *) n->data, 0, n->src[0]->ne[1], 1, n->src[0]->ne[0], st);
+            break;
+        case GGML_OP_AXPY_SPARSE:
+            ggml_cuda_op_axpy_sparse(ctx, n->src[0], n->src[1], n, (const char *) n->src[0]->data, (const float *) n->src[1]->data,
+                                     nullptr, (float *) n->data, 0, n->src[0]->ne[1], 1, n->src[0]->ne[1], st);
+            break;
+        case GGML_OP_FATRELU:
+            ggml_cuda_op_fatrelu(ctx, n);
+            break;
+        case GGML_OP_UNARY:
+            GGML_ASSERT(ggml_get_unary_op(n) == GGML_UNARY_OP_RELU);
+            ggml_cuda_op_relu(ctx, n);
+            break;
+        case GGML_OP_MUL:
+            ggml_cuda_op_mul(ctx, n);
+            break;
+        default:
+            GGML_ABORT("glue harness: unexpected op %s", ggml_op_name(n->op));
+    }
+}
+
+}  // namespace
+
+extern "C" int spif_gluetest_layer(int arch, int wtype, const void * w_up, const void * w_gate, const void * w_down, const float * x,
+                                   const float * sparse_idx, int n_embd, int n_ff, float * up_ref, float * up_glue, float * y_ref,
+                                   float * y_glue_ops, float * y_glue_fused, int * nodes_total, int * nodes_fused) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        return -1;
+    }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    ggml_backend_cuda_context ctx(dev);
+    cudaStream_t              st = ctx.stream();
+
+    ggml_init_params ip = { ggml_tensor_overhead() * 64 + ggml_graph_overhead(), nullptr, /*no_alloc=*/true };
+    ggml_context *   c  = ggml_init(ip);
+    ggml_cgraph *    gf = ggml_new_graph(c);
+    ggml_tensor *    Wu = leaf(c, (ggml_type) wtype, n_embd, n_ff, w_up);
+    ggml_tensor *    Wg = arch != 2 ? leaf(c, (ggml_type) wtype, n_embd, n_ff, w_gate) : nullptr;
+    ggml_tensor *    Wd = leaf(c, (ggml_type) wtype, n_embd, n_ff, w_down);
+    ggml_tensor *    X  = leaf(c, GGML_TYPE_F32, n_embd, 1, x);
+    ggml_tensor *    P  = leaf(c, GGML_TYPE_F32, n_ff, 1, sparse_idx);
+    // build_sparse_ffn, gpu_only (src/llama-graph.cpp:969-971, 979-981, 1063-1098): each sparse op is expanded where it is built
+    ggml_tensor * cur_up = ggml_mul_mat_sparse(c, Wu, X, P, nullptr);
+    ggml_build_forward_expand(gf, cur_up);
+    ggml_tensor * first_up = cur_up;
+    ggml_tensor * cur_gate = nullptr;
+    if (Wg) {
+        cur_gate = ggml_mul_mat_sparse(c, Wg, X, P, nullptr);
+        ggml_build_forward_expand(gf, cur_gate);
+    }
+    ggml_tensor * hid = nullptr;
+    switch (arch) {
+        case 0:
+            cur_gate = ggml_fatrelu(c, cur_gate, 0.01f, false);
+            hid      = ggml_mul(c, cur_gate, cur_up);
+            break;
+        case 1:
+            cur_up   = ggml_relu(c, cur_up);
+            cur_gate = ggml_relu(c, cur_gate);
+            hid      = ggml_mul(c, cur_gate, cur_up);
+            break;
+        default:
+            hid = ggml_relu(c, cur_up);
+            break;
+    }
+    ggml_tensor * down = ggml_axpy_sparse(c, Wd, hid, P, nullptr);
+    ggml_build_forward_expand(gf, down);
+
+    const int          n_nodes = ggml_graph_n_nodes(gf);
+    std::vector<void *> bufs;
+    for (int i = 0; i < n_nodes; ++i) {
+        ggml_tensor * n = ggml_graph_node(gf, i);
+        void *        d = nullptr;
+        CUDA_CHECK(cudaMalloc(&d, ggml_nbytes(n)));
+        n->data = d;
+        bufs.push_back(d);
+    }
+    auto poison = [&]() {
+        for (int i = 0; i < n_nodes; ++i) {
+            ggml_tensor * n = ggml_graph_node(gf, i);
+            CUDA_CHECK(cudaMemsetAsync(n->data, 0xFF, ggml_nbytes(n), st));  // NaN: a node nobody wrote shows up
+        }
+    };
+    auto fetch = [&](ggml_tensor * n, float * dst) {
+        CUDA_CHECK(cudaMemcpyAsync(dst, n->data, ggml_nbytes(n), cudaMemcpyDeviceToDevice, st));
+    };
+    // A: the reference's kernels
+    poison();
+    for (int i = 0; i < n_nodes; ++i) {
+        ref_node(ctx, ggml_graph_node(gf, i));
+    }
+    fetch(first_up, up_ref);
+    fetch(down, y_ref);
+    // B: the sparse ops through the glue, everything else through the reference's stock kernels
+    poison();
+    for (int i = 0; i < n_nodes; ++i) {
+        ggml_tensor * n = ggml_graph_node(gf, i);
+        if (n->op == GGML_OP_MUL_MAT_SPARSE) {
+            spif_glue_mul_mat_sparse(ctx, n->src[0], n->src[1], n);
+        } else if (n->op == GGML_OP_AXPY_SPARSE) {
+            spif_glue_axpy_sparse(ctx, n->src[0], n->src[1], n);
+        } else if (n->op == GGML_OP_FATRELU) {
+            spif_glue_fatrelu(ctx, n);
+        } else {
+            ref_node(ctx, n);
+        }
+    }
+    fetch(first_up, up_glue);
+    fetch(down, y_glue_ops);
+    // C: the node loop with the fusion hook
+    poison();
+    int fused = 0;
+    for (int i = 0; i < n_nodes;) {
+        const int used = spif_glue_try_fuse_sparse_ffn(ctx, gf, i);
+        if (used > 0) {
+            fused += used;
+            i += used;
+        } else {
+            ref_node(ctx, ggml_graph_node(gf, i));
+            ++i;
+        }
+    }
+    fetch(down, y_glue_fused);
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    *nodes_total = n_nodes;
+    *nodes_fused = fused;
+    for (void * d : bufs) {
+        cudaFree(d);
+    }
+    ggml_free(c);
+    return 0;
+}

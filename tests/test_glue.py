@@ -27,3 +27,58 @@ def test_glue_compiles_against_reference_headers(tmp_path):
         assert name in syms, name
     for name in ("spif_mul_mat_sparse", "spif_axpy_sparse", "spif_sparse_ffn", "spif_sparse_ffn_lookahead"):
         assert f"U {name}" in syms, f"glue must bind the C-ABI symbol {name}"
+
+
+# ---- the glue, executed on a GPU (oracle/glue_harness.cu): the reference's graph, context and pool; its kernels beside ours
+GLUETEST = os.path.join(ROOT, "oracle", "_ref", "libspif_gluetest.so")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("arch", [0, 1, 2])
+@pytest.mark.parametrize("n_embd,n_ff", [(1024, 4096), (5120, 13824)])
+def test_glue_runs_reference_graph_on_gpu(arch, n_embd, n_ff):
+    """One layer of build_sparse_ffn's graph (built with the reference's constructors, in its node order) three ways: the
+    reference's CUDA kernels node by node, the same loop with the sparse ops routed through glue/ggml_cuda_spif.cu, and the
+    loop with the fusion hook (one spif_sparse_ffn call).  Tolerances: against the reference kernels 2e-3 (they accumulate
+    in half2 at GGML_PREC_DEFAULT, mm-sparse.cu:355-361, and add with float atomics); against the CPU oracle 1e-3."""
+    import ctypes
+
+    import numpy as np
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    if not os.path.exists(GLUETEST):
+        pytest.skip("oracle/_ref/libspif_gluetest.so not built (needs /root/reference at build time)")
+    import synth
+    from oracle_lib import F16, Oracle
+    lib = ctypes.CDLL(GLUETEST)
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    lib.spif_gluetest_layer.restype = ci
+    lib.spif_gluetest_layer.argtypes = [ci, ci] + [vp] * 5 + [ci, ci] + [vp] * 5 + [ctypes.POINTER(ci), ctypes.POINTER(ci)]
+    o = Oracle()
+    seed = synth.SEED0 + 5 * n_embd + n_ff + arch
+    Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+    qu, qg, qd = (o.quantize(F16, w) for w in (Wu, Wg, Wd))
+    x = synth.activations(n_embd, 1, seed + 1)
+    p = synth.direct_mask(n_ff, 1, 0.10, seed + 2)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    du, dg, dd, dx, dp = dev(qu), dev(qg), dev(qd), dev(x[0]), dev(p[0])
+    up_ref, up_glue = torch.empty(n_ff, device="cuda"), torch.empty(n_ff, device="cuda")
+    y_ref, y_ops, y_fused = (torch.empty(n_embd, device="cuda") for _ in range(3))
+    n_total, n_fused = ci(0), ci(0)
+    ptr = lambda t: vp(t.data_ptr())
+    rc = lib.spif_gluetest_layer(arch, F16, ptr(du), ptr(dg), ptr(dd), ptr(dx), ptr(dp), n_embd, n_ff, ptr(up_ref), ptr(up_glue),
+                                 ptr(y_ref), ptr(y_ops), ptr(y_fused), ctypes.byref(n_total), ctypes.byref(n_fused))
+    assert rc == 0
+    torch.cuda.synchronize()
+    rel = lambda a, b: float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+    up_ref, up_glue, y_ref, y_ops, y_fused = (t.cpu().numpy() for t in (up_ref, up_glue, y_ref, y_ops, y_fused))
+    act = ~(p[0] < 0.5)
+    assert np.all(up_glue[~act] == 0.0) and np.all(up_ref[~act] == 0.0)          # dense, zero-filled dst (mm-sparse.cu:397)
+    assert rel(up_glue, up_ref) < 2e-3, rel(up_glue, up_ref)
+    assert rel(y_ops, y_ref) < 2e-3, rel(y_ops, y_ref)
+    assert rel(y_fused, y_ref) < 2e-3, rel(y_fused, y_ref)
+    assert n_total.value == {0: 5, 1: 6, 2: 3}[arch] and n_fused.value == n_total.value  # the whole layer became one call
+    y_cpu = o.sparse_ffn(arch, F16, qu, qg, qd, x, p, n_embd, n_ff)[0][0]
+    assert rel(y_ops, y_cpu) < 1e-3 and rel(y_fused, y_cpu) < 1e-3
+    assert rel(up_glue, o.mul_mat_sparse(F16, qu, x, p, n_embd, n_ff)[0]) < 1e-3

@@ -14,6 +14,8 @@
 #include "ggml.h"
 #include "mm-sparse.cuh"
 #include "axpy-sparse.cuh"
+#include "mmq-sparse.cuh"
+#include "axpyq-sparse.cuh"
 #include "unary.cuh"
 #include "binbcast.cuh"
 
@@ -39,10 +41,19 @@ void ref_node(ggml_backend_cuda_context & ctx, ggml_tensor * n) {
     cudaStream_t st = ctx.stream();
     switch (n->op) {
         case GGML_OP_MUL_MAT_SPARSE:
+            if (n->src[0]->type == GGML_TYPE_Q8_0) {  // ggml-cuda.cu:2474-2476
+                ggml_cuda_mul_mat_sparse_q(ctx, n->src[0], n->src[1], n);
+                break;
+            }
             ggml_cuda_op_mul_mat_sparse(ctx, n->src[0], n->src[1], n, (const char *) n->src[0]->data, (const float *) n->src[1]->data,
                                         nullptr, (float *) n->data, 0, n->src[0]->ne[1], 1, n->src[0]->ne[0], st);
             break;
         case GGML_OP_AXPY_SPARSE:
+            if (n->src[0]->type == GGML_TYPE_Q8_0) {  // ggml-cuda.cu:2491-2493
+                ggml_cuda_op_axpy_sparse_q(ctx, n->src[0], n->src[1], n, (const char *) n->src[0]->data, (const float *) n->src[1]->data,
+                                           nullptr, (float *) n->data, 0, n->src[0]->ne[1], 1, n->src[0]->ne[1], st);
+                break;
+            }
             ggml_cuda_op_axpy_sparse(ctx, n->src[0], n->src[1], n, (const char *) n->src[0]->data, (const float *) n->src[1]->data,
                                      nullptr, (float *) n->data, 0, n->src[0]->ne[1], 1, n->src[0]->ne[1], st);
             break;

@@ -150,11 +150,13 @@ struct spif_glue_lookahead_state {
     void *          list[2];   // spif_active_list_bytes(m) each
 };
 
-// up / gate / down: the layer's sparse nodes as above; pred_*: the tensors build_predictor reads for layer l+1
-// (llama-graph.cpp:865-894); sparse_idx_next: the tensor the predictor's SIGMOID node writes.  il selects the list parity.
+// up / gate / down: the layer's sparse nodes as above; x_pred: the tensor build_predictor is called on for layer l+1 (the FFN's
+// own input, llama-graph.cpp:939-946; for the predictor-only call of layer 0 its own input); pred_*: the weights build_predictor
+// reads (llama-graph.cpp:865-894); sparse_idx_next: the tensor the predictor's SIGMOID node writes.  il selects the list parity.
 void spif_glue_lookahead(ggml_backend_cuda_context & ctx, spif_glue_lookahead_state & st, int il, int arch, const ggml_tensor * up,
-                         const ggml_tensor * gate, ggml_tensor * down, const ggml_tensor * pred_up, const ggml_tensor * pred_up_b,
-                         const ggml_tensor * pred_down, const ggml_tensor * pred_down_b, ggml_tensor * sparse_idx_next) {
+                         const ggml_tensor * gate, ggml_tensor * down, const ggml_tensor * x_pred, const ggml_tensor * pred_up,
+                         const ggml_tensor * pred_up_b, const ggml_tensor * pred_down, const ggml_tensor * pred_down_b,
+                         ggml_tensor * sparse_idx_next) {
     spif_ffn_args  a = {};
     spif_pred_args q = {};
     const bool     has_ffn = up != NULL, has_pred = pred_up != NULL;
@@ -184,7 +186,8 @@ void spif_glue_lookahead(ggml_backend_cuda_context & ctx, spif_glue_lookahead_st
         q.bpu    = pred_up_b ? (const float *) pred_up_b->data : NULL;
         q.wpd    = pred_down->data;
         q.bpd    = pred_down_b ? (const float *) pred_down_b->data : NULL;
-        q.x      = has_ffn ? a.x : (const float *) sparse_idx_next->src[0]->data;  // look-ahead: the FFN's own input
+        GGML_ASSERT(x_pred != NULL && (!has_ffn || x_pred->data == up->src[1]->data));  // look-ahead: the FFN's own input
+        q.x      = (const float *) x_pred->data;
         q.sparse_idx_out = (float *) sparse_idx_next->data;
         n_embd = q.n_embd, n_ff = n_ff ? n_ff : q.m;
     }

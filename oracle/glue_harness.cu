@@ -185,3 +185,147 @@ extern "C" int spif_gluetest_layer(int arch, int wtype, const void * w_up, const
     ggml_free(c);
     return 0;
 }
+
+// ---- the look-ahead glue on a two-layer chain ---------------------------------------------------------------------------
+// Reference order (src/llama-graph.cpp:932-946): layer 0 predicts its own mask from x_0; while layer 0 runs, the mask of
+// layer 1 is predicted from x_0 too (the FFN's input); then layer 1 runs on x_1.  Pass A: build_predictor's six nodes and
+// build_sparse_ffn's nodes through the reference's kernels.  Pass B: three spif_glue_lookahead calls (predictor only;
+// FFN 0 + predictor 1; FFN 1 only) on the same tensors.
+#include "mmvf.cuh"
+#include "spif_b200.h"
+
+struct spif_glue_lookahead_state {
+    spif_shard_comm comm;
+    void *          list[2];
+};
+void spif_glue_lookahead(ggml_backend_cuda_context & ctx, spif_glue_lookahead_state & st, int il, int arch, const ggml_tensor * up,
+                         const ggml_tensor * gate, ggml_tensor * down, const ggml_tensor * x_pred, const ggml_tensor * pred_up,
+                         const ggml_tensor * pred_up_b, const ggml_tensor * pred_down, const ggml_tensor * pred_down_b,
+                         ggml_tensor * sparse_idx_next);
+
+namespace {
+void ref_pred_node(ggml_backend_cuda_context & ctx, ggml_tensor * n) {
+    switch (n->op) {
+        case GGML_OP_MUL_MAT:
+            ggml_cuda_mul_mat_vec_f(ctx, n->src[0], n->src[1], nullptr, n, nullptr);  // n_tok == 1 (ggml-cuda.cu mul_mat dispatch)
+            break;
+        case GGML_OP_ADD:
+            ggml_cuda_op_add(ctx, n);
+            break;
+        case GGML_OP_UNARY:
+            if (ggml_get_unary_op(n) == GGML_UNARY_OP_RELU) {
+                ggml_cuda_op_relu(ctx, n);
+            } else {
+                GGML_ASSERT(ggml_get_unary_op(n) == GGML_UNARY_OP_SIGMOID);
+                ggml_cuda_op_sigmoid(ctx, n);
+            }
+            break;
+        default:
+            GGML_ABORT("glue harness: unexpected predictor op %s", ggml_op_name(n->op));
+    }
+}
+}  // namespace
+
+// weights: [2] device pointers per matrix (layer 0, layer 1); x: [2][n_embd]; outputs: p_* [2][n_ff], y_* [2][n_embd] (device)
+extern "C" int spif_gluetest_lookahead(int wtype, void ** w_up, void ** w_gate, void ** w_down, void ** wpu, void ** wpd, float ** bpd,
+                                       const float * x, int n_embd, int n_ff, int r, float * p_ref, float * p_glue, float * y_ref,
+                                       float * y_glue) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        return -1;
+    }
+    ggml_backend_cuda_context ctx(dev);
+    cudaStream_t              st = ctx.stream();
+    ggml_init_params ip = { ggml_tensor_overhead() * 128 + ggml_graph_overhead(), nullptr, /*no_alloc=*/true };
+    ggml_context *   c  = ggml_init(ip);
+    ggml_cgraph *    gf = ggml_new_graph(c);
+    std::vector<void *> bufs;
+    auto out_buf = [&](ggml_tensor * n) {
+        void * d = nullptr;
+        CUDA_CHECK(cudaMalloc(&d, ggml_nbytes(n)));
+        n->data = d;
+        bufs.push_back(d);
+    };
+    ggml_tensor * X[2], * PU[2], * PD[2], * BPD[2], * Wu[2], * Wg[2], * Wd[2], * sig[2], * up[2], * gate[2], * down[2];
+    for (int l = 0; l < 2; ++l) {
+        X[l]   = leaf(c, GGML_TYPE_F32, n_embd, 1, x + (size_t) l * n_embd);
+        PU[l]  = leaf(c, (ggml_type) wtype, n_embd, r, wpu[l]);
+        PD[l]  = leaf(c, (ggml_type) wtype, r, n_ff, wpd[l]);
+        BPD[l] = leaf(c, GGML_TYPE_F32, n_ff, 1, bpd[l]);
+        Wu[l]  = leaf(c, (ggml_type) wtype, n_embd, n_ff, w_up[l]);
+        Wg[l]  = leaf(c, (ggml_type) wtype, n_embd, n_ff, w_gate[l]);
+        Wd[l]  = leaf(c, (ggml_type) wtype, n_embd, n_ff, w_down[l]);
+    }
+    // build_predictor (llama-graph.cpp:865-894) for both layers, both from x_0 (layer 0: its own input; layer 1: look-ahead)
+    std::vector<ggml_tensor *> pred_nodes[2];
+    for (int l = 0; l < 2; ++l) {
+        ggml_tensor * cur = ggml_mul_mat(c, PU[l], X[0]);
+        pred_nodes[l].push_back(cur);
+        cur = ggml_relu(c, cur);
+        pred_nodes[l].push_back(cur);
+        cur = ggml_mul_mat(c, PD[l], cur);
+        pred_nodes[l].push_back(cur);
+        cur = ggml_add(c, cur, BPD[l]);
+        pred_nodes[l].push_back(cur);
+        cur = ggml_sigmoid(c, cur);
+        pred_nodes[l].push_back(cur);
+        sig[l] = cur;
+        for (ggml_tensor * n : pred_nodes[l]) {
+            out_buf(n);
+        }
+    }
+    // build_sparse_ffn (ProSparse recipe) for both layers on x_l with the predicted sparse_idx
+    std::vector<ggml_tensor *> ffn_nodes[2];
+    for (int l = 0; l < 2; ++l) {
+        up[l]   = ggml_mul_mat_sparse(c, Wu[l], X[l], sig[l], nullptr);
+        gate[l] = ggml_mul_mat_sparse(c, Wg[l], X[l], sig[l], nullptr);
+        ggml_tensor * act = ggml_fatrelu(c, gate[l], 0.01f, false);
+        ggml_tensor * hid = ggml_mul(c, act, up[l]);
+        down[l]           = ggml_axpy_sparse(c, Wd[l], hid, sig[l], nullptr);
+        ffn_nodes[l]      = { up[l], gate[l], act, hid, down[l] };
+        for (ggml_tensor * n : ffn_nodes[l]) {
+            out_buf(n);
+        }
+    }
+    (void) gf;
+    const size_t pb = sizeof(float) * (size_t) n_ff, yb = sizeof(float) * (size_t) n_embd;
+    // A: reference kernels, reference order
+    for (ggml_tensor * n : pred_nodes[0]) ref_pred_node(ctx, n);
+    for (ggml_tensor * n : pred_nodes[1]) ref_pred_node(ctx, n);
+    for (int l = 0; l < 2; ++l) {
+        for (ggml_tensor * n : ffn_nodes[l]) ref_node(ctx, n);
+        CUDA_CHECK(cudaMemcpyAsync(p_ref + (size_t) l * n_ff, sig[l]->data, pb, cudaMemcpyDeviceToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(y_ref + (size_t) l * n_embd, down[l]->data, yb, cudaMemcpyDeviceToDevice, st));
+    }
+    // B: the look-ahead glue.  Persistent state as the cache manager would create it once: zeroed comm (world 1), two lists.
+    spif_glue_lookahead_state ls = {};
+    ls.comm.rank = 0, ls.comm.world = 1, ls.comm.cap_floats = (n_embd + r + 3) / 4 * 4;
+    const size_t cb = spif_shard_comm_data_bytes(1, ls.comm.cap_floats);
+    CUDA_CHECK(cudaMalloc(&ls.comm.data[0], cb));
+    CUDA_CHECK(cudaMalloc(&ls.comm.seq, sizeof(uint32_t) * SPIF_COMM_SEQ_WORDS));
+    CUDA_CHECK(cudaMemsetAsync(ls.comm.data[0], 0, cb, st));
+    CUDA_CHECK(cudaMemsetAsync(ls.comm.seq, 0, sizeof(uint32_t) * SPIF_COMM_SEQ_WORDS, st));
+    for (int k = 0; k < 2; ++k) {
+        CUDA_CHECK(cudaMalloc(&ls.list[k], spif_active_list_bytes(n_ff)));
+    }
+    for (int l = 0; l < 2; ++l) {  // poison what pass B must write
+        CUDA_CHECK(cudaMemsetAsync(sig[l]->data, 0xFF, pb, st));
+        CUDA_CHECK(cudaMemsetAsync(down[l]->data, 0xFF, yb, st));
+    }
+    spif_glue_lookahead(ctx, ls, 0, 0, nullptr, nullptr, nullptr, X[0], PU[0], nullptr, PD[0], BPD[0], sig[0]);   // predictor(0) from x_0
+    spif_glue_lookahead(ctx, ls, 0, 0, up[0], gate[0], down[0], X[0], PU[1], nullptr, PD[1], BPD[1], sig[1]);     // FFN(0) + predictor(1)
+    spif_glue_lookahead(ctx, ls, 1, 0, up[1], gate[1], down[1], nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);  // FFN(1)
+    for (int l = 0; l < 2; ++l) {
+        CUDA_CHECK(cudaMemcpyAsync(p_glue + (size_t) l * n_ff, sig[l]->data, pb, cudaMemcpyDeviceToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(y_glue + (size_t) l * n_embd, down[l]->data, yb, cudaMemcpyDeviceToDevice, st));
+    }
+    int err = 0;
+    const int rc = spif_shard_comm_status(&ls.comm, &err, (spif_stream_t) st);
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    for (void * d : bufs) {
+        cudaFree(d);
+    }
+    cudaFree(ls.comm.data[0]), cudaFree(ls.comm.seq), cudaFree(ls.list[0]), cudaFree(ls.list[1]);
+    ggml_free(c);
+    return rc ? rc : err;
+}

@@ -85,3 +85,56 @@ def test_glue_runs_reference_graph_on_gpu(arch, wtype, n_embd, n_ff):
     y_cpu = o.sparse_ffn(arch, wtype, qu, qg, qd, x, p, n_embd, n_ff)[0][0]
     assert rel(y_ops, y_cpu) < tol_cpu and rel(y_fused, y_cpu) < tol_cpu
     assert rel(up_glue, o.mul_mat_sparse(wtype, qu, x, p, n_embd, n_ff)[0]) < tol_cpu
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_embd,r,n_ff", [(1024, 256, 4096), (5120, 1024, 13824)])
+def test_glue_lookahead_chain_on_gpu(n_embd, r, n_ff):
+    """spif_glue_lookahead (the single-launch fast path) on a two-layer chain of the reference's tensors: predictor(0); FFN(0) +
+    predictor(1) from x_0; FFN(1) -- against build_predictor's and build_sparse_ffn's nodes run through the reference's own CUDA
+    kernels in the reference's order.  Masks may differ only where the probability is within 1e-3 of the threshold (the reference's
+    predictor runs mul_mat_vec_f with half2 products); if they agree, y must agree to 2e-3."""
+    import ctypes
+
+    import numpy as np
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    if not os.path.exists(GLUETEST):
+        pytest.skip("oracle/_ref/libspif_gluetest.so not built (needs /root/reference at build time)")
+    import synth
+    from oracle_lib import F16, Oracle
+    lib = ctypes.CDLL(GLUETEST)
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    lib.spif_gluetest_lookahead.restype = ci
+    lib.spif_gluetest_lookahead.argtypes = [ci] + [vp] * 7 + [ci, ci, ci] + [vp] * 4
+    o = Oracle()
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    keep, cols = [], [[] for _ in range(6)]
+    for l in range(2):
+        seed = synth.SEED0 + 9 * n_embd + n_ff + 100 * l
+        Wu, Wg, Wd = synth.ffn_weights(n_embd, n_ff, seed)
+        wpu, wpd, bpd = synth.predictor_weights(n_embd, r, n_ff, 0.1, seed + 3)
+        ts = [dev(o.quantize(F16, w)) for w in (Wu, Wg, Wd, wpu, wpd)] + [dev(bpd)]
+        keep.append(ts)
+        for k, t in enumerate(ts):
+            cols[k].append(t.data_ptr())
+    arrs = [(vp * 2)(*c) for c in cols]
+    x = dev(np.concatenate([synth.activations(n_embd, 1, synth.SEED0 + 77 + l) for l in range(2)]))
+    p_ref, p_glue = torch.zeros((2, n_ff), device="cuda"), torch.zeros((2, n_ff), device="cuda")
+    y_ref, y_glue = torch.zeros((2, n_embd), device="cuda"), torch.zeros((2, n_embd), device="cuda")
+    ptr = lambda t: vp(t.data_ptr())
+    rc = lib.spif_gluetest_lookahead(F16, *[ctypes.cast(a, vp) for a in arrs], ptr(x), n_embd, n_ff, r, ptr(p_ref), ptr(p_glue),
+                                     ptr(y_ref), ptr(y_glue))
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    p_ref, p_glue, y_ref, y_glue = (t.cpu().numpy() for t in (p_ref, p_glue, y_ref, y_glue))
+    assert np.all(np.isfinite(p_glue)) and np.all(np.isfinite(y_glue))
+    assert np.abs(p_glue - p_ref).max() < 2e-3
+    flips = (p_glue < 0.5) != (p_ref < 0.5)
+    assert np.all(np.abs(p_ref[flips] - 0.5) < 1e-3), int(flips.sum())
+    rel = lambda a, b: float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+    for l in range(2):
+        if not flips[l].any():
+            assert rel(y_glue[l], y_ref[l]) < 2e-3, (l, rel(y_glue[l], y_ref[l]))
+    assert 0.03 < float((~(p_glue < 0.5)).mean()) < 0.3       # a real mask, not all-or-nothing

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SPIF_B200_ABI_VERSION 3
+#define SPIF_B200_ABI_VERSION 4
 
 typedef struct CUstream_st * spif_stream_t; /* == cudaStream_t */
 
@@ -192,6 +192,9 @@ typedef struct spif_shard_comm {
     int32_t reserved;
     void *  data[SPIF_COMM_MAX_WORLD];  /* 8-byte words [2][world][cap_floats]  (spif_shard_comm_data_bytes), 16-byte aligned */
     void *  seq;                        /* local uint32_t [SPIF_COMM_SEQ_WORDS], zero-initialised: [0] calls completed, [2] error */
+    void *  mc;                         /* nullable: a MULTICAST mapping of the same buffers (NVLS: cuMulticastBindMem / torch symmetric
+                                           memory's multicast_ptr).  One store through it lands in every rank's copy: the kernels then
+                                           issue one store per word instead of one per peer.  NULL: unicast stores to data[r]. */
 } spif_shard_comm;
 size_t spif_shard_comm_data_bytes(int world, int cap_floats);
 /* y[0..n) = sum over ranks of y, in place; n % 4 == 0, n <= cap_floats */

@@ -38,7 +38,7 @@ class LayerIo(ctypes.Structure):
 class ShardCommStruct(ctypes.Structure):
     """struct spif_shard_comm (include/spif_b200.h)"""
     _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("cap_floats", ctypes.c_int32),
-                ("reserved", ctypes.c_int32), ("data", c_vp * 8), ("seq", c_vp)]
+                ("reserved", ctypes.c_int32), ("data", c_vp * 8), ("seq", c_vp), ("mc", c_vp)]
 
 
 # name -> (restype, argtypes); every symbol include/spif_b200.h declares

@@ -27,6 +27,7 @@
 struct spif_comm_dev {
     uint2 *    data[SPIF_COMM_MAX_WORLD];  // [2][world][cap] words {float bits, seq}
     uint32_t * seq;                        // local control words, see above
+    uint2 *    mc;                         // nullable: multicast mapping of the buffers (one store reaches every rank's copy)
     int        rank, world, cap;
 };
 
@@ -86,12 +87,19 @@ __device__ __forceinline__ float4 spif_peer_allreduce_f4(const spif_comm_dev & c
     const uint32_t par     = seq & 1u;
     const size_t   out_off = ((size_t) par * c.world + c.rank) * c.cap + (size_t) idx4 * 4;
     const uint32_t mine[4] = { __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w) };
-#pragma unroll 1
-    for (int r = 1; r < c.world; ++r) {  // start with the next rank: spreads the stores over the links
-        const int dst = (c.rank + r) % c.world;
+    if (c.mc) {  // NVLS multicast: the switch replicates the word into every rank's buffer (our own copy is never read)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            st_word_sys(c.data[dst] + out_off + e, mine[e], seq);
+            st_word_sys(c.mc + out_off + e, mine[e], seq);
+        }
+    } else {
+#pragma unroll 1
+        for (int r = 1; r < c.world; ++r) {  // start with the next rank: spreads the stores over the links
+            const int dst = (c.rank + r) % c.world;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                st_word_sys(c.data[dst] + out_off + e, mine[e], seq);
+            }
         }
     }
     uint2 w[SPIF_COMM_MAX_WORLD][4];
@@ -149,6 +157,7 @@ static inline int spif_comm_to_dev(const spif_shard_comm * h, spif_comm_dev & d)
         d.data[r] = (uint2 *) h->data[r];
     }
     d.seq   = (uint32_t *) h->seq;
+    d.mc    = (h->world > 1) ? (uint2 *) h->mc : nullptr;
     d.rank  = h->rank;
     d.world = h->world;
     d.cap   = h->cap_floats;

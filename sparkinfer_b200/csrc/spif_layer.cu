@@ -668,8 +668,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer_kernel(const __grid_consta
                         float     z   = k + bpu_s[row - ra];
                         z             = (z > 0.f) ? z : 0.f;
                         const size_t off = ((size_t) par * world + p.comm.rank) * p.comm.cap + h1_off + row;
-                        for (int r = 0; r < world; ++r) {
-                            st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
+                        if (p.comm.mc) {
+                            st_word_sys(p.comm.mc + off, __float_as_uint(z), seq);
+                        } else {
+                            for (int r = 0; r < world; ++r) {
+                                st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
+                            }
                         }
                     }
                     if (d.y + d.z >= rb) {  // hint for the pollers: this CTA's words are on their way (not a release: every

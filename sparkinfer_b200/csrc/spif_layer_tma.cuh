@@ -547,8 +547,12 @@ __global__ void __launch_bounds__(MAXT, 1) spif_layer4_kernel(const __grid_const
                         float     z   = s + bpu_s[row - ra];
                         z             = (z > 0.f) ? z : 0.f;
                         const size_t off = ((size_t) par * world + p.comm.rank) * p.comm.cap + h1_off + row;
-                        for (int r = 0; r < world; ++r) {
-                            st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
+                        if (p.comm.mc) {  // one multicast store instead of one per shard
+                            st_word_sys(p.comm.mc + off, __float_as_uint(z), seq);
+                        } else {
+                            for (int r = 0; r < world; ++r) {
+                                st_word_sys(p.comm.data[r] + off, __float_as_uint(z), seq);
+                            }
                         }
                     }
                     if (a + n >= rb) {  // hint for the pollers (not a release: every word carries its own sequence number)

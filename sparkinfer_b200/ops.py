@@ -74,7 +74,13 @@ class ShardComm:
             self.buf = symm.empty(data_b, dtype=torch.uint8, device=device)
             self.buf.zero_()
             self.handle = symm.rendezvous(self.buf, group)
-            ptrs = [int(p) for p in self.handle.buffer_ptrs]
+            off = int(getattr(self.handle, "offset", 0) or 0)
+            ptrs = [int(p) + off for p in self.handle.buffer_ptrs]
+            assert ptrs[rank] == self.buf.data_ptr(), "symmetric-memory offset"
+            # NVLS multicast mapping of the same buffers (one store reaches every rank): SPIF_COMM_MULTICAST=0 keeps unicast stores
+            import os
+            mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            self.multicast = (mc + off) if (mc and os.environ.get("SPIF_COMM_MULTICAST", "1") != "0") else 0
             torch.cuda.synchronize()
             torch.distributed.barrier(group)  # everybody's buffers are zero before anyone stores into them
         self.seq = torch.zeros(self.SEQ_WORDS, dtype=torch.int32, device=device)
@@ -83,6 +89,7 @@ class ShardComm:
         for r in range(world):
             c.data[r] = ptrs[r]
         c.seq = self.seq.data_ptr()
+        c.mc = getattr(self, "multicast", 0) or None
         self.c = c
         self.rank, self.world, self.cap = rank, world, cap
 

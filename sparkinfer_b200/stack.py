@@ -51,6 +51,8 @@ class FfnStack:
             torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN, group=group)
             self.comm = comm if int(ok.item()) == 1 else None
         self.exchange = "none" if group is None else ("peer" if self.comm is not None else "nccl")
+        if self.exchange == "peer" and getattr(self.comm, "multicast", 0):
+            self.exchange = "peer+multicast"
         self.flags = flags
         self.ws = ops.Workspace(n_embd, n_ff_local, n_tok, device)
         self.x = torch.zeros((self.L, n_tok, n_embd), dtype=torch.float32, device=device)

@@ -307,6 +307,37 @@ int  spif_model_split_perm(const spif_model_split * ms, int layer, int32_t * per
 int  spif_model_split_write(const char * path_host, int group_size, const float * pattern_host, int n_layer,
                             const int32_t * perms_host /* [n_layer][n_ff] */, int n_ff);
 
+/* ---- model file (GGUF): the path's hyper-parameters and tensors, host code ------------------------------------------------
+ * Consumer of what the reference's loader reads for this path from the model GGUF (src/llama-model.cpp:661, 2730-2768;
+ * written by convert_hf_to_gguf.py:4597-4648 -- sparkinfer_b200/convert.py is the producer here):
+ *   KV      general.architecture, {arch}.block_count / embedding_length / feed_forward_length /
+ *           attention.layer_norm_rms_epsilon, {arch}.pred_lora (predictor rank per layer, 0 = dense layer);
+ *   tensors blk.N.ffn_up.weight, blk.N.ffn_gate.weight {n_embd, n_ff}; blk.N.ffn_down.weight TRANSPOSED {n_embd, n_ff} (one
+ *           row per neuron, the w_down_t of spif_ffn_args); blk.N.ffn_pred_up.weight {n_embd, r}, blk.N.ffn_pred_down.weight
+ *           {r, n_ff}, their optional .bias; blk.N.ffn_norm.weight {n_embd}.
+ * GGUF v2/v3, mapped read-only; spif_gguf_read copies rows [row0, row0 + n_rows) of one tensor (a row = ne[0] elements; a 1-D
+ * tensor = ne[0] rows of one element) into caller memory, so a GPU shard stages only the neuron rows it holds.  `type` is the
+ * ggml type id, equal to SPIF_TYPE_* for the types the library computes in (I32 = 26 is readable too); nbytes = 0 marks a type
+ * the path does not read (spif_gguf_read: SPIF_E_TYPE).  SPIF_E_SHAPE: malformed / truncated file, missing key or tensor.  */
+typedef struct spif_gguf spif_gguf;
+typedef struct spif_gguf_tensor {
+    int32_t  type;
+    int32_t  n_dims;
+    int64_t  ne[4];   /* ggml order: ne[0] = row length in elements, ne[1] = rows */
+    uint64_t offset;  /* of the tensor's first byte from the start of the file */
+    uint64_t nbytes;
+} spif_gguf_tensor;
+int  spif_gguf_open(const char * path_host, spif_gguf ** out);
+void spif_gguf_close(spif_gguf * g);
+int  spif_gguf_hparams(const spif_gguf * g, char * arch_out, int arch_cap, int32_t * n_layer, int32_t * n_embd, int32_t * n_ff,
+                       float * rms_eps);
+int  spif_gguf_pred_rank(const spif_gguf * g, int32_t * ranks_out, int n_layer);
+int  spif_gguf_n_tensors(const spif_gguf * g);
+int  spif_gguf_tensor_at(const spif_gguf * g, int i, char * name_out, int name_cap, spif_gguf_tensor * out);
+int  spif_gguf_find(const spif_gguf * g, const char * name, spif_gguf_tensor * out);
+int  spif_gguf_read(const spif_gguf * g, const spif_gguf_tensor * t, int64_t row0, int64_t n_rows, void * dst_host,
+                    size_t dst_bytes);
+
 /* ---- online shard balancer: host-side state (plan -> exec -> anchor) ----------------------------------------------------
  * Counterpart of the reference's per-layer cache state (cache_meta, group_maps, dfr_decay_pack: src/llama-sparkinfer.h,
  * ggml/include/ggml-sparkinfer.hpp:16-24) and of the plan / exec / anchor split of ggml_sparkinfer_reload

@@ -35,6 +35,12 @@ class LayerIo(ctypes.Structure):
     _fields_ = [("norm_w", c_vp), ("norm_eps", ctypes.c_float), ("reserved", ctypes.c_int32), ("residual", c_vp)]
 
 
+class GgufTensor(ctypes.Structure):
+    """struct spif_gguf_tensor (include/spif_b200.h)"""
+    _fields_ = [("type", ctypes.c_int32), ("n_dims", ctypes.c_int32), ("ne", ctypes.c_int64 * 4), ("offset", ctypes.c_uint64),
+                ("nbytes", ctypes.c_uint64)]
+
+
 class ShardCommStruct(ctypes.Structure):
     """struct spif_shard_comm (include/spif_b200.h)"""
     _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32), ("cap_floats", ctypes.c_int32),
@@ -87,6 +93,15 @@ SYMBOLS = {
     "spif_model_split_pattern": (c_i, [c_vp, c_vp, c_i]),
     "spif_model_split_perm": (c_i, [c_vp, c_i, c_vp, c_i]),
     "spif_model_split_write": (c_i, [ctypes.c_char_p, c_i, c_vp, c_i, c_vp, c_i]),
+    "spif_gguf_open": (c_i, [ctypes.c_char_p, ctypes.POINTER(c_vp)]),
+    "spif_gguf_close": (None, [c_vp]),
+    "spif_gguf_hparams": (c_i, [c_vp, ctypes.c_char_p, c_i, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32),
+                                ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(c_f)]),
+    "spif_gguf_pred_rank": (c_i, [c_vp, c_vp, c_i]),
+    "spif_gguf_n_tensors": (c_i, [c_vp]),
+    "spif_gguf_tensor_at": (c_i, [c_vp, c_i, ctypes.c_char_p, c_i, ctypes.POINTER(GgufTensor)]),
+    "spif_gguf_find": (c_i, [c_vp, ctypes.c_char_p, ctypes.POINTER(GgufTensor)]),
+    "spif_gguf_read": (c_i, [c_vp, ctypes.POINTER(GgufTensor), c_i64, c_i64, c_vp, c_sz]),
 }
 
 _lib = None

@@ -47,6 +47,8 @@ class ShardBalancer:
         """layers: this rank's LayerWeights (m rows each); shard_of_group: per layer int array [n_g] (same on all ranks).
         Slot s of shard r initially holds the s-th smallest group id placed on r (placement.shard_rows order)."""
         self.layers, self.rank, self.world, self.group = layers, rank, world, group
+        assert all(getattr(w, "up_b", None) is None and getattr(w, "gate_b", None) is None for w in layers), \
+            "the balancer moves weight rows, predictor-down rows and their bias; per-neuron FFN biases (OPT) are not moved"
         self.g = g
         self.L = len(layers)
         self.n_slot = layers[0].m // g

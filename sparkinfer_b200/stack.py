@@ -18,12 +18,15 @@ from . import ops
 
 class LayerWeights:
     """device-resident rows of one layer held by this rank (all byte tensors in ggml row layout)"""
-    __slots__ = ("up", "gate", "down_t", "pred_up", "pred_down", "pred_down_b", "m")
+    __slots__ = ("up", "gate", "down_t", "pred_up", "pred_down", "pred_down_b", "m", "pred_up_b", "up_b", "gate_b", "down_b")
 
-    def __init__(self, up, gate, down_t, pred_up, pred_down, pred_down_b, m):
+    def __init__(self, up, gate, down_t, pred_up, pred_down, pred_down_b, m, pred_up_b=None, up_b=None, gate_b=None,
+                 down_b=None):
         self.up, self.gate, self.down_t = up, gate, down_t
         self.pred_up, self.pred_down, self.pred_down_b = pred_up, pred_down, pred_down_b
         self.m = m
+        # optional F32 biases (llama-graph.cpp:874, 1049-1059, 1136-1139); down_b on ONE shard only: it is added once per sum
+        self.pred_up_b, self.up_b, self.gate_b, self.down_b = pred_up_b, up_b, gate_b, down_b
 
 
 class FfnStack:
@@ -75,19 +78,19 @@ class FfnStack:
     def predict(self, l, x_from):
         w = self.layers[l]
         if self.topk > 0:
-            ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
+            ops.predictor(w.pred_up, w.pred_up_b, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
                           flags=self.flags, ws=self.ws_pred, out=self.p[l], logits_out=self.logits)
             ops.topk_mask(self.logits, self.topk, out=self.p[l])
             return 3
-        ops.predictor(w.pred_up, None, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
+        ops.predictor(w.pred_up, w.pred_up_b, w.pred_down, w.pred_down_b, self.x[x_from], self.p_type, self.r, self.m,
                       flags=self.flags, ws=self.ws_pred, out=self.p[l])
         return 2  # kernels: predictor up GEMV, predictor down GEMV+sigmoid
 
     def ffn(self, l, want_stats=False, mask_stable=False, exchange=False):
         w = self.layers[l]
         fl = self.flags | (ops.FLAG_MASK_STABLE if mask_stable else 0)
-        ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, flags=fl,
-                       ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None,
+        ops.sparse_ffn(self.arch, self.w_type, w.up, w.gate, w.down_t, self.x[l], self.p[l], self.m, up_b=w.up_b,
+                       gate_b=w.gate_b, down_b=w.down_b, flags=fl, ws=self.ws, out=self.y[l], stats=self.stats[l] if want_stats else None,
                        comm=self.comm if (exchange and self.group is not None) else None)
         return 2  # kernels: fused gate/up/act/down, partial reduction (+ shard exchange)
 
@@ -179,10 +182,11 @@ class FfnStack:
         if l_ffn is not None:
             w = self.layers[l_ffn]
             ffn = dict(arch=self.arch, w_type=self.w_type, up=w.up, gate=w.gate, down_t=w.down_t, cur=self.x[l_ffn, 0],
-                       n_ff=self.m, flags=self.flags, out=self.y[l_ffn, 0], stats=self.stats[l_ffn, 0] if want_stats else None)
+                       n_ff=self.m, up_b=w.up_b, gate_b=w.gate_b, down_b=w.down_b, flags=self.flags, out=self.y[l_ffn, 0], stats=self.stats[l_ffn, 0] if want_stats else None)
         if l_pred is not None:
             w = self.layers[l_pred]
-            pred = dict(pred_up=w.pred_up, pred_down=w.pred_down, pred_down_b=w.pred_down_b, cur=self.x[x_from, 0],
+            pred = dict(pred_up=w.pred_up, pred_up_b=w.pred_up_b, pred_down=w.pred_down, pred_down_b=w.pred_down_b,
+                        cur=self.x[x_from, 0],
                         p_type=self.p_type, r=self.r, m=self.m, flags=self.flags, out=self.p[l_pred, 0],
                         logits_out=self.logits[0] if self.topk > 0 else None)
         ops.sparse_ffn_lookahead(self.comm, self.ws, ffn=ffn, pred=pred,
@@ -210,7 +214,8 @@ class FfnStack:
             ops.mask_to_list(self.p[l, 0], out=self.lists[l % 2])
             w = self.layers[l]
             ops.sparse_ffn_lookahead(self.comm, self.ws, ffn=dict(arch=self.arch, w_type=self.w_type, up=w.up, gate=w.gate,
-                                                                  down_t=w.down_t, cur=self.x[l, 0], n_ff=self.m, flags=self.flags,
+                                                                  down_t=w.down_t, cur=self.x[l, 0], n_ff=self.m, up_b=w.up_b,
+                                                                  gate_b=w.gate_b, down_b=w.down_b, flags=self.flags,
                                                                   out=self.y[l, 0], stats=self.stats[l, 0] if want_stats else None),
                                      list_in=self.lists[l % 2])
             n += 2
@@ -256,3 +261,81 @@ class FfnStack:
         if self.graph is None:
             self.capture()
         self.graph.replay()
+
+    # -- from the model file ----------------------------------------------------------------------------------------------
+    ARCH_OF_GGUF = {"prosparse-llama": ops.ARCH_PROSPARSE, "bamboo": ops.ARCH_RELU_GATED, "qwen2": ops.ARCH_RELU_GATED,
+                    "opt": ops.ARCH_RELU_UP, "falcon": ops.ARCH_RELU_UP, "llama": ops.ARCH_SILU_GATED}
+
+    @classmethod
+    def from_gguf(cls, path, n_tok=1, device="cuda", flags=0, layers=None, group=None, rows_of_layer=None, exchange="peer",
+                  topk=0):
+        """the sparse-FFN stack of a model GGUF (sparkinfer_b200/convert.py or the reference's converter), resident on `device`.
+        What the reference's loader does for these tensors (src/llama-model.cpp:2730-2768): blk.N.ffn_up / ffn_gate / ffn_down
+        (transposed: one row per neuron), blk.N.ffn_pred_up / ffn_pred_down (+ .bias), rank from {arch}.pred_lora.
+        layers: which blocks (default all).  Sharded (group != None): rows_of_layer[l] = ascending neuron rows this rank holds
+        (placement.shard_rows); only those rows are read from the file; ffn_pred_up is replicated; b_down goes to rank 0.
+        Rows are staged through pinned host memory.  -> (stack, info dict with norm weights `ffn_norm` [L, n_embd] and rms_eps)"""
+        import numpy as np
+
+        from .gguf_io import GGML_F32, ModelGguf
+        with ModelGguf(path) as g:
+            if g.arch not in cls.ARCH_OF_GGUF:
+                raise ValueError(f"{path}: architecture {g.arch} has no sparse-FFN path")
+            arch = cls.ARCH_OF_GGUF[g.arch]
+            which = list(range(g.n_layer)) if layers is None else list(layers)
+            ranks = {int(g.pred_rank[l]) for l in which}
+            if len(ranks) != 1 or 0 in ranks:
+                raise ValueError(f"{path}: the stack needs one predictor rank for all its layers, pred_lora gives {sorted(ranks)}")
+            r = ranks.pop()
+            rank0 = group is None or torch.distributed.get_rank(group) == 0
+
+            def to_dev(name, rows=None, f32=False):
+                t = g.find(name)
+                if t is None:
+                    return None
+                if f32 and t.type != GGML_F32:
+                    raise ValueError(f"{name}: bias / norm vectors are F32 in the file (type {t.type})")
+                if rows is None:
+                    host = g.read_rows(name)
+                else:  # runs of consecutive rows -> one read each
+                    rows = np.asarray(rows, dtype=np.int64)
+                    cuts = np.nonzero(np.diff(rows) != 1)[0] + 1
+                    host = np.concatenate([g.read_rows(name, int(run[0]), len(run)) for run in np.split(rows, cuts)])
+                pinned = torch.from_numpy(host).pin_memory()
+                d = pinned.to(device, non_blocking=True).reshape(-1)
+                return d.view(torch.float32) if f32 else d
+
+            lw, norms, w_type, p_type, m = [], [], None, None, None
+            for i, l in enumerate(which):
+                rows = None if rows_of_layer is None else rows_of_layer[i]
+                up_t, pu_t = g.find(f"blk.{l}.ffn_up.weight"), g.find(f"blk.{l}.ffn_pred_up.weight")
+                dn_t, pd_t = g.find(f"blk.{l}.ffn_down.weight"), g.find(f"blk.{l}.ffn_pred_down.weight")
+                if None in (up_t, pu_t, dn_t, pd_t):
+                    raise ValueError(f"{path}: layer {l} lacks ffn_up / ffn_down / ffn_pred_up / ffn_pred_down")
+                E, F = int(up_t.ne[0]), int(up_t.ne[1])
+                if (int(dn_t.ne[0]), int(dn_t.ne[1])) != (E, F):
+                    raise ValueError(f"blk.{l}.ffn_down.weight is {dn_t.ne[0]} x {dn_t.ne[1]}: not stored transposed (one row per "
+                                     f"neuron, convert_hf_to_gguf.py:4640-4648)")
+                if (int(pu_t.ne[0]), int(pu_t.ne[1]), int(pd_t.ne[0]), int(pd_t.ne[1])) != (E, r, r, F):
+                    raise ValueError(f"layer {l}: predictor shapes do not fit n_embd {E}, rank {r}, n_ff {F}")
+                if w_type is None:
+                    w_type, p_type, m = int(up_t.type), int(pu_t.type), (F if rows is None else len(rows))
+                if (int(up_t.type), int(dn_t.type), int(pu_t.type), int(pd_t.type)) != (w_type, w_type, p_type, p_type):
+                    raise ValueError(f"layer {l}: mixed tensor types")
+                gate = to_dev(f"blk.{l}.ffn_gate.weight", rows)
+                if (gate is None) != (arch == ops.ARCH_RELU_UP):
+                    raise ValueError(f"layer {l}: ffn_gate does not match architecture {g.arch}")
+                lw.append(LayerWeights(
+                    up=to_dev(f"blk.{l}.ffn_up.weight", rows), gate=gate, down_t=to_dev(f"blk.{l}.ffn_down.weight", rows),
+                    pred_up=to_dev(f"blk.{l}.ffn_pred_up.weight"), pred_down=to_dev(f"blk.{l}.ffn_pred_down.weight", rows),
+                    pred_down_b=to_dev(f"blk.{l}.ffn_pred_down.bias", rows, f32=True), m=m,
+                    pred_up_b=to_dev(f"blk.{l}.ffn_pred_up.bias", f32=True), up_b=to_dev(f"blk.{l}.ffn_up.bias", rows, f32=True),
+                    gate_b=to_dev(f"blk.{l}.ffn_gate.bias", rows, f32=True),
+                    down_b=to_dev(f"blk.{l}.ffn_down.bias", f32=True) if rank0 else None))
+                norms.append(to_dev(f"blk.{l}.ffn_norm.weight", f32=True))
+            torch.cuda.synchronize(device)
+            st = cls(arch, w_type, p_type, g.n_embd, m, r, lw, n_tok=n_tok, group=group, device=device, flags=flags,
+                     exchange=exchange, topk=topk)
+            info = {"arch": g.arch, "n_layer": len(which), "n_embd": g.n_embd, "n_ff": g.n_ff, "r": r, "rms_eps": g.rms_eps,
+                    "ffn_norm": torch.stack(norms) if all(n is not None for n in norms) else None}
+        return st, info

@@ -66,7 +66,7 @@ def test_ctypes_mirrors_match_the_header_layout(tmp_path):
     from sparkinfer_b200 import _lib
     from sparkinfer_b200.balancer import Move
     mirrors = {"spif_ffn_args": _lib.FfnArgs, "spif_pred_args": _lib.PredArgs, "spif_layer_io": _lib.LayerIo,
-               "spif_shard_comm": _lib.ShardCommStruct, "spif_move": Move}
+               "spif_shard_comm": _lib.ShardCommStruct, "spif_move": Move, "spif_gguf_tensor": _lib.GgufTensor}
     src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
     structs = {}
     for name, body in re.findall(r"typedef struct (spif_[a-z_]+) \{(.*?)\}\s*\1;", src, flags=re.S):

@@ -3,7 +3,9 @@
 // libspif_b200.so.  It is compiled against the reference's headers by tests/test_glue.py (nvcc -c, no link), so every
 // field it reads from ggml_tensor / ggml_backend_cuda_context exists with that name and type in the reference tree.
 //
-// How to use it: add this file to GGML_SOURCES_CUDA, link -lspif_b200, and in ggml-cuda.cu
+// How to use it: `patch -p1 < glue/reference_tree.patch` in the reference tree and configure with
+// -DGGML_CUDA_SPIF_B200_DIR=<this checkout> (tests/test_glue.py applies the patch to the reference's files and compiles the
+// patched dispatch).  What the patch does: add this file to GGML_SOURCES_CUDA, link -lspif_b200, and in ggml-cuda.cu
 //   * replace the bodies of ggml_cuda_mul_mat_sparse / ggml_cuda_axpy_sparse (ggml-cuda.cu:2463-2497) by calls to
 //     spif_glue_mul_mat_sparse / spif_glue_axpy_sparse;
 //   * route GGML_OP_FATRELU / GGML_OP_SHIFTED_STEP (ggml-cuda.cu:2802-2807) to spif_glue_fatrelu / spif_glue_shifted_step;

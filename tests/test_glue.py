@@ -29,6 +29,36 @@ def test_glue_compiles_against_reference_headers(tmp_path):
         assert f"U {name}" in syms, f"glue must bind the C-ABI symbol {name}"
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF, "ggml", "src", "ggml-cuda", "ggml-cuda.cu")), reason="reference tree absent")
+def test_reference_tree_patch_applies_and_compiles(tmp_path):
+    """glue/reference_tree.patch (the patched reference tree): applies cleanly to the reference's ggml-cuda.cu
+    and CMakeLists.txt, and the patched dispatch file compiles with -DGGML_CUDA_SPIF_B200, leaving exactly the glue's entry
+    points undefined; without the define the file is the reference's own."""
+    d = tmp_path / "tree" / "ggml" / "src" / "ggml-cuda"
+    d.mkdir(parents=True)
+    for f in ("ggml-cuda.cu", "CMakeLists.txt"):
+        shutil.copy(os.path.join(REF, "ggml", "src", "ggml-cuda", f), d / f)
+    r = subprocess.run(["patch", "-p1", "--no-backup-if-mismatch", "-i", os.path.join(ROOT, "glue", "reference_tree.patch")],
+                       cwd=tmp_path / "tree", capture_output=True, text=True)
+    assert r.returncode == 0 and "FAILED" not in r.stdout and "fuzz" not in r.stdout, r.stdout + r.stderr
+    cm = (d / "CMakeLists.txt").read_text()
+    assert "GGML_CUDA_SPIF_B200_DIR" in cm and "glue/ggml_cuda_spif.cu" in cm and "spif_b200" in cm
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    g = os.path.join(REF, "ggml")
+    cmd = [nvcc, "-std=c++17", "-gencode", "arch=compute_100,code=sm_100", "-c", str(d / "ggml-cuda.cu"), "-o",
+           str(tmp_path / "ggml-cuda.o"), "-I", os.path.join(g, "include"), "-I", os.path.join(g, "src"),
+           "-I", os.path.join(g, "src", "ggml-cuda"), "-DGGML_USE_CUDA", "-DGGML_CUDA_USE_GRAPHS", "-DGGML_CUDA_SPIF_B200",
+           "-DGGML_CUDA_PEER_MAX_BATCH_SIZE=128", "-w"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-4000:]
+    syms = subprocess.run(["nm", "-C", str(tmp_path / "ggml-cuda.o")], capture_output=True, text=True).stdout
+    for name in ("spif_glue_mul_mat_sparse", "spif_glue_axpy_sparse", "spif_glue_fatrelu", "spif_glue_shifted_step",
+                 "spif_glue_try_fuse_sparse_ffn"):
+        assert f"U {name}(" in syms, name
+    # the reference's own sparse kernels are no longer reached from the dispatch
+    assert "ggml_cuda_mul_mat_sparse_q" not in syms and "ggml_cuda_op_fatrelu" not in syms
+
+
 # ---- the glue, executed on a GPU (oracle/glue_harness.cu): the reference's graph, context and pool; its kernels beside ours
 GLUETEST = os.path.join(ROOT, "oracle", "_ref", "libspif_gluetest.so")
 

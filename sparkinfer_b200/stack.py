@@ -268,12 +268,15 @@ class FfnStack:
 
     @classmethod
     def from_gguf(cls, path, n_tok=1, device="cuda", flags=0, layers=None, group=None, rows_of_layer=None, exchange="peer",
-                  topk=0):
+                  topk=0, model_split=None):
         """the sparse-FFN stack of a model GGUF (sparkinfer_b200/convert.py or the reference's converter), resident on `device`.
         What the reference's loader does for these tensors (src/llama-model.cpp:2730-2768): blk.N.ffn_up / ffn_gate / ffn_down
         (transposed: one row per neuron), blk.N.ffn_pred_up / ffn_pred_down (+ .bias), rank from {arch}.pred_lora.
         layers: which blocks (default all).  Sharded (group != None): rows_of_layer[l] = ascending neuron rows this rank holds
         (placement.shard_rows); only those rows are read from the file; ffn_pred_up is replicated; b_down goes to rank 0.
+        model_split: path of a model-split file (`-ms`): the rows are loaded in ITS order (blk.N.ffn_reorder_perms, new_row ->
+        old_row: what the reference's cache manager does at load time, src/llama-sparkinfer.cpp:283-352), and with a group each
+        rank takes its contiguous block of the reordered rows (model_split.shard_rows_from_split); replaces rows_of_layer.
         Rows are staged through pinned host memory.  -> (stack, info dict with norm weights `ffn_norm` [L, n_embd] and rms_eps)"""
         import numpy as np
 
@@ -288,6 +291,13 @@ class FfnStack:
                 raise ValueError(f"{path}: the stack needs one predictor rank for all its layers, pred_lora gives {sorted(ranks)}")
             r = ranks.pop()
             rank0 = group is None or torch.distributed.get_rank(group) == 0
+            if model_split is not None:
+                from .model_split import read_split, shard_rows_from_split
+                _, _, perms = read_split(model_split)
+                if perms.shape[1] != g.n_ff or perms.shape[0] < g.n_layer:
+                    raise ValueError(f"{model_split}: permutations of {perms.shape[1]} rows x {perms.shape[0]} layers do not fit {path}")
+                rows_of_layer = shard_rows_from_split(perms, which, 0 if group is None else torch.distributed.get_rank(group),
+                                                      1 if group is None else torch.distributed.get_world_size(group))
 
             def to_dev(name, rows=None, f32=False):
                 t = g.find(name)

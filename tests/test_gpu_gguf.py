@@ -95,3 +95,34 @@ def test_sharded_rows_from_gguf(oracle, tmp_path):
         ys.append((st.y[0, 0].cpu().numpy(), st.p[0, 0].cpu().numpy()))
     assert ys[1][1].shape == (F // 2,) and np.array_equal(ys[1][1], ys[0][1][halves[0]]) and np.array_equal(ys[2][1], ys[0][1][halves[1]])
     assert rel_err(ys[1][0] + ys[2][0], ys[0][0]) < 1e-5
+
+
+def test_model_split_order_from_gguf(oracle, tmp_path):
+    """profile -> model-split producer -> load in the split's order: masks are the unsplit masks permuted, y is unchanged"""
+    from sparkinfer_b200 import model_split as ms
+    from sparkinfer_b200.convert import convert
+    from sparkinfer_b200.stack import FfnStack
+    model, pred, _ = checkpoint(tmp_path)
+    out = str(tmp_path / "m.gguf")
+    convert(model, out, pred_path=pred, outtype="f16", pred_bias=True)
+    plain, _ = FfnStack.from_gguf(out, device="cuda")
+    xs = np.stack([np.stack([synth.activations(E, 1, synth.SEED0 + 900 + 7 * s + l)[0] for l in range(L)]) for s in range(6)])
+    rates = ms.profile_rates(plain, xs)
+    assert rates.shape == (L, F) and 0.02 < rates.mean() < 0.3
+    pattern, perms = ms.build_split(rates, g=16, n_shards=2)
+    split = str(tmp_path / "ms.gguf")
+    ms.write_split(split, 16, pattern, perms)
+    reordered, _ = FfnStack.from_gguf(out, device="cuda", model_split=split)
+    x = torch.from_numpy(xs[0][:, None, :]).cuda()
+    res = []
+    for st in (plain, reordered):
+        st.x.copy_(x)
+        st.step_fused()
+        torch.cuda.synchronize()
+        res.append((st.p.cpu().numpy(), st.y.cpu().numpy()))
+    for l in range(L):
+        p_new, p_old = res[1][0][l, 0], res[0][0][l, 0][perms[l]]
+        assert np.abs(p_new - p_old).max() < 1e-6, l                         # a row's dot does not depend on where the row sits
+        clear = np.abs(p_old - 0.5) > 1e-5
+        assert np.array_equal((p_new < 0.5)[clear], (p_old < 0.5)[clear]), l
+        assert rel_err(res[1][1][l, 0], res[0][1][l, 0]) < 1e-4, l          # same neurons, another summation order

@@ -233,8 +233,18 @@ int spif_gguf_open(const char * path, spif_gguf ** out) {
     }
     const uint64_t data_start = (c.pos + al - 1) / al * al;
     for (spif_gguf_tensor & t : g->tensors) {
-        const size_t rb = row_bytes_of(t.type, t.ne[0]);
-        t.nbytes        = (uint64_t) rb * (uint64_t) (t.ne[1] * t.ne[2] * t.ne[3]);  // 0: a type the path does not read
+        const size_t rb   = row_bytes_of(t.type, t.ne[0]);
+        uint64_t     rows = 1, nbytes = 0;
+        bool         wraps = false;
+        for (int d = 1; d < 4; ++d) {
+            wraps |= __builtin_mul_overflow(rows, (uint64_t) t.ne[d], &rows);
+        }
+        wraps |= __builtin_mul_overflow(rows, (uint64_t) rb, &nbytes);
+        if (wraps) {
+            delete g;
+            return SPIF_E_SHAPE;
+        }
+        t.nbytes = nbytes;  // 0: a type the path does not read
         t.offset += data_start;
         if (t.offset > g->size || t.nbytes > g->size - t.offset) {
             delete g;

@@ -156,6 +156,16 @@ def test_malformed_files_are_error_codes(tmp_path):
         with pytest.raises(_lib.SpifError) as e:
             ModelGguf(str(p))
         assert e.value.code in (-2, -5), (name, e.value.code)
+    # a tensor whose dimensions multiply past 2^64: rejected, not wrapped into a small size
+    import struct
+    name = b"blk.0.ffn_up.weight"
+    kv = struct.pack("<Q", 20) + b"general.architecture" + struct.pack("<IQ", 8, 5) + b"llama"
+    info = struct.pack("<Q", len(name)) + name + struct.pack("<I4QIQ", 4, 1 << 40, 1 << 40, 1 << 40, 1 << 40, 0, 0)
+    p = tmp_path / "wraps.gguf"
+    p.write_bytes(b"GGUF" + struct.pack("<IQQ", 3, 1, 1) + kv + info + b"\0" * 64)
+    with pytest.raises(_lib.SpifError) as e:
+        ModelGguf(str(p))
+    assert e.value.code == -2
     with pytest.raises(_lib.SpifError):
         ModelGguf(str(tmp_path / "does_not_exist.gguf"))
     with ModelGguf(GOLDEN) as g:

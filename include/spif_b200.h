@@ -24,7 +24,8 @@
  * SPIF_DIRECT_SMALL, SPIF_RED_FIRST, SPIF_FFN_CTAS, SPIF_PDL_LATE, SPIF_DG_WARPS, SPIF_DG_VL, SPIF_DG_ASYNC, SPIF_CTAS_PER_SM,
  * SPIF_STAGES, SPIF_SMEM_SPLIT, SPIF_GU_PCT, SPIF_DSLOTS, SPIF_TOPK_CLUSTER) and two debug switches that do NOT
  * (SPIF_LAYER_DEBUG, SPIF_BATCH_DEBUG: timing floors with the arithmetic or the loads skipped).  Defaults are the measured
- * best; DESIGN.md section 4 lists meaning and default of each.  None is needed in production.
+ * best; DESIGN.md section 4 lists meaning and default of each.  None is needed in production.  The Python host reads two
+ * more: SPIF_COMM_MULTICAST=0 (ShardComm: leave spif_shard_comm.mc NULL, unicast exchange stores) and SPIF_BENCH_VERBOSE.
  */
 #ifndef SPIF_B200_H
 #define SPIF_B200_H

@@ -79,7 +79,10 @@ class ShardComm:
             assert ptrs[rank] == self.buf.data_ptr(), "symmetric-memory offset"
             # NVLS multicast mapping of the same buffers (one store reaches every rank): SPIF_COMM_MULTICAST=0 keeps unicast stores
             import os
-            mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            try:
+                mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            except Exception:  # no NVLS on this box / driver: unicast stores
+                mc = 0
             self.multicast = (mc + off) if (mc and os.environ.get("SPIF_COMM_MULTICAST", "1") != "0") else 0
             torch.cuda.synchronize()
             torch.distributed.barrier(group)  # everybody's buffers are zero before anyone stores into them

@@ -338,6 +338,8 @@ int  spif_gguf_tensor_at(const spif_gguf * g, int i, char * name_out, int name_c
 int  spif_gguf_find(const spif_gguf * g, const char * name, spif_gguf_tensor * out);
 int  spif_gguf_read(const spif_gguf * g, const spif_gguf_tensor * t, int64_t row0, int64_t n_rows, void * dst_host,
                     size_t dst_bytes);
+int  spif_gguf_gather(const spif_gguf * g, const spif_gguf_tensor * t, const int32_t * rows_host, int64_t n_rows, void * dst_host,
+                      size_t dst_bytes); /* row rows_host[i] -> row i of dst: a model-split permutation or a shard's neuron_idx */
 
 /* ---- online shard balancer: host-side state (plan -> exec -> anchor) ----------------------------------------------------
  * Counterpart of the reference's per-layer cache state (cache_meta, group_maps, dfr_decay_pack: src/llama-sparkinfer.h,

@@ -102,6 +102,7 @@ SYMBOLS = {
     "spif_gguf_tensor_at": (c_i, [c_vp, c_i, ctypes.c_char_p, c_i, ctypes.POINTER(GgufTensor)]),
     "spif_gguf_find": (c_i, [c_vp, ctypes.c_char_p, ctypes.POINTER(GgufTensor)]),
     "spif_gguf_read": (c_i, [c_vp, ctypes.POINTER(GgufTensor), c_i64, c_i64, c_vp, c_sz]),
+    "spif_gguf_gather": (c_i, [c_vp, ctypes.POINTER(GgufTensor), c_vp, c_i64, c_vp, c_sz]),
 }
 
 _lib = None

@@ -367,4 +367,27 @@ int spif_gguf_read(const spif_gguf * g, const spif_gguf_tensor * t, int64_t row0
     return 0;
 }
 
+// rows[i] of tensor t -> row i of dst_host, for a row list in any order (a model-split permutation, a shard's neuron_idx):
+// what spif_gguf_read does for a range, row by row in one call
+int spif_gguf_gather(const spif_gguf * g, const spif_gguf_tensor * t, const int32_t * rows_idx, int64_t n_rows, void * dst,
+                     size_t dst_bytes) {
+    SPIF_REQUIRE(g && t && dst && rows_idx, SPIF_E_NULL);
+    const bool    vec  = t->n_dims <= 1;
+    const int64_t rows = vec ? t->ne[0] : t->ne[1] * t->ne[2] * t->ne[3];
+    const size_t  rb   = row_bytes_of(t->type, vec ? 1 : t->ne[0]);
+    SPIF_REQUIRE(rb != 0 && t->nbytes != 0, SPIF_E_TYPE);
+    SPIF_REQUIRE(n_rows >= 0, SPIF_E_SHAPE);
+    SPIF_REQUIRE(dst_bytes >= (size_t) n_rows * rb, SPIF_E_WORKSPACE);
+    SPIF_REQUIRE(t->offset <= g->size && t->nbytes <= g->size - t->offset && (uint64_t) rows * rb == t->nbytes, SPIF_E_SHAPE);
+    for (int64_t i = 0; i < n_rows; ++i) {
+        SPIF_REQUIRE(rows_idx[i] >= 0 && rows_idx[i] < rows, SPIF_E_SHAPE);
+    }
+    const unsigned char * src = g->map + t->offset;
+    unsigned char *       out = (unsigned char *) dst;
+    for (int64_t i = 0; i < n_rows; ++i) {
+        memcpy(out + (size_t) i * rb, src + (size_t) rows_idx[i] * rb, rb);
+    }
+    return 0;
+}
+
 }  // extern "C"

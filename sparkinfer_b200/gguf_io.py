@@ -93,6 +93,20 @@ class ModelGguf:
               f"spif_gguf_read({name})")
         return out
 
+    def gather_rows(self, name, rows, out=None):
+        """rows[i] of tensor `name` -> row i of the result, any order (a model-split permutation, a shard's neuron list)"""
+        t = self.find(name)
+        if t is None:
+            raise KeyError(name)
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        rb = row_bytes(t.type, 1 if t.n_dims <= 1 else t.ne[0])
+        if out is None:
+            out = np.empty((rows.size, rb), dtype=np.uint8)
+        assert out.dtype == np.uint8 and out.flags.c_contiguous
+        check(self.L.spif_gguf_gather(self.h, ctypes.byref(t), rows.ctypes.data_as(ctypes.c_void_p), rows.size,
+                                      out.ctypes.data_as(ctypes.c_void_p), out.nbytes), f"spif_gguf_gather({name})")
+        return out
+
 
 # ---- row quantisers (the converter's --outtype) ---------------------------------------------------------------------------
 def _roundf(v):

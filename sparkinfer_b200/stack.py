@@ -307,10 +307,8 @@ class FfnStack:
                     raise ValueError(f"{name}: bias / norm vectors are F32 in the file (type {t.type})")
                 if rows is None:
                     host = g.read_rows(name)
-                else:  # runs of consecutive rows -> one read each
-                    rows = np.asarray(rows, dtype=np.int64)
-                    cuts = np.nonzero(np.diff(rows) != 1)[0] + 1
-                    host = np.concatenate([g.read_rows(name, int(run[0]), len(run)) for run in np.split(rows, cuts)])
+                else:  # a shard's rows / a model-split order: one gather in the library
+                    host = g.gather_rows(name, rows)
                 pinned = torch.from_numpy(host).pin_memory()
                 d = pinned.to(device, non_blocking=True).reshape(-1)
                 return d.view(torch.float32) if f32 else d

@@ -65,6 +65,10 @@ def test_parser_reads_reference_written_file():
             # a shard's rows only
             part = g.read_rows(f"blk.{l}.ffn_down.weight", 16, 32).view(np.float16)
             assert np.array_equal(part, want[16:48])
+            idx = np.random.default_rng(l).permutation(tiny.N_FF)[:40]       # any order, e.g. a model-split permutation
+            assert np.array_equal(g.gather_rows(f"blk.{l}.ffn_down.weight", idx).view(np.float16), want[idx])
+            assert np.array_equal(g.gather_rows(f"blk.{l}.ffn_pred_down.bias", idx).view(np.float32).reshape(-1),
+                                  t[f"pred.{l}.fc2.bias"][idx])
             pu = g.find(f"blk.{l}.ffn_pred_up.weight")
             pd = g.find(f"blk.{l}.ffn_pred_down.weight")
             assert (pu.ne[0], pu.ne[1], pd.ne[0], pd.ne[1]) == (tiny.N_EMBD, tiny.RANK, tiny.RANK, tiny.N_FF)
@@ -174,6 +178,61 @@ def test_malformed_files_are_error_codes(tmp_path):
         with pytest.raises(_lib.SpifError) as e:  # rows past the end
             g.read_rows("blk.0.ffn_up.weight", tiny.N_FF - 4, 8)
         assert e.value.code == -2
+        with pytest.raises(_lib.SpifError) as e:  # a row index outside the tensor
+            g.gather_rows("blk.0.ffn_up.weight", [0, tiny.N_FF])
+        assert e.value.code == -2
         with pytest.raises(_lib.SpifError) as e:  # destination too small
             g.read_rows("blk.0.ffn_up.weight", 0, 8, out=np.empty((8, 2 * tiny.N_EMBD), dtype=np.uint8)[:4])
         assert e.value.code == -4
+
+
+def test_from_gguf_stages_the_rows_it_should(tmp_path, monkeypatch):
+    """FfnStack.from_gguf's host logic without a GPU: device = cpu, pinning and the stack constructor stubbed.  Whole layers,
+    a shard's rows, and a model-split order must hand the constructor exactly the file's rows in that order."""
+    torch = pytest.importorskip("torch")
+    from sparkinfer_b200 import model_split as ms
+    from sparkinfer_b200.convert import convert
+    from sparkinfer_b200.gguf_io import quantize_rows
+    from sparkinfer_b200.stack import FfnStack
+    model, pred = hf_dir(tmp_path)
+    out = str(tmp_path / "m.gguf")
+    convert(model, out, pred_path=pred, outtype="q8_0", pred_bias=True)
+    got = {}
+
+    def fake_init(self, arch, w_type, p_type, n_embd, m, r, layers, **kw):
+        got.update(arch=arch, w_type=w_type, p_type=p_type, n_embd=n_embd, m=m, r=r, layers=layers, kw=kw)
+
+    monkeypatch.setattr(FfnStack, "__init__", fake_init)
+    monkeypatch.setattr(torch.Tensor, "pin_memory", lambda self: self)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    t = tiny.tiny_model()
+    F, E, R = tiny.N_FF, tiny.N_EMBD, tiny.RANK
+
+    def check(rows_per_layer, which):
+        assert (got["arch"], got["w_type"], got["p_type"], got["n_embd"], got["r"]) == (0, Q8_0, F16, E, R)
+        for i, l in enumerate(which):
+            rows = rows_per_layer[i]
+            w = got["layers"][i]
+            assert got["m"] == len(rows) == w.m
+            up = quantize_rows(t[f"model.layers.{l}.mlp.up_proj.weight"], Q8_0)[rows]
+            dn = quantize_rows(t[f"model.layers.{l}.mlp.down_proj.weight"].T, Q8_0)[rows]
+            pd = quantize_rows(t[f"pred.{l}.fc2.weight"], F16)[rows]
+            assert np.array_equal(w.up.numpy().reshape(len(rows), -1), up)
+            assert np.array_equal(w.down_t.numpy().reshape(len(rows), -1), dn)
+            assert np.array_equal(w.pred_down.numpy().reshape(len(rows), -1), pd)
+            assert np.array_equal(w.pred_down_b.numpy(), t[f"pred.{l}.fc2.bias"][rows])
+            assert w.pred_up.numel() == R * E * 2 and np.array_equal(w.pred_up_b.numpy(), t[f"pred.{l}.fc1.bias"])  # replicated
+            assert w.up_b is None and w.gate_b is None and w.down_b is None and w.gate is not None
+
+    st, info = FfnStack.from_gguf(out, device="cpu")
+    check([np.arange(F)] * 2, [0, 1])
+    assert info["ffn_norm"].shape == (2, E) and info["r"] == R
+    mine = np.concatenate([np.arange(16 * gi, 16 * gi + 16) for gi in range(1, F // 16, 2)])  # odd groups: this shard's rows
+    FfnStack.from_gguf(out, device="cpu", layers=[1], rows_of_layer=[mine])
+    check([mine], [1])
+    rates = np.random.default_rng(3).random((2, F))
+    pattern, perms = ms.build_split(rates, g=16)
+    split = str(tmp_path / "ms.gguf")
+    ms.write_split(split, 16, pattern, perms)
+    FfnStack.from_gguf(out, device="cpu", model_split=split)
+    check([perms[0], perms[1]], [0, 1])

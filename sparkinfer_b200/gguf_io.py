@@ -39,7 +39,7 @@ class ModelGguf:
         nl, ne, nf, eps = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32(), ctypes.c_float()
         check(self.L.spif_gguf_hparams(self.h, arch, 64, ctypes.byref(nl), ctypes.byref(ne), ctypes.byref(nf), ctypes.byref(eps)),
               "spif_gguf_hparams")
-        self.arch, self.n_layer, self.n_embd, self.n_ff, self.rms_eps = arch.value.decode(), nl.value, ne.value, nf.value, eps.value
+        self.arch, self.n_layer, self.n_embd, self.n_ff, self.rms_eps = arch.value.decode(errors="surrogateescape"), nl.value, ne.value, nf.value, eps.value
         self.pred_rank = np.zeros(self.n_layer, dtype=np.int32)
         check(self.L.spif_gguf_pred_rank(self.h, self.pred_rank.ctypes.data_as(ctypes.c_void_p), self.n_layer), "spif_gguf_pred_rank")
 
@@ -64,13 +64,13 @@ class ModelGguf:
         out, buf = [], ctypes.create_string_buffer(256)
         for i in range(self.L.spif_gguf_n_tensors(self.h)):
             check(self.L.spif_gguf_tensor_at(self.h, i, buf, 256, None), "spif_gguf_tensor_at")
-            out.append(buf.value.decode())
+            out.append(buf.value.decode(errors="surrogateescape"))  # names are bytes in the file
         return out
 
     def find(self, name):
         """-> _lib.GgufTensor or None (optional tensors: biases, ffn_gate of the ungated architectures)"""
         t = _lib.GgufTensor()
-        rc = self.L.spif_gguf_find(self.h, name.encode(), ctypes.byref(t))
+        rc = self.L.spif_gguf_find(self.h, name.encode(errors="surrogateescape"), ctypes.byref(t))
         if rc == -2:  # SPIF_E_SHAPE: no tensor of that name
             return None
         check(rc, f"spif_gguf_find({name})")

@@ -236,3 +236,35 @@ def test_from_gguf_stages_the_rows_it_should(tmp_path, monkeypatch):
     ms.write_split(split, 16, pattern, perms)
     FfnStack.from_gguf(out, device="cpu", model_split=split)
     check([perms[0], perms[1]], [0, 1])
+
+
+def test_parser_survives_corrupted_headers(tmp_path):
+    """test-gguf.cpp style robustness: bytes of the header region of a valid file overwritten at random -> spif_gguf_open returns
+    (0 or an error code) and, when it opens, every indexed tensor can be read or is refused; never a crash or an overrun."""
+    from sparkinfer_b200 import _lib
+    from sparkinfer_b200.gguf_io import ModelGguf
+    raw = bytearray(open(GOLDEN, "rb").read())
+    head = 2600  # KV + tensor infos of the golden file end before this
+    rng = np.random.default_rng(99)
+    opened = 0
+    for it in range(400):
+        b = bytearray(raw)
+        for _ in range(int(rng.integers(1, 4))):
+            pos = int(rng.integers(4, head))
+            b[pos] = int(rng.integers(0, 256)) if rng.random() < 0.7 else 0xFF
+        if it % 5 == 0:
+            b = b[:int(rng.integers(8, len(b)))]
+        p = tmp_path / "fuzz.gguf"
+        p.write_bytes(bytes(b))
+        try:
+            g = ModelGguf(str(p))
+        except _lib.SpifError:
+            continue
+        opened += 1
+        for n in g.names():
+            try:
+                g.read_rows(n)
+            except (_lib.SpifError, ValueError, KeyError):
+                pass
+        g.close()
+    assert opened > 20  # most single-byte damage to names / values still parses

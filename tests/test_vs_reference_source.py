@@ -1,0 +1,122 @@
+"""CPU: host logic pinned to the REFERENCE'S OWN CODE where that code cannot be linked (it lives inside member functions of
+src/llama-sparkinfer.cpp that need a loaded llama_model and a CUDA context): the statements are cut out of the reference source
+AT TEST TIME, wrapped in a function with the variables they use, compiled with g++ and run beside the library on seeded inputs.
+Nothing of the reference is stored in this repository; skipped where /root/reference is absent (the GPU box).
+
+  * the cache budget split over the layers, ctor src/llama-sparkinfer.cpp:177-202  == spif_cache_group_budget
+  * the swap-list walk of sparkinfer_reload_plan, src/llama-sparkinfer.cpp:45-91: which (incoming group, slot) pairs a
+    wanted-set / resident-set difference produces == the pairing rule the shard balancer keeps (ascending order on both
+    sides, the incoming group takes the slot of the outgoing one)."""
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+REF = os.environ.get("SPIF_REFERENCE", "/root/reference")
+SRC = os.path.join(REF, "src", "llama-sparkinfer.cpp")
+pytestmark = pytest.mark.skipif(not os.path.exists(SRC), reason="reference tree absent")
+
+
+def cut(text, first_marker, end_marker):
+    """the statements from the line containing first_marker up to (not including) the line containing end_marker"""
+    lines = text.splitlines()
+    a = next(i for i, ln in enumerate(lines) if first_marker in ln)
+    b = next(i for i, ln in enumerate(lines) if i > a and end_marker in ln)
+    return "\n".join(lines[a:b])
+
+
+def build(tmp_path, name, code):
+    src = tmp_path / f"{name}.cpp"
+    src.write_text(code)
+    so = tmp_path / f"lib{name}.so"
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-o", str(so), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return ctypes.CDLL(str(so))
+
+
+def test_cache_budget_equals_the_reference_ctor_loops(tmp_path):
+    from sparkinfer_b200 import _lib
+    body = cut(open(SRC).read(), "const int  n_group_cache_budget = vram_budget", "auto create_tensor = ")
+    assert "ffn_norm_pattern[il]" in body and "before_rr" in body, "the reference's loops moved: update the markers"
+    lib = build(tmp_path, "refbudget", f"""
+#include <algorithm>
+#include <cstdint>
+#include <vector>
+extern "C" void ref_budget(int64_t vram_budget, int64_t n_bytes_group, int has_ffn_gate, const float * ffn_norm_pattern,
+                           int n_layer, int n_group, int * out) {{
+{body}
+    for (int il = 0; il < n_layer; ++il) {{
+        out[il] = n_group_cache[il];
+    }}
+}}
+""")
+    L = _lib.load()
+    rng = np.random.default_rng(11)
+    for case in range(300):
+        n_layer = int(rng.integers(1, 81))
+        n_group = int(rng.choice([64, 432, 864, 1024]))
+        gate = int(rng.integers(0, 2))
+        group_bytes = int(rng.choice([16 * 10240, 16 * 5440, 8 * 16384, 16 * 2880]))
+        pattern = rng.random(n_layer).astype(np.float32) + 0.05
+        pattern /= pattern.sum()
+        full = group_bytes * (3 if gate else 2) * n_group * n_layer
+        vram = int(full * rng.choice([0.0, 0.03, 0.25, 0.6, 0.97, 1.0, 1.7]))
+        want = np.zeros(n_layer, dtype=np.int32)
+        got = np.full(n_layer, -7, dtype=np.int32)
+        lib.ref_budget(ctypes.c_int64(vram), ctypes.c_int64(group_bytes), gate, pattern.ctypes.data_as(ctypes.c_void_p), n_layer,
+                       n_group, want.ctypes.data_as(ctypes.c_void_p))
+        assert L.spif_cache_group_budget(vram, group_bytes, gate, pattern.ctypes.data, n_layer, n_group, got.ctypes.data) == 0
+        assert np.array_equal(got, want), (case, n_layer, n_group, gate, vram, got, want)
+
+
+def test_reload_plan_walk_equals_the_reference(tmp_path):
+    """sparkinfer_reload_plan's walk, cut from the reference and run on plain arrays: for wanted-but-absent groups W and
+    resident-but-unwanted groups C (both as 0/1 vectors over the groups) it pairs the k-th W with the k-th C in ascending order
+    and hands the incoming group the outgoing group's cache slot; slot count, neuron_idx and neuron_mask stay consistent.
+    This pins what "a swap" means in the reference; the shard balancer keeps the same rule per move (group_in takes the slot
+    group_out leaves, buffers never resize), which tests/test_sharding.py::test_balancer_state_machine_c_abi checks on
+    spif_balancer_plan / _commit."""
+    text = open(SRC).read()
+    body = cut(text, "int weight_idx = 0;", "reload_records.push_back")
+    assert "group_maps[cache_idx]" in body and "reload_plan[reload_count]" in body, "the reference's walk moved: update the markers"
+    lib = build(tmp_path, "refplan", f"""
+#include <cstdint>
+struct copy_pair {{ int weight_idx, cache_idx; }};
+extern "C" int ref_plan(const float * weight_only, const float * cache_only, int32_t * neuron_idx, int32_t * group_maps,
+                        int32_t * neuron_mask, int g, int n_g, copy_pair * reload_plan) {{
+    int reload_count = 0;
+{body}
+    return reload_count;
+}}
+""")
+    rng = np.random.default_rng(5)
+    for case in range(200):
+        n_g, g = int(rng.choice([8, 32, 64])), int(rng.choice([1, 4, 16]))
+        m_g = int(rng.integers(1, n_g))
+        resident = np.sort(rng.choice(n_g, m_g, replace=False))                 # groups in the cache, slot s holds resident[s]
+        group_maps = np.full(n_g, -1, dtype=np.int32)
+        group_maps[resident] = np.arange(m_g)
+        neuron_mask = np.repeat((group_maps >= 0).astype(np.int32), g)
+        neuron_idx = (resident[:, None] * g + np.arange(g)[None, :]).reshape(-1).astype(np.int32)
+        k = int(rng.integers(0, min(m_g, n_g - m_g) + 1))
+        outgoing = np.sort(rng.choice(resident, k, replace=False))
+        incoming = np.sort(rng.choice(np.setdiff1d(np.arange(n_g), resident), k, replace=False))
+        weight_only = np.zeros(n_g, dtype=np.float32)
+        cache_only = np.zeros(n_g, dtype=np.float32)
+        weight_only[incoming], cache_only[outgoing] = 1, 1
+        plan = np.zeros((max(k, 1), 2), dtype=np.int32)
+        slots_before = group_maps.copy()
+        n = lib.ref_plan(weight_only.ctypes.data_as(ctypes.c_void_p), cache_only.ctypes.data_as(ctypes.c_void_p),
+                         neuron_idx.ctypes.data_as(ctypes.c_void_p), group_maps.ctypes.data_as(ctypes.c_void_p),
+                         neuron_mask.ctypes.data_as(ctypes.c_void_p), g, n_g, plan.ctypes.data_as(ctypes.c_void_p))
+        assert n == k
+        # the rule the balancer keeps: k-th incoming group (ascending) takes the slot of the k-th outgoing group (ascending)
+        for i in range(k):
+            assert plan[i, 0] == incoming[i] and plan[i, 1] == slots_before[outgoing[i]]
+            assert group_maps[incoming[i]] == slots_before[outgoing[i]] and group_maps[outgoing[i]] == -1
+            assert np.array_equal(neuron_idx[plan[i, 1] * g:(plan[i, 1] + 1) * g], incoming[i] * g + np.arange(g))
+        assert np.array_equal(np.repeat((group_maps >= 0).astype(np.int32), g), neuron_mask)
+        assert (group_maps >= 0).sum() == m_g                                   # slots never resize

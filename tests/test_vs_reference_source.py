@@ -4,6 +4,7 @@ AT TEST TIME, wrapped in a function with the variables they use, compiled with g
 Nothing of the reference is stored in this repository; skipped where /root/reference is absent (the GPU box).
 
   * the cache budget split over the layers, ctor src/llama-sparkinfer.cpp:177-202  == spif_cache_group_budget
+  * reorder_tensor_2d / _1d, src/llama-sparkinfer.cpp:293-322                    == spif_reorder_rows
   * the swap-list walk of sparkinfer_reload_plan, src/llama-sparkinfer.cpp:45-91: which (incoming group, slot) pairs a
     wanted-set / resident-set difference produces == the pairing rule the shard balancer keeps (ascending order on both
     sides, the incoming group takes the slot of the outgoing one)."""
@@ -120,3 +121,60 @@ extern "C" int ref_plan(const float * weight_only, const float * cache_only, int
             assert np.array_equal(neuron_idx[plan[i, 1] * g:(plan[i, 1] + 1) * g], incoming[i] * g + np.arange(g))
         assert np.array_equal(np.repeat((group_maps >= 0).astype(np.int32), g), neuron_mask)
         assert (group_maps >= 0).sum() == m_g                                   # slots never resize
+
+
+def test_row_reorder_equals_the_reference_lambdas(tmp_path):
+    """reorder_tensor_2d / reorder_tensor_1d (src/llama-sparkinfer.cpp:293-322), cut from the reference and compiled over a
+    minimal stand-in for ggml_tensor (only the fields and helpers the lambdas touch) == spif_reorder_rows on the same bytes."""
+    from sparkinfer_b200 import _lib
+    body = cut(open(SRC).read(), "auto reorder_tensor_2d = [&]", "auto reorder_if_exists = [&]")
+    assert "perm[new_row]" in body and "perm[new_i]" in body, "the reference's lambdas moved: update the markers"
+    lib = build(tmp_path, "refreorder", f"""
+#include <cstdint>
+#include <cstring>
+#include <vector>
+struct ggml_tensor {{ int type; int64_t ne[4]; size_t nb[4]; void * data; }};
+static size_t ggml_row_size(int type, int64_t n) {{   // the four types of the path (ggml.c type traits)
+    return type == 0 ? 4 * n : type == 1 || type == 30 ? 2 * n : type == 8 ? n / 32 * 34 : type == 2 ? n / 32 * 18 : 0;
+}}
+static int64_t ggml_nrows(const ggml_tensor * t) {{ return t->ne[1] * t->ne[2] * t->ne[3]; }}
+static size_t  ggml_nbytes(const ggml_tensor * t) {{ return ggml_row_size(t->type, t->ne[0]) * ggml_nrows(t); }}
+static void ggml_backend_tensor_get(const ggml_tensor * t, void * dst, size_t off, size_t n) {{ memcpy(dst, (char *) t->data + off, n); }}
+static void ggml_backend_tensor_set(ggml_tensor * t, const void * src, size_t off, size_t n) {{ memcpy((char *) t->data + off, src, n); }}
+extern "C" void ref_reorder(int type, int64_t ne0, int64_t ne1, void * data, const int32_t * perm_in, int one_d) {{
+    ggml_tensor tensor_obj = {{ type, {{ ne0, ne1, 1, 1 }}, {{ 0, 0, 0, 0 }}, data }};
+    tensor_obj.nb[0] = ggml_row_size(type, 1);
+    tensor_obj.nb[1] = ggml_row_size(type, ne0);
+    std::vector<int32_t> perm_v(perm_in, perm_in + (one_d ? ne0 : ne1));
+    std::vector<uint8_t> buf_src(ggml_nbytes(&tensor_obj)), buf_dst(ggml_nbytes(&tensor_obj));
+    auto * src_buf = buf_src.data();
+    auto * dst_buf = buf_dst.data();
+{body}
+    if (one_d) {{
+        reorder_tensor_1d(&tensor_obj, perm_v);
+    }} else {{
+        reorder_tensor_2d(&tensor_obj, perm_v);
+    }}
+}}
+""")
+    L = _lib.load()
+    rng = np.random.default_rng(21)
+    for type_, cols in ((1, 320), (30, 64), (8, 256), (2, 512), (0, 96)):
+        n = int(rng.choice([64, 432, 1024]))
+        rb = L.spif_row_size(type_, cols)
+        src = rng.integers(0, 256, (n, rb), dtype=np.uint8)
+        perm = rng.permutation(n).astype(np.int32)
+        want = src.copy()
+        lib.ref_reorder(type_, ctypes.c_int64(cols), ctypes.c_int64(n), want.ctypes.data_as(ctypes.c_void_p),
+                        perm.ctypes.data_as(ctypes.c_void_p), 0)
+        got = np.empty_like(src)
+        assert L.spif_reorder_rows(src.ctypes.data, got.ctypes.data, perm.ctypes.data, n, rb) == 0
+        assert np.array_equal(got, want) and np.array_equal(got, src[perm])
+    bias = rng.normal(size=864).astype(np.float32)                              # 1-D: a bias / score vector, 4 bytes per row
+    perm = rng.permutation(864).astype(np.int32)
+    want = bias.copy()
+    lib.ref_reorder(0, ctypes.c_int64(864), ctypes.c_int64(1), want.ctypes.data_as(ctypes.c_void_p),
+                    perm.ctypes.data_as(ctypes.c_void_p), 1)
+    got = np.empty_like(bias)
+    assert L.spif_reorder_rows(bias.ctypes.data, got.ctypes.data, perm.ctypes.data, 864, 4) == 0
+    assert np.array_equal(got, want) and np.array_equal(got, bias[perm])

@@ -178,3 +178,92 @@ extern "C" void ref_reorder(int type, int64_t ne0, int64_t ne1, void * data, con
     got = np.empty_like(bias)
     assert L.spif_reorder_rows(bias.ctypes.data, got.ctypes.data, perm.ctypes.data, 864, 4) == 0
     assert np.array_equal(got, want) and np.array_equal(got, bias[perm])
+
+
+REFLIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libspif_ref.so")
+
+
+@pytest.mark.skipif(not os.path.exists(REFLIB), reason="oracle/_ref not built")
+def test_decay_adaptation_equals_the_reference_executor(tmp_path):
+    """The adaptive decay of the balancer (a14).  The reference adapts it in SingleThreadExecutor::make_anchor
+    (ggml/include/ggml-sparkinfer.hpp:143-175): lambda *= 1 +- dx, clamped to [0.05, 0.95], raised when work arrived while the
+    reload was still running.  Here the reference's header itself is INCLUDED (not restated) in a small harness that drives the
+    real executor thread through a raise / lower sequence; spif_balancer_plan is driven through the same sequence by its own
+    trigger (the promised balance held / did not hold).  Same arithmetic, same start value and step from the reference's
+    constants: the trajectories must be bit-identical, including both clamps."""
+    from sparkinfer_b200 import _lib
+    src = tmp_path / "reflambda.cpp"
+    src.write_text("""
+#include "ggml-sparkinfer.hpp"
+#include <future>
+extern "C" float ref_init_decay(void) { return k_spif_init_dfr_decay; }
+extern "C" float ref_dx_decay(void) { return k_spif_dx_dfr_decay; }
+extern "C" void ref_lambda_walk(float * decay2, const int * raise, int n, float * out) {
+    SingleThreadExecutor ex;
+    const auto W = SingleThreadExecutor::SPIF_WAIT_MUL_MAT_SPARSE;
+    for (int i = 0; i < n; ++i) {
+        if (raise[i]) {  // a kernel is submitted while the anchor is still active: it lands in `pending`
+            std::promise<void> gate;
+            auto gf = gate.get_future().share();
+            ex.post([gf] { gf.wait(); });          // keeps the worker busy until the submit below has happened
+            ex.make_anchor(W, decay2);
+            auto fut = ex.submit(W, [] {});
+            gate.set_value();
+            fut.get();                              // runs after the anchor task moved it: decay2 is updated by then
+        } else {         // nothing arrives before the anchor task runs
+            ex.make_anchor(W, decay2);
+            std::promise<void> done;
+            auto df = done.get_future();
+            ex.post([&done] { done.set_value(); });
+            df.get();
+        }
+        out[i] = decay2[0];
+    }
+}
+""")
+    so = tmp_path / "libreflambda.so"
+    r = subprocess.run(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-pthread", "-I", os.path.join(REF, "ggml", "include"),
+                        "-o", str(so), str(src), "-L", os.path.dirname(REFLIB), "-lspif_ref", f"-Wl,-rpath,{os.path.dirname(REFLIB)}"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lib = ctypes.CDLL(str(so))
+    lib.ref_init_decay.restype = ctypes.c_float
+    lib.ref_dx_decay.restype = ctypes.c_float
+    lam0, dx = lib.ref_init_decay(), lib.ref_dx_decay()
+    assert abs(lam0 - 0.67) < 1e-6 and abs(dx - 0.05) < 1e-6
+    rng = np.random.default_rng(2)
+    seq = np.concatenate([np.ones(10), np.zeros(70), np.ones(5), rng.integers(0, 2, 60)]).astype(np.int32)  # both clamps, then mixed
+    decay = np.array([lam0, 1 - lam0], dtype=np.float32)
+    want = np.zeros(seq.size, dtype=np.float32)
+    lib.ref_lambda_walk(decay.ctypes.data_as(ctypes.c_void_p), seq.ctypes.data_as(ctypes.c_void_p), int(seq.size),
+                        want.ctypes.data_as(ctypes.c_void_p))
+    assert want.max() == np.float32(0.95) and want.min() == np.float32(0.05)
+
+    # the library: 1 layer, 4 groups on 2 shards, no swaps allowed (max_swaps = 0), so every plan promises the balance it sees
+    L = _lib.load()
+    sog = np.array([[0, 0, 1, 1]], dtype=np.int32)
+    h = ctypes.c_void_p()
+    assert L.spif_balancer_create(1, 4, 2, 0, sog.ctypes.data, lam0, dx, ctypes.c_float(0.02), ctypes.byref(h)) == 0
+    n_moves, n_swaps = ctypes.c_int(), ctypes.c_int()
+    ib, ia = ctypes.c_float(), ctypes.c_float()
+
+    def plan(a):  # shard 0 carries `a` per slot, shard 1 carries 1: imbalance 2a / (a + 1)
+        scores = np.array([[[a, a]], [[1, 1]]], dtype=np.float32)
+        assert L.spif_balancer_plan(h, scores.ctypes.data, 0, ctypes.c_float(0.0), None, 0, ctypes.byref(n_moves), ctypes.byref(ib),
+                                    ctypes.byref(ia), ctypes.byref(n_swaps)) == 0
+        assert n_moves.value == 0
+        assert L.spif_balancer_commit(h) == 0
+        lam = ctypes.c_float()
+        assert L.spif_balancer_state(h, ctypes.byref(lam), None, None) == 0
+        return lam.value
+
+    a = 1.0
+    assert plan(a) == lam0                      # the first plan has no promise to check: no adaptation
+    got = []
+    for up in seq:
+        prev = 2 * a / (a + 1)
+        a = a * 1.2 if up else 1.0              # the promised balance is missed by more than drift_tol / holds
+        assert not up or 2 * a / (a + 1) > prev * 1.025, "run of raises too long for the imbalance range of this toy layout"
+        got.append(plan(a))
+    L.spif_balancer_destroy(h)
+    assert np.array_equal(np.array(got, dtype=np.float32), want), (got[:12], want[:12])

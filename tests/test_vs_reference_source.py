@@ -5,6 +5,8 @@ Nothing of the reference is stored in this repository; skipped where /root/refer
 
   * the cache budget split over the layers, ctor src/llama-sparkinfer.cpp:177-202  == spif_cache_group_budget
   * reorder_tensor_2d / _1d, src/llama-sparkinfer.cpp:293-322                    == spif_reorder_rows
+  * the decay adaptation of SingleThreadExecutor::make_anchor, ggml/include/ggml-sparkinfer.hpp:143-175 (header INCLUDED, the
+    real executor thread driven)                                                 == spif_balancer_plan's lambda trajectory
   * the swap-list walk of sparkinfer_reload_plan, src/llama-sparkinfer.cpp:45-91: which (incoming group, slot) pairs a
     wanted-set / resident-set difference produces == the pairing rule the shard balancer keeps (ascending order on both
     sides, the incoming group takes the slot of the outgoing one)."""

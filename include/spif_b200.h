@@ -38,7 +38,7 @@ extern "C" {
 #endif
 
 /* bumped when a struct layout or a signature changes; additions of entry points do not bump it.
- * 2: spif_pred_args / look-ahead layer;  3: spif_layer_io, balancer, model split;  4: spif_shard_comm.mc (multicast mapping) */
+ * 3 -> 4: spif_shard_comm gained `mc` (multicast mapping of the exchange buffers) at its end */
 #define SPIF_B200_ABI_VERSION 4
 
 typedef struct CUstream_st * spif_stream_t; /* == cudaStream_t */

@@ -1,4 +1,4 @@
-# usage: bash tools/r2mc.sh N   (NVLS multicast stores for the shard exchange: parity at world 2, then the bench with and without)
+# usage: bash tools/sessions/r2mc.sh N   (NVLS multicast stores for the shard exchange: parity at world 2, then the bench with and without)
 N=${1:-2}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_multi.py -x -q > gpurun_out/r2mc_tests_n$N.log 2>&1; echo "multi tests rc=$?"; tail -3 gpurun_out/r2mc_tests_n$N.log

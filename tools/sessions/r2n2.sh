@@ -1,4 +1,4 @@
-# usage: bash tools/r2n2.sh N    (multi-GPU: parity test, then the bench exactly as the driver launches it)
+# usage: bash tools/sessions/r2n2.sh N    (multi-GPU: parity test, then the bench exactly as the driver launches it)
 N=${1:-2}
 mkdir -p gpurun_out
 if [ "$N" = "2" ]; then
